@@ -1,0 +1,179 @@
+// CSR construction: stable counting sort of edge ids by an int32 key.
+//
+// Replaces the unsorted `index` argument of the reference's scatter_add_ /
+// index_add_ call sites (EGCLStack.py:292-298, PAINNStack.py:254-257,
+// utils/model/model.py:279-286, SCFStack.py:285) by an explicit, reusable CSR.
+//
+// Pipeline (all on `stream`, integer atomics only -- the result is unique):
+//   1. histogram   cnt[key[e]]++ , remembering the (arbitrary) arrival slot
+//   2. scan        rowptr = exclusive prefix sum of cnt
+//   3. scatter     tmp[rowptr[key[e]] + slot[e]] = e
+//   4. segsort     perm[seg] = ascending sort of tmp[seg]   (rank by counting)
+// Step 4 removes the arrival-order nondeterminism of step 1, so perm is the
+// stable order a sequential CPU loop over e = 0..E-1 would produce.
+#include "hgk_common.cuh"
+
+namespace hgk {
+
+thread_local char g_err[512] = {0};
+char* error_buffer() { return g_err; }
+int fail(int status, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return status;
+}
+
+__global__ void __launch_bounds__(256)
+k_csr_hist(const int32_t* __restrict__ key, int64_t E, int32_t N,
+           int32_t* __restrict__ cnt, int32_t* __restrict__ slot) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; e < E; e += stride) {
+    int32_t k = key[e];
+    // out-of-range keys are clamped so a corrupt index cannot write out of bounds
+    k = k < 0 ? 0 : (k >= N ? N - 1 : k);
+    slot[e] = atomicAdd(&cnt[k], 1);
+  }
+}
+
+// Exclusive scan of cnt[0..N) into rowptr[0..N], single CTA, 1024 threads x 8 items.
+constexpr int kScanThreads = 1024;
+constexpr int kScanItems = 8;
+__global__ void __launch_bounds__(kScanThreads)
+k_exclusive_scan(const int32_t* __restrict__ cnt, int64_t N,
+                 int32_t* __restrict__ rowptr) {
+  __shared__ int32_t warp_sums[kScanThreads / 32];
+  __shared__ int32_t carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < N; base += (int64_t)kScanThreads * kScanItems) {
+    int32_t v[kScanItems];
+    int32_t local = 0;
+    const int64_t first = base + (int64_t)tid * kScanItems;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      v[i] = (first + i < N) ? cnt[first + i] : 0;
+      local += v[i];
+    }
+    // inclusive scan of `local` across the CTA
+    int32_t incl = local;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      int32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += t;
+    }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+      int32_t ws = warp_sums[lane];
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, ws, off);
+        if (lane >= off) ws += t;
+      }
+      warp_sums[lane] = ws;  // inclusive over warps
+    }
+    __syncthreads();
+    const int32_t carry = carry_s;
+    int32_t excl = carry + incl - local + (wid > 0 ? warp_sums[wid - 1] : 0);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      if (first + i < N) rowptr[first + i] = excl;
+      excl += v[i];
+    }
+    __syncthreads();
+    if (tid == kScanThreads - 1) carry_s = carry + warp_sums[kScanThreads / 32 - 1];
+    __syncthreads();
+  }
+  if (tid == 0) rowptr[N] = carry_s;
+}
+
+__global__ void __launch_bounds__(256)
+k_csr_scatter(const int32_t* __restrict__ key, int64_t E, int32_t N,
+              const int32_t* __restrict__ rowptr, const int32_t* __restrict__ slot,
+              int32_t* __restrict__ tmp) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; e < E; e += stride) {
+    int32_t k = key[e];
+    k = k < 0 ? 0 : (k >= N ? N - 1 : k);
+    tmp[rowptr[k] + slot[e]] = (int32_t)e;
+  }
+}
+
+// One warp per segment: rank-by-counting sort of distinct int32 values.
+__global__ void __launch_bounds__(256)
+k_csr_segsort(const int32_t* __restrict__ rowptr, int64_t N,
+              const int32_t* __restrict__ tmp, int32_t* __restrict__ perm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t n = warp; n < N; n += nwarps) {
+    const int32_t beg = rowptr[n], end = rowptr[n + 1];
+    const int32_t len = end - beg;
+    for (int32_t t = lane; t < len; t += 32) {
+      const int32_t v = tmp[beg + t];
+      int32_t rank = 0;
+      for (int32_t s = 0; s < len; ++s) rank += (tmp[beg + s] < v) ? 1 : 0;
+      perm[beg + rank] = v;
+    }
+  }
+}
+
+}  // namespace hgk
+
+using namespace hgk;
+
+extern "C" int hgk_version(void) { return 100; }
+extern "C" const char* hgk_last_error(void) { return hgk::error_buffer(); }
+
+extern "C" int64_t hgk_csr_build_workspace_bytes(int64_t E, int64_t N) {
+  if (E < 0 || N < 0) return 0;
+  return align_up(4 * N, 256) + 2 * align_up(4 * E, 256) + 256;
+}
+
+namespace hgk {
+int csr_build_impl(const int32_t* key, int64_t E, int64_t N, int32_t* rowptr,
+                   int32_t* perm, void* workspace, cudaStream_t st) {
+  char* ws = (char*)workspace;
+  int32_t* cnt = (int32_t*)ws;
+  int32_t* slot = (int32_t*)(ws + align_up(4 * N, 256));
+  int32_t* tmp = (int32_t*)(ws + align_up(4 * N, 256) + align_up(4 * E, 256));
+  if (N == 0) {
+    cudaMemsetAsync(rowptr, 0, 4, st);
+    return check_launch("csr_build(memset)");
+  }
+  cudaMemsetAsync(cnt, 0, 4 * N, st);
+  if (E > 0) {
+    const int blocks = (int)imin64(ceil_div(E, 256), (int64_t)kNumSM * 16);
+    k_csr_hist<<<blocks, 256, 0, st>>>(key, E, (int32_t)N, cnt, slot);
+  }
+  k_exclusive_scan<<<1, kScanThreads, 0, st>>>(cnt, N, rowptr);
+  if (E > 0) {
+    const int blocks = (int)imin64(ceil_div(E, 256), (int64_t)kNumSM * 16);
+    k_csr_scatter<<<blocks, 256, 0, st>>>(key, E, (int32_t)N, rowptr, slot, tmp);
+    const int sblocks = (int)imin64(ceil_div(N, 8), (int64_t)kNumSM * 32);
+    k_csr_segsort<<<sblocks, 256, 0, st>>>(rowptr, N, tmp, perm);
+  }
+  return check_launch("csr_build");
+}
+}  // namespace hgk
+
+extern "C" int hgk_csr_build(const int32_t* key, int64_t E, int64_t N,
+                             int32_t* rowptr, int32_t* perm, void* workspace,
+                             int64_t workspace_bytes, void* stream) {
+  HGK_REQUIRE(E >= 0 && N >= 0, "csr_build: negative size (E=%lld N=%lld)",
+              (long long)E, (long long)N);
+  HGK_REQUIRE(E < (1ll << 31) && N < (1ll << 31), "csr_build: sizes must fit int32");
+  HGK_REQUIRE(rowptr != nullptr, "csr_build: rowptr is NULL");
+  HGK_REQUIRE(E == 0 || (key && perm), "csr_build: key/perm is NULL with E>0");
+  HGK_REQUIRE(E == 0 || N > 0, "csr_build: E>0 needs N>0");
+  if (workspace_bytes < hgk_csr_build_workspace_bytes(E, N) || !workspace)
+    return fail(HGK_ERR_WORKSPACE, "csr_build: workspace %lld < %lld bytes",
+                (long long)workspace_bytes,
+                (long long)hgk_csr_build_workspace_bytes(E, N));
+  return csr_build_impl(key, E, N, rowptr, perm, workspace, (cudaStream_t)stream);
+}

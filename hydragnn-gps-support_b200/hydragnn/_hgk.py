@@ -1,0 +1,154 @@
+"""ctypes binding of libhgk.so (the C ABI declared in include/hgk.h).
+
+This is the only module that touches the shared library.  There is no CPU
+fallback: if the library is missing or a tensor is not a CUDA tensor the call
+raises.  Everything is launched on torch's current CUDA stream.
+"""
+import ctypes
+import os
+
+import torch
+
+_PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG_ROOT, "libhgk.so")
+
+_c_i32 = ctypes.c_int32
+_c_i64 = ctypes.c_int64
+_c_ptr = ctypes.c_void_p
+_c_f32 = ctypes.c_float
+_c_f64 = ctypes.c_double
+
+# name -> (restype, argtypes); mirrors include/hgk.h one to one
+_SIGNATURES = {
+    "hgk_version": (_c_i32, []),
+    "hgk_last_error": (ctypes.c_char_p, []),
+    "hgk_csr_build_workspace_bytes": (_c_i64, [_c_i64, _c_i64]),
+    "hgk_csr_build": (_c_i32, [_c_ptr, _c_i64, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr]),
+    "hgk_contract_node": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_i32, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_i64, _c_ptr,
+         _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_i32, _c_ptr],
+    ),
+    "hgk_contract_edge_w": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_i32,
+         _c_ptr, _c_ptr, _c_i64, _c_i32, _c_i32, _c_ptr],
+    ),
+    "hgk_contract_edge_u": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr,
+         _c_ptr, _c_i64, _c_i64, _c_i32, _c_i32, _c_ptr],
+    ),
+    "hgk_edge_gather_add": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_pna_aggregate_fwd": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
+         _c_i64, _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_pna_aggregate_bwd": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
+         _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_radius_graph_workspace_bytes": (_c_i64, [_c_i64, _c_i64]),
+    "hgk_radius_graph_count": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_f64, _c_i32, _c_i32, _c_i32,
+         _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr],
+    ),
+    "hgk_radius_graph_fill": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_f64, _c_i32, _c_i32, _c_i32,
+         _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr],
+    ),
+    "hgk_attn_varlen_fwd": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64,
+         _c_ptr, _c_i64, _c_i64, _c_i32, _c_i32, _c_f32, _c_ptr],
+    ),
+    "hgk_attn_varlen_bwd": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr,
+         _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_i64,
+         _c_i32, _c_i32, _c_f32, _c_ptr],
+    ),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+class HgkError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libhgk.so once; raise loudly if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with "
+                "`python hydragnn-gps-support_b200/csrc/build.py` "
+                "(or __graft_entry__.build()). There is no CPU fallback."
+            )
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the symbol is absent
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(status, what):
+    if status != 0:
+        msg = lib().hgk_last_error()
+        raise HgkError(f"{what} failed with status {status}: {msg.decode() if msg else ''}")
+
+
+def stream_ptr():
+    return _c_ptr(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL); refuses CPU tensors."""
+    if t is None:
+        return _c_ptr(0)
+    if not t.is_cuda:
+        raise HgkError("libhgk needs CUDA tensors; there is no CPU path")
+    return _c_ptr(t.data_ptr())
+
+
+def rows(t, channels=1):
+    """Validate a [rows, F] or [rows, C, F] fp32 operand; return (tensor, ld).
+
+    Rows may be strided (views into a wider matrix), columns must be unit
+    stride and channels F apart."""
+    if t.dtype != torch.float32:
+        raise HgkError(f"expected float32, got {t.dtype}")
+    if t.dim() == 2:
+        if t.size(0) > 1 and t.size(1) > 0 and t.stride(1) != 1 and t.size(1) != 1:
+            t = t.contiguous()
+        elif t.size(1) == 1 and t.stride(1) != 1:
+            t = t.contiguous()
+        ld = t.stride(0) if t.size(0) > 1 else t.size(1)
+        if ld < t.size(1):
+            t = t.contiguous()
+            ld = t.size(1)
+        return t, ld
+    if t.dim() == 3:
+        F = t.size(2)
+        ok = (t.stride(2) == 1 or F == 1) and (t.stride(1) == F or t.size(1) == 1)
+        if not ok:
+            t = t.contiguous()
+        ld = t.stride(0) if t.size(0) > 1 else t.size(1) * F
+        if ld < t.size(1) * F:
+            t = t.contiguous()
+            ld = t.size(1) * F
+        return t, ld
+    raise HgkError(f"expected a 2-D or 3-D tensor, got {t.dim()}-D")

@@ -1,0 +1,14 @@
+from .topo import Topo, build_csr
+from .contract import (
+    contract_node,
+    contract_edge_w,
+    contract_edge_u,
+    segment_sum,
+    segment_mean,
+    gather,
+    gather_mul_segment_sum,
+    edge_gather_add,
+)
+from .radius import radius_graph, MODE_ASE, MODE_CLUSTER
+from .attention import attn_varlen
+from .pna import pna_aggregate

@@ -1,0 +1,68 @@
+"""Variable-length multi-head attention core (hgk_attn_varlen_fwd / _bwd).
+
+Replaces the core of the reference's GPS global attention
+(hydragnn/globalAtt/gps.py:126-133): to_dense_batch -> nn.MultiheadAttention ->
+boolean unpad.  q, k, v are the already projected [N, H*D] node matrices; the
+segments (`cu_seqlens`) say which nodes attend to each other.
+"""
+import math
+
+import torch
+
+from .. import _hgk
+
+
+class AttnVarlen(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, cu_seqlens, H, scale):
+        L = _hgk.lib()
+        N, HD = q.shape
+        D = HD // H
+        q_t, ldq = _hgk.rows(q)
+        k_t, ldk = _hgk.rows(k)
+        v_t, ldv = _hgk.rows(v)
+        o = torch.empty((N, HD), dtype=torch.float32, device=q.device)
+        lse = torch.empty((N, H), dtype=torch.float32, device=q.device)
+        S = cu_seqlens.numel() - 1
+        _hgk.check(
+            L.hgk_attn_varlen_fwd(_hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
+                                  _hgk.ptr(v_t), ldv, _hgk.ptr(cu_seqlens), S, N, H, D, float(scale),
+                                  _hgk.stream_ptr()),
+            "hgk_attn_varlen_fwd",
+        )
+        ctx.save_for_backward(q_t, k_t, v_t, o, lse, cu_seqlens)
+        ctx.H, ctx.scale = H, scale
+        return o
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, do):
+        q, k, v, o, lse, cu = ctx.saved_tensors
+        L = _hgk.lib()
+        N, HD = o.shape
+        H = ctx.H
+        D = HD // H
+        do_t, lddo = _hgk.rows(do)
+        dq = torch.empty((N, HD), dtype=torch.float32, device=o.device)
+        dk = torch.empty_like(dq)
+        dv = torch.empty_like(dq)
+        delta = torch.empty((N, H), dtype=torch.float32, device=o.device)
+        _hgk.check(
+            L.hgk_attn_varlen_bwd(_hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
+                                  _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse),
+                                  _hgk.ptr(q), q.stride(0) if N > 1 else HD,
+                                  _hgk.ptr(k), k.stride(0) if N > 1 else HD,
+                                  _hgk.ptr(v), v.stride(0) if N > 1 else HD,
+                                  _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(ctx.scale),
+                                  _hgk.stream_ptr()),
+            "hgk_attn_varlen_bwd",
+        )
+        return dq, dk, dv, None, None, None
+
+
+def attn_varlen(q, k, v, cu_seqlens, num_heads, scale=None):
+    """softmax(q k^T * scale) v inside each segment; q,k,v [N, H*D] fp32."""
+    D = q.size(1) // num_heads
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    return AttnVarlen.apply(q, k, v, cu_seqlens.to(torch.int32), num_heads, scale)

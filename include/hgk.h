@@ -1,0 +1,216 @@
+/*
+ * hgk.h -- C ABI of libhgk.so, the sm_100a kernel library behind the HydraGNN
+ * message-passing hot path.
+ *
+ * The reference (ArCho48/HydraGNN-gps-support) is 100 % Python and has no FFI
+ * boundary of its own; every entry point below replaces a *library call site*
+ * of the reference, cited as file:line relative to the reference tree.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - the caller owns every buffer: inputs, outputs and workspace.  No entry
+ *     point allocates, frees or synchronises the device;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *     all work is enqueued on it, so torch's stream semantics hold when the
+ *     caller passes torch.cuda.current_stream().cuda_stream;
+ *   - sizes are int64_t, indices int32_t, features float (fp32);
+ *   - return value: 0 on success, a negative hgk_status otherwise; a
+ *     human-readable reason is kept per thread in hgk_last_error();
+ *   - "segment order": every segmented reduction adds its terms sequentially
+ *     in CSR order (k = rowptr[n] .. rowptr[n+1]-1) with separate IEEE
+ *     multiply and add (no FMA contraction), i.e. exactly the order a
+ *     sequential CPU scatter_add_/index_add_ over a stable CSR visits them.
+ *     Results are bit-reproducible run to run; no float atomics anywhere.
+ */
+#ifndef HGK_H_
+#define HGK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  HGK_OK = 0,
+  HGK_ERR_INVALID_ARG = -1, /* null pointer, negative size, bad mode            */
+  HGK_ERR_UNSUPPORTED = -2, /* shape outside what the kernel was written for    */
+  HGK_ERR_WORKSPACE = -3,   /* workspace too small                              */
+  HGK_ERR_CUDA = -4         /* a CUDA runtime call or launch failed             */
+} hgk_status;
+
+/* Library version (major*10000 + minor*100 + patch). */
+int hgk_version(void);
+/* Reason of the last non-zero status returned on this host thread. */
+const char* hgk_last_error(void);
+
+/* ------------------------------------------------------------------------- *
+ * CSR construction
+ * Replaces the implicit "index" argument of torch scatter_add_/index_add_
+ * (reference: hydragnn/models/EGCLStack.py:292-298, PAINNStack.py:254-257,
+ * utils/model/model.py:279-286) and PyG MessagePassing.propagate's
+ * aggregation index (SCFStack.py:285).
+ *
+ * key[E] in [0,N)  ->  rowptr[N+1], perm[E]: perm lists edge ids grouped by
+ * key, ascending edge id inside each group (a stable counting sort).
+ * workspace: hgk_csr_build_workspace_bytes(E, N) bytes.
+ * ------------------------------------------------------------------------- */
+int64_t hgk_csr_build_workspace_bytes(int64_t E, int64_t N);
+int hgk_csr_build(const int32_t* key, int64_t E, int64_t N, int32_t* rowptr,
+                  int32_t* perm, void* workspace, int64_t workspace_bytes,
+                  void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * The contraction family.  All four gather/scatter convolutions of the
+ * reference (SchNet CFConv SCFStack.py:285-293, E_GCL EGCLStack.py:240-271,
+ * PainnMessage PAINNStack.py:237-257, global_mean_pool Base.py:478, energy
+ * sum Base.py:598) and every derivative of them that the force loss needs
+ * (Base.py:614-620, create_graph=True) are partial derivatives of ONE
+ * multilinear form
+ *
+ *     Phi(G,X,W,U) = sum_e sum_c sum_f G[i_e,c,f] * X[j_e,c,f] * W[e,f] * U[e,c]
+ *
+ * so three kernels are closed under differentiation to any order:
+ *   node   : dPhi/dG  (segmented reduce to nodes)   -- also dPhi/dX with i<->j
+ *   edge_w : dPhi/dW  (per-edge product, [E,F])
+ *   edge_u : dPhi/dU  (per-edge dot over f, [E,C])
+ * A NULL operand stands for "all ones".  Channel counts: C in {1,3}; an
+ * operand with 1 channel is broadcast over c.  ld* are row strides in floats
+ * (a row is one node or one edge; channels are contiguous, each F wide).
+ * ------------------------------------------------------------------------- */
+
+/* out[n, c, f] = sum_{k in seg(n)} A[gidx[e], c|0, f] * W[e, f] * U[e, c],
+ *   e = perm ? perm[k] : k,  seg(n) = [rowptr[n], rowptr[n+1]).
+ * CA: channels of A (1 or C); CO: channels of out (C, or 1 = also sum over c).
+ * gidx may be NULL only if A is NULL.  Empty segments write zeros. */
+int hgk_contract_node(float* out, int64_t ldo, int32_t CO, const float* A,
+                      int64_t lda, int32_t CA, const float* W, int64_t ldw,
+                      const float* U, const int32_t* rowptr,
+                      const int32_t* perm, const int32_t* gidx, int64_t N,
+                      int64_t E, int32_t F, int32_t C, void* stream);
+
+/* EW[e, f] = sum_c G[gi[e], c|0, f] * X[xi[e], c|0, f] * U[e, c]
+ * (G or X may be NULL = ones; with U NULL and C channels the sum over c is a
+ * plain sum.)  CG, CX in {1, C}. */
+int hgk_contract_edge_w(float* EW, int64_t ldew, const float* G, int64_t ldg,
+                        int32_t CG, const int32_t* gi, const float* X,
+                        int64_t ldx, int32_t CX, const int32_t* xi,
+                        const float* U, int64_t E, int32_t F, int32_t C,
+                        void* stream);
+
+/* EU[e, c] = sum_f G[gi[e], c|0, f] * X[xi[e], c|0, f] * W[e, f]
+ * The f-sum is a fixed-shape tree (per-lane sequential partials, then a
+ * butterfly), identical for every launch. */
+int hgk_contract_edge_u(float* EU, const float* G, int64_t ldg, int32_t CG,
+                        const int32_t* gi, const float* X, int64_t ldx,
+                        int32_t CX, const int32_t* xi, const float* W,
+                        int64_t ldw, int64_t E, int32_t F, int32_t C,
+                        void* stream);
+
+/* out[e, f] = P[pi[e], f] + Q[qi[e], f]   (Q may be NULL)
+ * The per-edge input of E_GCL.edge_model / PNAConv.message in split-weight
+ * form: Linear(cat[x_i, x_j, ...]) = x_i W_a + x_j W_b + ... computed on the
+ * N node rows, then gathered (reference: EGCLStack.py:240-245, 282). */
+int hgk_edge_gather_add(float* out, int64_t ldo, const float* P, int64_t ldp,
+                        const int32_t* pi, const float* Q, int64_t ldq,
+                        const int32_t* qi, int64_t E, int32_t F, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
+ * DegreeScalerAggregation with aggregators mean,min,max,std).
+ * h[e,:] = P[dst(e),:] + Q[src[e],:] (+ R[e,:]) is formed in registers,
+ * never stored.  Segments are destination rows n (dst(e) = n).
+ *   out[n, 0:F]=mean, [F:2F]=min, [2F:3F]=max, [3F:4F]=std
+ *   std = sqrt(max(E[h^2]-E[h]^2, 1e-5)), zeroed where <= sqrt(1e-5);
+ *   empty segment -> all zeros.  cntmin/cntmax[n,f] = number of edges of the
+ *   segment that attain the min / max (torch.scatter_reduce splits the
+ *   gradient of amin/amax evenly among ties); needed by the backward.
+ * ------------------------------------------------------------------------- */
+int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntmax,
+                          const float* P, const float* Q, const float* R,
+                          const int32_t* rowptr, const int32_t* perm,
+                          const int32_t* src, int64_t N, int64_t E, int32_t F,
+                          void* stream);
+/* gh[e, f] = d loss / d h[e, f] given gout[N, 4F] and the forward's out /
+ * cntmin / cntmax; dst[e] is the segment id of edge e. */
+int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* out,
+                          const int32_t* cntmin, const int32_t* cntmax,
+                          const float* P, const float* Q, const float* R,
+                          const int32_t* rowptr, const int32_t* src,
+                          const int32_t* dst, int64_t N, int64_t E, int32_t F,
+                          void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Radius graph on cell-list bins, batched over graphs.
+ * Replaces ase.neighborlist.neighbor_list + _remove_true_self_loops +
+ * _limit_neighbors (hydragnn/preprocess/graph_samples_checks_and_updates.py:
+ * 146-282) and PyG RadiusGraph / RadiusInteractionGraph -> torch_cluster
+ * radius_graph (same file :109-114, models/SCFStack.py:59-61).
+ *
+ *   pos[N,3] fp32; gptr[B+1] node offsets of the B graphs;
+ *   cell[B,3,3] fp32 row vectors and pbc[B,3] (uint8) or both NULL (no PBC).
+ *   mode HGK_RG_ASE   : d = sqrt(|pos[j]-pos[i]+S.cell|^2) in fp64, keep d <  r
+ *                       (ASE semantics; i==j kept when S != 0, and when
+ *                        S == 0 only if `loop`)
+ *   mode HGK_RG_CLUSTER: d2 in fp32 (mul, add, add; no FMA), keep d2 < r*r
+ *                       (torch_cluster semantics; i==j kept only if `loop`)
+ * An edge is (src=i, dst=j, S).  Edges come out grouped by dst ascending and,
+ * inside a dst, ordered by (d, src, Sx, Sy, Sz); at most max_nbr nearest are
+ * kept per dst (max_nbr <= 0: unlimited).
+ *
+ * Three calls (the host needs the edge count to size the outputs):
+ *   1. hgk_radius_graph_count  -> deg_raw[N] (all matches), deg[N] (capped)
+ *   2. caller prefix-sums both into rowptr_raw[N+1], rowptr[N+1]
+ *   3. hgk_radius_graph_fill   -> src[E], dst[E], shift_int[E,3], dist[E]
+ *                                 (dist fp64 in ASE mode = d, in CLUSTER mode
+ *                                  = d2 promoted), E = rowptr[N]
+ * workspace (same buffer for 1 and 3, contents must survive in between):
+ *   hgk_radius_graph_workspace_bytes(N, B) + for fill 24*E_raw bytes more,
+ *   passed separately as `cand` (E_raw = rowptr_raw[N]).
+ * ------------------------------------------------------------------------- */
+enum { HGK_RG_ASE = 0, HGK_RG_CLUSTER = 1 };
+int64_t hgk_radius_graph_workspace_bytes(int64_t N, int64_t B);
+int hgk_radius_graph_count(const float* pos, const int32_t* gptr,
+                           const float* cell, const uint8_t* pbc, int64_t N,
+                           int64_t B, double r, int32_t max_nbr, int32_t loop,
+                           int32_t mode, int32_t* deg_raw, int32_t* deg,
+                           void* workspace, int64_t workspace_bytes,
+                           void* stream);
+int hgk_radius_graph_fill(const float* pos, const int32_t* gptr,
+                          const float* cell, const uint8_t* pbc, int64_t N,
+                          int64_t B, double r, int32_t max_nbr, int32_t loop,
+                          int32_t mode, const int32_t* rowptr_raw,
+                          const int32_t* rowptr, int32_t* src, int32_t* dst,
+                          int32_t* shift_int, double* dist, void* cand,
+                          int64_t cand_bytes, void* workspace,
+                          int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * GPS global attention, variable-length segments (reference:
+ * hydragnn/globalAtt/gps.py:126-133 = to_dense_batch + nn.MultiheadAttention
+ * core + unpad).  q,k,v,o: [N, H, D] fp32 (row stride ld* floats, head h at
+ * column h*D); cu_seqlens[S+1] node offsets of the S segments; attention is
+ * restricted to nodes of the same segment (S=1, cu=[0,N] reproduces the
+ * reference's whole-batch attention).  scale multiplies q.k.
+ * lse[N,H] = log-sum-exp of the scaled scores (natural log), kept for bwd.
+ * Online-softmax streaming: no [L,L] score matrix is ever stored.
+ * ------------------------------------------------------------------------- */
+int hgk_attn_varlen_fwd(float* o, int64_t ldo, float* lse, const float* q,
+                        int64_t ldq, const float* k, int64_t ldk,
+                        const float* v, int64_t ldv,
+                        const int32_t* cu_seqlens, int64_t S, int64_t N,
+                        int32_t H, int32_t D, float scale, void* stream);
+/* dq,dk,dv: [N,H,D] contiguous; delta[N,H] is workspace written by the call
+ * (rowsum(do*o)). */
+int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta,
+                        const float* dout, int64_t lddo, const float* o,
+                        int64_t ldo, const float* lse, const float* q,
+                        int64_t ldq, const float* k, int64_t ldk,
+                        const float* v, int64_t ldv,
+                        const int32_t* cu_seqlens, int64_t S, int64_t N,
+                        int32_t H, int32_t D, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HGK_H_ */
