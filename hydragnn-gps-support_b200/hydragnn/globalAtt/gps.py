@@ -1,0 +1,99 @@
+"""GraphGPS layer on the B200 path.
+
+Same constructor and forward contract as the reference's GPSConv
+(hydragnn/globalAtt/gps.py:32-152).  The global-attention branch no longer pads
+(`to_dense_batch`) or calls nn.MultiheadAttention's fused path: the QKV projection
+is one GEMM on the N node rows, the softmax(QK^T)V core runs in the varlen
+kernel (ops/attention.py) over `cu_seqlens`, and the output projection is one
+GEMM.  `self.attn` is still an nn.MultiheadAttention so parameter names and
+initialisation are the reference's.
+
+Segments: the reference never passes `graph_batch`, so all nodes of the
+mini-batch attend to each other -- that is the default here
+(cu_seqlens = [0, N]).  Passing `graph_batch` (sorted graph ids) or `cu_seqlens`
+selects per-graph attention.
+"""
+from typing import Any, Dict, Optional
+
+import torch
+import torch.nn.functional as F
+from torch import Tensor
+from torch.nn import Dropout, Linear, Sequential
+
+from ..nn import activation_resolver, normalization_resolver
+from ..ops import attn_varlen
+
+
+class GPSConv(torch.nn.Module):
+    def __init__(
+        self,
+        channels: int,
+        conv: Optional[torch.nn.Module],
+        heads: int = 1,
+        dropout: float = 0.0,
+        act: str = "relu",
+        act_kwargs: Optional[Dict[str, Any]] = None,
+        norm: Optional[str] = "batch_norm",
+        norm_kwargs: Optional[Dict[str, Any]] = None,
+        attn_type: str = "multihead",
+        attn_kwargs: Optional[Dict[str, Any]] = None,
+    ):
+        super().__init__()
+        self.channels, self.conv, self.heads = channels, conv, heads
+        self.dropout, self.attn_type = dropout, attn_type
+        if attn_type != "multihead":
+            # the reference's only other option is PyG's PerformerAttention (gps.py:62-67)
+            raise ValueError(f"{attn_type} is not supported")
+        self.attn = torch.nn.MultiheadAttention(channels, heads, batch_first=True, **(attn_kwargs or {}))
+        self.mlp = Sequential(
+            Linear(channels, channels * 2),
+            activation_resolver(act, **(act_kwargs or {})),
+            Dropout(dropout),
+            Linear(channels * 2, channels),
+            Dropout(dropout),
+        )
+        norm_kwargs = norm_kwargs or {}
+        self.norm1 = normalization_resolver(norm, channels, **norm_kwargs)
+        self.norm2 = normalization_resolver(norm, channels, **norm_kwargs)
+        self.norm3 = normalization_resolver(norm, channels, **norm_kwargs)
+
+    def _global_attention(self, x: Tensor, graph_batch, cu_seqlens) -> Tensor:
+        n = x.size(0)
+        if cu_seqlens is None:
+            if graph_batch is None:
+                cu_seqlens = torch.tensor([0, n], dtype=torch.int32, device=x.device)
+            else:
+                counts = torch.bincount(graph_batch)
+                cu_seqlens = torch.zeros(counts.numel() + 1, dtype=torch.int32, device=x.device)
+                cu_seqlens[1:] = torch.cumsum(counts, 0)
+        qkv = F.linear(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
+        c = self.channels
+        o = attn_varlen(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu_seqlens, self.heads)
+        return F.linear(o, self.attn.out_proj.weight, self.attn.out_proj.bias)
+
+    def forward(self, inv_node_feat: Tensor, equiv_node_feat: Tensor,
+                graph_batch: Optional[Tensor] = None, cu_seqlens: Optional[Tensor] = None, **kwargs):
+        hs = []
+        if self.conv is not None:  # local MPNN branch (gps.py:112-123)
+            h, equiv_node_feat = self.conv(inv_node_feat=inv_node_feat,
+                                           equiv_node_feat=equiv_node_feat, **kwargs)
+            h = F.dropout(h, p=self.dropout, training=self.training)
+            h = h + inv_node_feat
+            if self.norm1 is not None:
+                h = self.norm1(h)
+            hs.append(h)
+        h = self._global_attention(inv_node_feat, graph_batch, cu_seqlens)  # gps.py:126-133
+        h = F.dropout(h, p=self.dropout, training=self.training)
+        h = h + inv_node_feat
+        if self.norm2 is not None:
+            h = self.norm2(h)
+        hs.append(h)
+        out = sum(hs)
+        out = out + self.mlp(out)
+        if self.norm3 is not None:
+            out = self.norm3(out)
+        return out, equiv_node_feat
+
+    def __repr__(self) -> str:
+        return (f"{self.__class__.__name__}({self.channels}, conv={self.conv}, "
+                f"heads={self.heads}, attn_type={self.attn_type})")

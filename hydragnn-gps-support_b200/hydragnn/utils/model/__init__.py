@@ -1,0 +1,8 @@
+from .model import (
+    activation_function_selection,
+    loss_function_selection,
+    unsorted_segment_mean,
+    unsorted_segment_sum,
+    update_multibranch_heads,
+)
+from .operations import get_edge_vectors_and_lengths
