@@ -12,24 +12,52 @@ import torch
 from .. import _hgk
 
 
+def _attn_fwd_raw(q, k, v, cu_seqlens, H, scale):
+    L = _hgk.lib()
+    N, HD = q.shape
+    D = HD // H
+    q_t, ldq = _hgk.rows(q)
+    k_t, ldk = _hgk.rows(k)
+    v_t, ldv = _hgk.rows(v)
+    o = torch.empty((N, HD), dtype=torch.float32, device=q.device)
+    lse = torch.empty((N, H), dtype=torch.float32, device=q.device)
+    S = cu_seqlens.numel() - 1
+    _hgk.check(
+        L.hgk_attn_varlen_fwd(_hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
+                              _hgk.ptr(v_t), ldv, _hgk.ptr(cu_seqlens), S, N, H, D, float(scale),
+                              _hgk.stream_ptr()),
+        "hgk_attn_varlen_fwd",
+    )
+    return o, lse, q_t, k_t, v_t
+
+
+def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
+    L = _hgk.lib()
+    N, HD = o.shape
+    D = HD // H
+    do_t, lddo = _hgk.rows(do)
+    dq = torch.empty((N, HD), dtype=torch.float32, device=o.device)
+    dk = torch.empty_like(dq)
+    dv = torch.empty_like(dq)
+    delta = torch.empty((N, H), dtype=torch.float32, device=o.device)
+    _, ldq = _hgk.rows(q)
+    _, ldk = _hgk.rows(k)
+    _, ldv = _hgk.rows(v)
+    _hgk.check(
+        L.hgk_attn_varlen_bwd(_hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
+                              _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse),
+                              _hgk.ptr(q), ldq, _hgk.ptr(k), ldk, _hgk.ptr(v), ldv,
+                              _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(scale),
+                              _hgk.stream_ptr()),
+        "hgk_attn_varlen_bwd",
+    )
+    return dq, dk, dv
+
+
 class AttnVarlen(torch.autograd.Function):
     @staticmethod
     def forward(ctx, q, k, v, cu_seqlens, H, scale):
-        L = _hgk.lib()
-        N, HD = q.shape
-        D = HD // H
-        q_t, ldq = _hgk.rows(q)
-        k_t, ldk = _hgk.rows(k)
-        v_t, ldv = _hgk.rows(v)
-        o = torch.empty((N, HD), dtype=torch.float32, device=q.device)
-        lse = torch.empty((N, H), dtype=torch.float32, device=q.device)
-        S = cu_seqlens.numel() - 1
-        _hgk.check(
-            L.hgk_attn_varlen_fwd(_hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
-                                  _hgk.ptr(v_t), ldv, _hgk.ptr(cu_seqlens), S, N, H, D, float(scale),
-                                  _hgk.stream_ptr()),
-            "hgk_attn_varlen_fwd",
-        )
+        o, lse, q_t, k_t, v_t = _attn_fwd_raw(q, k, v, cu_seqlens, H, scale)
         ctx.save_for_backward(q_t, k_t, v_t, o, lse, cu_seqlens)
         ctx.H, ctx.scale = H, scale
         return o
@@ -38,25 +66,7 @@ class AttnVarlen(torch.autograd.Function):
     @torch.autograd.function.once_differentiable
     def backward(ctx, do):
         q, k, v, o, lse, cu = ctx.saved_tensors
-        L = _hgk.lib()
-        N, HD = o.shape
-        H = ctx.H
-        D = HD // H
-        do_t, lddo = _hgk.rows(do)
-        dq = torch.empty((N, HD), dtype=torch.float32, device=o.device)
-        dk = torch.empty_like(dq)
-        dv = torch.empty_like(dq)
-        delta = torch.empty((N, H), dtype=torch.float32, device=o.device)
-        _hgk.check(
-            L.hgk_attn_varlen_bwd(_hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
-                                  _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse),
-                                  _hgk.ptr(q), q.stride(0) if N > 1 else HD,
-                                  _hgk.ptr(k), k.stride(0) if N > 1 else HD,
-                                  _hgk.ptr(v), v.stride(0) if N > 1 else HD,
-                                  _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(ctx.scale),
-                                  _hgk.stream_ptr()),
-            "hgk_attn_varlen_bwd",
-        )
+        dq, dk, dv = _attn_bwd_raw(do, o, lse, q, k, v, cu, ctx.H, ctx.scale)
         return dq, dk, dv, None, None, None
 
 

@@ -218,24 +218,28 @@ def gather_mul_segment_sum(x, W, topo, side_out=1, side_in=0):
     return contract_node(topo, side_out, A=x, side_a=side_in, W=W, F=W.size(-1))
 
 
+def _edge_gather_add_raw(topo, P, side_p, Q, side_q):
+    L = _hgk.lib()
+    F = P.size(-1)
+    out = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
+    p_t, ldp = _hgk.rows(P)
+    q_t, ldq = _hgk.rows(Q)
+    _hgk.check(
+        L.hgk_edge_gather_add(_hgk.ptr(out), F, _hgk.ptr(p_t), ldp, _hgk.ptr(topo.idx[side_p]),
+                              _hgk.ptr(q_t), ldq, _hgk.ptr(topo.idx[side_q]), topo.E, F,
+                              _hgk.stream_ptr()),
+        "hgk_edge_gather_add",
+    )
+    return out
+
+
 class EdgeGatherAdd(torch.autograd.Function):
     """out[e,:] = P[idx[side_p][e],:] + Q[idx[side_q][e],:]  (split-weight edge-MLP input)."""
 
     @staticmethod
     def forward(ctx, P, Q, topo, side_p, side_q):
         ctx.topo, ctx.side_p, ctx.side_q = topo, side_p, side_q
-        L = _hgk.lib()
-        F = P.size(-1)
-        out = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
-        p_t, ldp = _hgk.rows(P)
-        q_t, ldq = _hgk.rows(Q)
-        _hgk.check(
-            L.hgk_edge_gather_add(_hgk.ptr(out), F, _hgk.ptr(p_t), ldp, _hgk.ptr(topo.idx[side_p]),
-                                  _hgk.ptr(q_t), ldq, _hgk.ptr(topo.idx[side_q]), topo.E, F,
-                                  _hgk.stream_ptr()),
-            "hgk_edge_gather_add",
-        )
-        return out
+        return _edge_gather_add_raw(topo, P, side_p, Q, side_q)
 
     @staticmethod
     def backward(ctx, g):

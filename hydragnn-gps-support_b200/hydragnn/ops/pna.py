@@ -11,24 +11,44 @@ from .. import _hgk
 from .contract import segment_sum
 
 
+def _pna_fwd_raw(P, Q, R, topo):
+    L = _hgk.lib()
+    N, F = P.shape
+    rowptr, perm = topo.csr(1)  # segments = destination (edge_index[1])
+    out = torch.empty((N, 4 * F), dtype=torch.float32, device=P.device)
+    cmin = torch.empty((N, F), dtype=torch.int32, device=P.device)
+    cmax = torch.empty((N, F), dtype=torch.int32, device=P.device)
+    _hgk.check(
+        L.hgk_pna_aggregate_fwd(_hgk.ptr(out), _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P),
+                                _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(perm),
+                                _hgk.ptr(topo.idx[0]), N, topo.E, F, _hgk.stream_ptr()),
+        "hgk_pna_aggregate_fwd",
+    )
+    return out, cmin, cmax
+
+
+def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo):
+    L = _hgk.lib()
+    N, F = P.shape
+    rowptr, _ = topo.csr(1)
+    gh = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
+    _hgk.check(
+        L.hgk_pna_aggregate_bwd(_hgk.ptr(gh), _hgk.ptr(gout.contiguous()), _hgk.ptr(out),
+                                _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P), _hgk.ptr(Q),
+                                _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(topo.idx[0]),
+                                _hgk.ptr(topo.idx[1]), N, topo.E, F, _hgk.stream_ptr()),
+        "hgk_pna_aggregate_bwd",
+    )
+    return gh
+
+
 class PNAAggregate(torch.autograd.Function):
     @staticmethod
     def forward(ctx, P, Q, R, topo):
-        L = _hgk.lib()
-        N, F = P.shape
         P = P.contiguous()
         Q = Q.contiguous()
         R = None if R is None else R.contiguous()
-        rowptr, perm = topo.csr(1)  # segments = destination (edge_index[1])
-        out = torch.empty((N, 4 * F), dtype=torch.float32, device=P.device)
-        cmin = torch.empty((N, F), dtype=torch.int32, device=P.device)
-        cmax = torch.empty((N, F), dtype=torch.int32, device=P.device)
-        _hgk.check(
-            L.hgk_pna_aggregate_fwd(_hgk.ptr(out), _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P),
-                                    _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(perm),
-                                    _hgk.ptr(topo.idx[0]), N, topo.E, F, _hgk.stream_ptr()),
-            "hgk_pna_aggregate_fwd",
-        )
+        out, cmin, cmax = _pna_fwd_raw(P, Q, R, topo)
         ctx.save_for_backward(P, Q, R, out, cmin, cmax)
         ctx.topo = topo
         return out
@@ -38,17 +58,7 @@ class PNAAggregate(torch.autograd.Function):
     def backward(ctx, gout):
         P, Q, R, out, cmin, cmax = ctx.saved_tensors
         topo = ctx.topo
-        L = _hgk.lib()
-        N, F = P.shape
-        rowptr, _ = topo.csr(1)
-        gh = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
-        _hgk.check(
-            L.hgk_pna_aggregate_bwd(_hgk.ptr(gh), _hgk.ptr(gout.contiguous()), _hgk.ptr(out),
-                                    _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P), _hgk.ptr(Q),
-                                    _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(topo.idx[0]),
-                                    _hgk.ptr(topo.idx[1]), N, topo.E, F, _hgk.stream_ptr()),
-            "hgk_pna_aggregate_bwd",
-        )
+        gh = _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo)
         gP = segment_sum(gh, topo, 1) if ctx.needs_input_grad[0] else None
         gQ = segment_sum(gh, topo, 0) if ctx.needs_input_grad[1] else None
         gR = gh if (R is not None and ctx.needs_input_grad[2]) else None

@@ -1,0 +1,209 @@
+"""ORACLE (test infrastructure only -- never imported by the product path).
+
+CPU restatement of every entry point of include/hgk.h in terms of the torch CPU ops the
+reference issues at the call site that entry point replaces (index_select, sequential
+index_add_/scatter_add_, dense softmax attention, scatter_reduce).  Two uses, both in
+tests/:
+  * `-m gpu` tests call the C ABI and compare with these functions on the same inputs
+    (bit-exact where hgk.h promises "segment order", a stated tolerance elsewhere);
+  * `-m "not gpu"` tests patch these functions under the product's autograd wrappers
+    (tests/cpu_patch.py) so the host-side logic of the stacks -- split weights, CSR sides,
+    double backward -- is checked against the golden reference outputs without a GPU.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import pyg_lite as pyg
+from . import hydragnn_ref as ref
+
+
+# hgk_csr_build: stable grouping of edge ids by key (a sequential scatter visits e = 0..E-1)
+def csr_build(key, num_rows):
+    key = key.long()
+    counts = torch.bincount(key, minlength=num_rows)
+    rowptr = torch.zeros(num_rows + 1, dtype=torch.int32)
+    rowptr[1:] = torch.cumsum(counts, 0)
+    perm = torch.sort(key, stable=True).indices.to(torch.int32)
+    return rowptr, perm
+
+
+def _bc(t, C):
+    """[rows, F] or [rows, CA, F] -> [rows, C, F] view."""
+    if t.dim() == 2:
+        t = t.unsqueeze(1)
+    return t.expand(t.size(0), C, t.size(2))
+
+
+# hgk_contract_node -- index_select + mul (+ mul) + index_add_  (SCFStack.py:285-293,
+# EGCLStack.py:292-298, PAINNStack.py:238-257, Base.py:478,598)
+def contract_node(key, num_rows, A, gidx, W, U, C, CO, F):
+    E = key.numel()
+    term = None
+    if A is not None:
+        term = _bc(A.index_select(0, gidx.long()), C)
+    if W is not None:
+        w = W.reshape(E, 1, F).expand(E, C, F)
+        term = w if term is None else term * w
+    if U is not None:
+        u = U.reshape(E, C, 1)
+        term = u.expand(E, C, F) if term is None else term * u
+    term = term.contiguous()
+    if CO == C:
+        out = torch.zeros((num_rows, C, F), dtype=torch.float32)
+        out.index_add_(0, key.long(), term)
+        return out.reshape(num_rows, F) if C == 1 else out
+    out = torch.zeros((num_rows, F), dtype=torch.float32)          # CO == 1 < C: also sum over c
+    out.index_add_(0, key.long().repeat_interleave(C), term.reshape(E * C, F))
+    return out
+
+
+# hgk_contract_edge_w -- per-edge product of two gathered rows (backward of the above w.r.t. W)
+def contract_edge_w(G, gi, X, xi, U, E, C, F):
+    term = None
+    if G is not None:
+        term = _bc(G.index_select(0, gi.long()), C)
+    if X is not None:
+        x = _bc(X.index_select(0, xi.long()), C)
+        term = x if term is None else term * x
+    if U is not None:
+        term = term * U.reshape(E, C, 1)
+    acc = term[:, 0]
+    for c in range(1, C):
+        acc = acc + term[:, c]
+    return acc.contiguous()
+
+
+# hgk_contract_edge_u -- per-edge dot product over features (fixed tree on the GPU; plain sum here)
+def contract_edge_u(G, gi, X, xi, W, E, C, F):
+    term = None
+    if G is not None:
+        term = _bc(G.index_select(0, gi.long()), C)
+    if X is not None:
+        x = _bc(X.index_select(0, xi.long()), C)
+        term = x if term is None else term * x
+    if W is not None:
+        term = term * W.reshape(E, 1, F)
+    return term.sum(dim=-1).contiguous()
+
+
+# hgk_edge_gather_add -- x[row] W_a + x[col] W_b of E_GCL.edge_model in split-weight form
+def edge_gather_add(P, pi, Q, qi):
+    out = P.index_select(0, pi.long())
+    if Q is not None:
+        out = out + Q.index_select(0, qi.long())
+    return out
+
+
+# hgk_pna_aggregate_fwd -- PyG PNAConv.propagate + aggregators mean,min,max,std (PNAStack.py:30-53)
+def pna_aggregate_fwd(P, Q, R, src, dst, N):
+    F = P.size(1)
+    h = P.index_select(0, dst.long()) + Q.index_select(0, src.long())
+    if R is not None:
+        h = h + R
+    idx = dst.long()
+    mean = pyg.scatter(h, idx, 0, N, "mean")
+    mn = pyg.scatter(h, idx, 0, N, "min")
+    mx = pyg.scatter(h, idx, 0, N, "max")
+    mean2 = pyg.scatter(h * h, idx, 0, N, "mean")
+    sd = (mean2 - mean * mean).clamp(min=1e-5).sqrt()
+    sd = sd.masked_fill(sd <= math.sqrt(1e-5), 0.0)
+    deg = torch.bincount(idx, minlength=N)
+    sd = sd * (deg > 0).unsqueeze(1)
+    cmin = torch.zeros((N, F), dtype=torch.int32).index_add_(0, idx, (h == mn[idx]).to(torch.int32))
+    cmax = torch.zeros((N, F), dtype=torch.int32).index_add_(0, idx, (h == mx[idx]).to(torch.int32))
+    return torch.cat([mean, mn, mx, sd], dim=1), cmin, cmax
+
+
+# hgk_pna_aggregate_bwd -- d/dh of the four aggregators (ties split evenly like scatter_reduce)
+def pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, src, dst, N):
+    F = P.size(1)
+    idx = dst.long()
+    h = P.index_select(0, idx) + Q.index_select(0, src.long())
+    if R is not None:
+        h = h + R
+    cnt = torch.bincount(idx, minlength=N).to(torch.float32).unsqueeze(1)[idx]
+    o, g = out[idx], gout[idx]
+    gh = g[:, :F] / cnt
+    gh = gh + torch.where(h == o[:, F:2 * F], g[:, F:2 * F] / cmin[idx].float(), torch.zeros_like(h))
+    gh = gh + torch.where(h == o[:, 2 * F:3 * F], g[:, 2 * F:3 * F] / cmax[idx].float(), torch.zeros_like(h))
+    sd = o[:, 3 * F:]
+    safe = torch.where(sd > 0, sd, torch.ones_like(sd))
+    gh = gh + torch.where(sd > 0, g[:, 3 * F:] * (h - o[:, :F]) / (cnt * safe), torch.zeros_like(h))
+    return gh
+
+
+# hgk_attn_varlen_fwd/_bwd -- to_dense_batch + MultiheadAttention core + unpad (gps.py:126-133)
+def attn_varlen_fwd(q, k, v, cu_seqlens, H, scale):
+    N, HD = q.shape
+    D = HD // H
+    o = torch.zeros((N, HD), dtype=torch.float32)
+    lse = torch.zeros((N, H), dtype=torch.float32)
+    cu = [int(c) for c in cu_seqlens]
+    for b, e in zip(cu[:-1], cu[1:]):
+        for h in range(H):
+            sl = slice(h * D, (h + 1) * D)
+            s = (q[b:e, sl] @ k[b:e, sl].t()) * scale
+            lse[b:e, h] = torch.logsumexp(s, dim=1)
+            o[b:e, sl] = torch.softmax(s, dim=1) @ v[b:e, sl]
+    return o, lse
+
+
+def attn_varlen_bwd(do, q, k, v, cu_seqlens, H, scale):
+    q, k, v = (t.detach().clone().requires_grad_(True) for t in (q, k, v))
+    with torch.enable_grad():
+        o, _ = attn_varlen_fwd_autograd(q, k, v, cu_seqlens, H, scale)
+        dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
+    return dq, dk, dv
+
+
+def attn_varlen_fwd_autograd(q, k, v, cu_seqlens, H, scale):
+    N, HD = q.shape
+    D = HD // H
+    cu = [int(c) for c in cu_seqlens]
+    rows = []
+    for b, e in zip(cu[:-1], cu[1:]):
+        heads = []
+        for h in range(H):
+            sl = slice(h * D, (h + 1) * D)
+            s = (q[b:e, sl] @ k[b:e, sl].t()) * scale
+            heads.append(torch.softmax(s, dim=1) @ v[b:e, sl])
+        rows.append(torch.cat(heads, dim=1))
+    return (torch.cat(rows, dim=0) if rows else q.new_zeros((0, HD))), None
+
+
+# hgk_radius_graph_{count,fill}: the two neighbour searches of the reference, per graph
+def radius_graph(pos, ptr, r, max_nbr, loop, cell=None, pbc=None, mode=1):
+    """-> src, dst (int32, global node ids), shift_int [E,3], dist fp64 [E], rowptr int32 [N+1].
+    mode 0 = ASE semantics (RadiusGraphPBC, graph_samples_checks_and_updates.py:146-282),
+    mode 1 = torch_cluster semantics (RadiusGraph / RadiusInteractionGraph)."""
+    pos = pos.detach().to(torch.float32).cpu()
+    ptr = [int(p) for p in ptr]
+    srcs, dsts, shifts, dists = [], [], [], []
+    for g, (b, e) in enumerate(zip(ptr[:-1], ptr[1:])):
+        p = pos[b:e]
+        if mode == 1:
+            ei = pyg.radius_graph_cluster(p, r, None, bool(loop), max_nbr if max_nbr and max_nbr > 0 else 0)
+            x = p.numpy().astype(np.float32)
+            d = x[ei[0].numpy()] - x[ei[1].numpy()]
+            sq = (d * d).astype(np.float32)
+            d2 = ((sq[:, 0] + sq[:, 1]).astype(np.float32) + sq[:, 2]).astype(np.float32)
+            S = np.zeros((ei.size(1), 3), dtype=np.int64)
+            dd = d2.astype(np.float64)
+            ei = ei.numpy()
+        else:
+            if cell is None:
+                c, pb = np.eye(3), np.zeros(3, dtype=bool)
+            else:
+                c, pb = cell[g].numpy(), np.asarray(pbc[g]).astype(bool)
+            ei, S, dd = ref.radius_graph_pbc(p.numpy(), c, pb, r, max_nbr, bool(loop))
+        srcs.append(ei[0] + b); dsts.append(ei[1] + b); shifts.append(S); dists.append(dd)
+    src = np.concatenate(srcs) if srcs else np.zeros(0, np.int64)
+    dst = np.concatenate(dsts) if dsts else np.zeros(0, np.int64)
+    N = pos.size(0)
+    rowptr = np.zeros(N + 1, dtype=np.int32)
+    np.cumsum(np.bincount(dst, minlength=N), out=rowptr[1:])
+    return (torch.from_numpy(src.astype(np.int32)), torch.from_numpy(dst.astype(np.int32)),
+            torch.from_numpy(np.concatenate(shifts).astype(np.int32).reshape(-1, 3)),
+            torch.from_numpy(np.concatenate(dists).astype(np.float64)), torch.from_numpy(rowptr))

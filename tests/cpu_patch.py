@@ -1,0 +1,94 @@
+"""Test-only: run the product's host logic on CPU by swapping the C-ABI launchers
+(hydragnn.ops.*._xxx_raw) for their CPU restatement in oracle/kernel_spec.py.
+
+The product itself has no CPU path (hydragnn._hgk refuses CPU tensors).  This patch exists so
+that `-m "not gpu"` tests can check everything ABOVE the kernels -- weight splitting, which
+CSR side each conv aggregates on, the autograd closure used by the force loss -- against the
+golden reference outputs in a container without a GPU.
+"""
+import contextlib
+
+import torch
+
+from oracle import kernel_spec as ks
+
+
+def _node_raw(topo, side_out, A, side_a, W, U, C, CO, F):
+    gidx = topo.idx[side_a] if A is not None else None
+    return ks.contract_node(topo.idx[side_out], topo.num_rows[side_out], A, gidx, W, U, C, CO, F)
+
+
+def _edge_w_raw(topo, G, side_g, X, side_x, U, C, F):
+    return ks.contract_edge_w(G, topo.idx[side_g] if G is not None else None,
+                              X, topo.idx[side_x] if X is not None else None, U, topo.E, C, F)
+
+
+def _edge_u_raw(topo, G, side_g, X, side_x, W, C, F):
+    return ks.contract_edge_u(G, topo.idx[side_g] if G is not None else None,
+                              X, topo.idx[side_x] if X is not None else None, W, topo.E, C, F)
+
+
+def _edge_gather_add_raw(topo, P, side_p, Q, side_q):
+    return ks.edge_gather_add(P, topo.idx[side_p], Q, topo.idx[side_q])
+
+
+def _pna_fwd_raw(P, Q, R, topo):
+    return ks.pna_aggregate_fwd(P, Q, R, topo.idx[0], topo.idx[1], P.size(0))
+
+
+def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo):
+    return ks.pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, topo.idx[0], topo.idx[1], P.size(0))
+
+
+def _attn_fwd_raw(q, k, v, cu, H, scale):
+    o, lse = ks.attn_varlen_fwd(q, k, v, cu, H, scale)
+    return o, lse, q, k, v
+
+
+def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
+    return ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
+
+
+def _build_csr(key, num_rows):
+    return ks.csr_build(key, num_rows)
+
+
+def _radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=None, mode=None,
+                  return_rowptr=False):
+    if mode is None:
+        mode = 0 if cell is not None else 1
+    src, dst, S, dist, rowptr = ks.radius_graph(pos, ptr, r, int(max_num_neighbors or 0), loop,
+                                                cell, pbc, mode)
+    out = {"edge_index": torch.stack([src, dst]).to(torch.int64), "src": src, "dst": dst,
+           "shift_int": S, "dist": dist, "rowptr": rowptr}
+    if cell is not None:
+        g = torch.bucketize(dst.long(), torch.as_tensor(ptr)[1:].long(), right=True)
+        out["edge_shifts"] = torch.einsum("ek,ekd->ed", S.float(), cell.float().reshape(-1, 3, 3)[g])
+    return out
+
+
+@contextlib.contextmanager
+def cpu_kernels():
+    from hydragnn.ops import attention, contract, pna, topo
+    import importlib
+
+    import hydragnn.ops as ops_pkg
+
+    scf_mod = importlib.import_module("hydragnn.models.SCFStack")
+
+    patches = [
+        (contract, "_node_raw", _node_raw), (contract, "_edge_w_raw", _edge_w_raw),
+        (contract, "_edge_u_raw", _edge_u_raw), (contract, "_edge_gather_add_raw", _edge_gather_add_raw),
+        (pna, "_pna_fwd_raw", _pna_fwd_raw), (pna, "_pna_bwd_raw", _pna_bwd_raw),
+        (attention, "_attn_fwd_raw", _attn_fwd_raw), (attention, "_attn_bwd_raw", _attn_bwd_raw),
+        (topo, "build_csr", _build_csr), (ops_pkg, "radius_graph", _radius_graph),
+        (scf_mod, "radius_graph", _radius_graph),
+    ]
+    saved = [(m, n, getattr(m, n)) for m, n, _ in patches]
+    try:
+        for m, n, f in patches:
+            setattr(m, n, f)
+        yield
+    finally:
+        for m, n, f in saved:
+            setattr(m, n, f)

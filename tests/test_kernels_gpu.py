@@ -1,0 +1,324 @@
+"""`-m gpu`: every entry point of include/hgk.h, called through the C ABI (ctypes), against its
+CPU restatement in oracle/kernel_spec.py on the same seeded inputs.
+
+Bars: bit-exact for index work (CSR, edge lists) and for the "segment order" reductions hgk.h
+promises (contract_node, contract_edge_w, edge_gather_add); stated fp32 tolerances for the tree
+reductions (contract_edge_u), PNA statistics and attention."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import kernel_spec as ks
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def ops(libhgk):
+    from hydragnn import ops as _ops
+    from hydragnn.ops import attention, contract, pna, topo
+
+    return dict(ops=_ops, contract=contract, pna=pna, attention=attention, topo=topo)
+
+
+def random_graph(gen, N, E, sorted_dst=False):
+    src = torch.randint(0, N, (E,), generator=gen)
+    dst = torch.randint(0, N, (E,), generator=gen)
+    if sorted_dst:
+        dst = torch.sort(dst).values
+    return torch.stack([src, dst])
+
+
+def make_topo(ops, ei, N, sorted_side=None):
+    return ops["topo"].Topo.from_edge_index(ei.to(DEV), N, sorted_side=sorted_side)
+
+
+# ----------------------------------------------------------------------------- CSR ---
+@pytest.mark.parametrize("N,E", [(1, 1), (7, 0), (50, 400), (1000, 20000), (8192, 475000), (3, 5000)])
+def test_csr_build_bit_exact(ops, N, E):
+    gen = torch.Generator().manual_seed(N + E)
+    key = torch.randint(0, N, (E,), generator=gen, dtype=torch.int32)
+    rowptr, perm = ops["topo"].build_csr(key.to(DEV), N)
+    r_ref, p_ref = ks.csr_build(key, N)
+    assert torch.equal(rowptr.cpu(), r_ref)
+    assert torch.equal(perm.cpu(), p_ref)
+
+
+# --------------------------------------------------------------- contraction family ---
+NODE_CASES = [
+    # (N, E, F, C, CA, CO, hasA, hasW, hasU, sorted)
+    (64, 600, 128, 1, 1, 1, True, True, False, False),      # CFConv aggregate
+    (64, 600, 128, 1, 1, 1, True, True, False, True),       # same, edges already grouped (perm NULL)
+    (64, 600, 128, 1, 1, 1, False, True, False, False),     # segment_sum
+    (40, 300, 3, 1, 1, 1, False, True, False, False),       # coordinate update, F=3 (scalar path)
+    (40, 300, 1, 1, 1, 1, False, True, False, True),        # energy sum, F=1
+    (50, 700, 64, 3, 1, 3, True, True, True, False),        # PaiNN direction term
+    (50, 700, 64, 3, 3, 3, True, True, False, False),       # PaiNN vector term
+    (50, 700, 12, 3, 3, 1, True, True, True, False),        # backward w.r.t. a 1-channel operand
+    (50, 700, 20, 3, 1, 3, True, False, True, False),
+    (30, 0, 16, 1, 1, 1, True, True, False, False),         # no edges -> zeros
+    (2000, 60000, 128, 1, 1, 1, True, True, False, True),
+    (33, 500, 6, 1, 1, 1, True, True, False, False),        # F not a multiple of 4
+]
+
+
+@pytest.mark.parametrize("case", NODE_CASES)
+def test_contract_node_bit_exact(ops, case):
+    N, E, F, C, CA, CO, hasA, hasW, hasU, srt = case
+    gen = torch.Generator().manual_seed(hash(case) % 1000)
+    ei = random_graph(gen, N, E, sorted_dst=srt)
+    A = (torch.randn(N, F, generator=gen) if CA == 1 else torch.randn(N, CA, F, generator=gen)) if hasA else None
+    W = torch.randn(E, F, generator=gen) if hasW else None
+    U = torch.randn(E, C, generator=gen) if hasU else None
+    topo = make_topo(ops, ei, N, sorted_side=1 if srt else None)
+    dev = lambda t: None if t is None else t.to(DEV)
+    got = ops["contract"]._node_raw(topo, 1, dev(A), 0, dev(W), dev(U), C, CO, F)
+    want = ks.contract_node(ei[1].int(), N, A, ei[0].int(), W, U, C, CO, F)
+    assert torch.equal(got.cpu().reshape(want.shape), want)
+    again = ops["contract"]._node_raw(topo, 1, dev(A), 0, dev(W), dev(U), C, CO, F)
+    assert torch.equal(got, again)   # run-to-run bit reproducible
+
+
+@pytest.mark.parametrize("F,C,CG,CX,hasG,hasX,hasU", [
+    (128, 1, 1, 1, True, True, False), (128, 1, 1, 1, True, False, False), (3, 1, 1, 1, True, False, False),
+    (64, 3, 3, 1, True, True, True), (64, 3, 3, 3, True, True, False), (10, 3, 1, 1, True, True, True),
+    (1, 1, 1, 1, True, False, False)])
+def test_contract_edge_w_bit_exact(ops, F, C, CG, CX, hasG, hasX, hasU):
+    gen = torch.Generator().manual_seed(F * 7 + C)
+    N, E = 80, 900
+    ei = random_graph(gen, N, E)
+    mk = lambda ch: torch.randn(N, F, generator=gen) if ch == 1 else torch.randn(N, ch, F, generator=gen)
+    G = mk(CG) if hasG else None
+    X = mk(CX) if hasX else None
+    U = torch.randn(E, C, generator=gen) if hasU else None
+    topo = make_topo(ops, ei, N)
+    dev = lambda t: None if t is None else t.to(DEV)
+    got = ops["contract"]._edge_w_raw(topo, dev(G), 0, dev(X), 1, dev(U), C, F)
+    want = ks.contract_edge_w(G, ei[0], X, ei[1], U, E, C, F)
+    assert torch.equal(got.cpu(), want)
+
+
+@pytest.mark.parametrize("F,C,CG,CX,hasW", [(128, 1, 1, 1, True), (64, 3, 3, 1, True), (64, 3, 3, 3, False),
+                                            (12, 3, 1, 3, True), (3, 1, 1, 1, False)])
+def test_contract_edge_u_close(ops, F, C, CG, CX, hasW):
+    gen = torch.Generator().manual_seed(F + C)
+    N, E = 80, 900
+    ei = random_graph(gen, N, E)
+    mk = lambda ch: torch.randn(N, F, generator=gen) if ch == 1 else torch.randn(N, ch, F, generator=gen)
+    G, X = mk(CG), mk(CX)
+    W = torch.randn(E, F, generator=gen) if hasW else None
+    topo = make_topo(ops, ei, N)
+    dev = lambda t: None if t is None else t.to(DEV)
+    got = ops["contract"]._edge_u_raw(topo, dev(G), 0, dev(X), 1, dev(W), C, F)
+    want = ks.contract_edge_u(G, ei[0], X, ei[1], W, E, C, F)
+    # fp32 dot product of F terms in a different (fixed tree) order: |err| <= F * eps * sum|terms|
+    torch.testing.assert_close(got.cpu(), want, rtol=1e-5, atol=1e-5)
+    again = ops["contract"]._edge_u_raw(topo, dev(G), 0, dev(X), 1, dev(W), C, F)
+    assert torch.equal(got, again)
+
+
+def test_edge_gather_add_bit_exact(ops):
+    gen = torch.Generator().manual_seed(3)
+    N, E, F = 100, 1500, 128
+    ei = random_graph(gen, N, E)
+    P, Q = torch.randn(N, F, generator=gen), torch.randn(N, F, generator=gen)
+    topo = make_topo(ops, ei, N)
+    got = ops["contract"]._edge_gather_add_raw(topo, P.to(DEV), 0, Q.to(DEV), 1)
+    assert torch.equal(got.cpu(), ks.edge_gather_add(P, ei[0], Q, ei[1]))
+
+
+def test_strided_operands(ops):
+    """Column slices of a wider matrix (PaiNN's split of the [E,3F] filter) are read in place."""
+    gen = torch.Generator().manual_seed(5)
+    N, E, F = 60, 800, 32
+    ei = random_graph(gen, N, E)
+    wide_w, wide_a = torch.randn(E, 3 * F, generator=gen), torch.randn(N, 3 * F, generator=gen)
+    topo = make_topo(ops, ei, N)
+    Wd, Ad = wide_w.to(DEV), wide_a.to(DEV)
+    for k in range(3):
+        got = ops["contract"]._node_raw(topo, 0, Ad[:, k * F:(k + 1) * F], 1, Wd[:, k * F:(k + 1) * F], None, 1, 1, F)
+        want = ks.contract_node(ei[0].int(), N, wide_a[:, k * F:(k + 1) * F], ei[1].int(),
+                                wide_w[:, k * F:(k + 1) * F], None, 1, 1, F)
+        assert torch.equal(got.cpu(), want)
+
+
+def test_autograd_closure_double_backward(ops):
+    """d/dA, d/dW, d/dU of contract_node and their derivatives against torch autograd on CPU."""
+    gen = torch.Generator().manual_seed(11)
+    N, E, F = 30, 200, 16
+    ei = random_graph(gen, N, E)
+    A = torch.randn(N, 3, F, generator=gen)
+    W = torch.randn(E, F, generator=gen)
+    U = torch.randn(E, 3, generator=gen)
+    probe = torch.randn(N, 3, F, generator=gen)
+
+    def loss_fn(a, w, u, contract):
+        out = contract(a, w, u)
+        (ga,) = torch.autograd.grad((out * probe.to(out.device)).sum(), a, create_graph=True)
+        return (ga ** 2).sum() + (out ** 2).sum()
+
+    topo = make_topo(ops, ei, N)
+    a, w, u = (t.clone().to(DEV).requires_grad_(True) for t in (A, W, U))
+    loss = loss_fn(a, w, u, lambda a_, w_, u_: ops["ops"].contract_node(topo, 0, A=a_, side_a=1, W=w_, U=u_, C=3, CO=3, F=F))
+    loss.backward()
+
+    a2, w2, u2 = (t.clone().requires_grad_(True) for t in (A, W, U))
+
+    def cpu_contract(a_, w_, u_):
+        term = a_[ei[1]] * w_.unsqueeze(1) * u_.unsqueeze(-1)
+        return torch.zeros(N, 3, F).index_add(0, ei[0], term)
+
+    loss2 = loss_fn(a2, w2, u2, cpu_contract)
+    loss2.backward()
+    torch.testing.assert_close(loss.detach().cpu(), loss2.detach(), rtol=1e-5, atol=1e-5)
+    for got, want in ((a, a2), (w, w2), (u, u2)):
+        torch.testing.assert_close(got.grad.cpu(), want.grad, rtol=2e-4, atol=2e-4)
+
+
+# ------------------------------------------------------------------------------ PNA ---
+@pytest.mark.parametrize("N,E,F,hasR", [(40, 300, 8, False), (40, 300, 8, True), (200, 3000, 128, True), (10, 0, 4, False)])
+def test_pna_aggregate(ops, N, E, F, hasR):
+    gen = torch.Generator().manual_seed(N + F)
+    ei = random_graph(gen, N, E)
+    # quantised values create exact ties for min / max
+    P = torch.randint(-3, 4, (N, F), generator=gen).float() * 0.25
+    Q = torch.randint(-3, 4, (N, F), generator=gen).float() * 0.25
+    R = torch.randn(E, F, generator=gen) if hasR else None
+    topo = make_topo(ops, ei, N)
+    dev = lambda t: None if t is None else t.to(DEV)
+    out, cmin, cmax = ops["pna"]._pna_fwd_raw(dev(P), dev(Q), dev(R), topo)
+    want, wmin, wmax = ks.pna_aggregate_fwd(P, Q, R, ei[0], ei[1], N)
+    F4 = out.size(1) // 4
+    assert torch.equal(out.cpu()[:, F4:3 * F4], want[:, F4:3 * F4])          # min, max: exact
+    assert torch.equal(cmin.cpu(), wmin) and torch.equal(cmax.cpu(), wmax)
+    torch.testing.assert_close(out.cpu(), want, rtol=1e-5, atol=1e-6)        # mean, std
+    gout = torch.randn(N, 4 * F, generator=gen)
+    gh = ops["pna"]._pna_bwd_raw(gout.to(DEV), out, cmin, cmax, dev(P), dev(Q), dev(R), topo)
+    want_gh = ks.pna_aggregate_bwd(gout, out.cpu(), cmin.cpu(), cmax.cpu(), P, Q, R, ei[0], ei[1], N)
+    torch.testing.assert_close(gh.cpu(), want_gh, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------------ attention ---
+@pytest.mark.parametrize("sizes,H,D", [([37], 4, 32), ([5, 64, 1, 130, 23], 4, 32), ([300], 2, 8),
+                                       ([9, 9, 9], 1, 16), ([70, 3], 4, 4), ([1024], 4, 32)])
+def test_attn_varlen(ops, sizes, H, D):
+    gen = torch.Generator().manual_seed(sum(sizes) + H)
+    N = sum(sizes)
+    cu = torch.tensor([0] + list(np.cumsum(sizes)), dtype=torch.int32)
+    q, k, v = (torch.randn(N, H * D, generator=gen) for _ in range(3))
+    do = torch.randn(N, H * D, generator=gen)
+    scale = 1.0 / np.sqrt(D)
+    o, lse, *_ = ops["attention"]._attn_fwd_raw(q.to(DEV), k.to(DEV), v.to(DEV), cu.to(DEV), H, scale)
+    o_ref, lse_ref = ks.attn_varlen_fwd(q, k, v, cu, H, scale)
+    # fp32 online softmax vs dense softmax: north_star tolerance rel 1e-5 (+ abs floor of a few ulp)
+    torch.testing.assert_close(o.cpu(), o_ref, rtol=1e-5, atol=2e-6)
+    torch.testing.assert_close(lse.cpu(), lse_ref, rtol=1e-5, atol=2e-6)
+    dq, dk, dv = ops["attention"]._attn_bwd_raw(do.to(DEV), o, lse, q.to(DEV), k.to(DEV), v.to(DEV),
+                                               cu.to(DEV), H, scale)
+    rq, rk, rv = ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
+    for got, want in ((dq, rq), (dk, rk), (dv, rv)):
+        torch.testing.assert_close(got.cpu(), want, rtol=1e-4, atol=1e-5)
+
+
+def test_attn_strided_qkv(ops):
+    """q,k,v as column blocks of the packed in_proj output (no copies)."""
+    gen = torch.Generator().manual_seed(2)
+    N, H, D = 150, 4, 32
+    qkv = torch.randn(N, 3 * H * D, generator=gen)
+    cu = torch.tensor([0, 50, 150], dtype=torch.int32)
+    c = H * D
+    qd = qkv.to(DEV)
+    out = ops["ops"].attn_varlen(qd[:, :c], qd[:, c:2 * c], qd[:, 2 * c:], cu.to(DEV), H)
+    ref, _ = ks.attn_varlen_fwd(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu, H, 1.0 / np.sqrt(D))
+    torch.testing.assert_close(out.cpu(), ref, rtol=1e-5, atol=2e-6)
+
+
+# --------------------------------------------------------------------- radius graph ---
+def _canon(src, dst, S):
+    order = np.lexsort((S[:, 2], S[:, 1], S[:, 0], src, dst))
+    return src[order], dst[order], S[order]
+
+
+@pytest.mark.parametrize("case", ["h2_loop0", "h2_loop1", "cr_loop0", "cr_loop1", "tri_loop0", "tri_loop1",
+                                  "h2_big_loop0", "h2_big_loop1"])
+def test_radius_graph_pbc_vs_reference_golden(ops, golden, case):
+    """Edge lists of the REAL reference RadiusGraphPBC (tests/golden), bit-exact after canonical sort."""
+    c = golden["pbc"][case]
+    n = c["pos"].size(0)
+    g = ops["ops"].radius_graph(c["pos"].to(DEV), torch.tensor([0, n]), c["r"], c["cap"], c["loop"],
+                                cell=c["cell"].reshape(1, 3, 3), pbc=c["pbc"].reshape(1, 3))
+    src, dst, S = _canon(g["src"].cpu().numpy(), g["dst"].cpu().numpy(), g["shift_int"].cpu().numpy())
+    ref_shift = c["edge_shifts"].numpy()
+    ref_S = np.rint(ref_shift @ np.linalg.inv(c["cell"].numpy().astype(np.float64))).astype(np.int64)
+    rs, rd, rS = _canon(c["edge_index"][0].numpy(), c["edge_index"][1].numpy(), ref_S)
+    assert np.array_equal(src, rs) and np.array_equal(dst, rd) and np.array_equal(S, rS)
+    assert torch.allclose(g["edge_shifts"].cpu(), torch.from_numpy(S).float() @ c["cell"], atol=1e-5)
+
+
+def _random_cells(gen, B):
+    cells = []
+    for _ in range(B):
+        a = 6.0 + 3.0 * torch.rand(3, generator=gen)
+        cell = torch.diag(a)
+        cell[1, 0] = 1.5 * torch.rand(1, generator=gen).item()
+        cell[2, 0] = 0.8 * torch.rand(1, generator=gen).item()
+        cell[2, 1] = 1.1 * torch.rand(1, generator=gen).item()
+        cells.append(cell)
+    return torch.stack(cells)
+
+
+@pytest.mark.parametrize("cap,loop,pbcs", [(0, False, (1, 1, 1)), (12, False, (1, 1, 1)), (0, True, (1, 1, 0)),
+                                           (20, True, (1, 0, 0)), (0, False, (0, 0, 0))])
+def test_radius_graph_ase_batched_bit_exact(ops, cap, loop, pbcs):
+    gen = torch.Generator().manual_seed(17 + cap)
+    B = 5
+    sizes = [int(s) for s in torch.randint(1, 60, (B,), generator=gen)]
+    ptr = torch.tensor([0] + list(np.cumsum(sizes)))
+    cells = _random_cells(gen, B)
+    pos = torch.cat([(torch.rand(n, 3, generator=gen) * 1.6 - 0.3) @ cells[b] for b, n in enumerate(sizes)])
+    pbc = torch.tensor([pbcs] * B, dtype=torch.bool)
+    g = ops["ops"].radius_graph(pos.to(DEV), ptr, 3.1, cap, loop, cell=cells, pbc=pbc)
+    src, dst, S, dist, rowptr = ks.radius_graph(pos, ptr, 3.1, cap, loop, cells, pbc, mode=0)
+    assert torch.equal(g["rowptr"].cpu(), rowptr)
+    assert torch.equal(g["src"].cpu(), src) and torch.equal(g["dst"].cpu(), dst)
+    assert torch.equal(g["shift_int"].cpu(), S)
+    assert torch.equal(g["dist"].cpu(), dist)     # fp64 distances, same operation order
+
+
+@pytest.mark.parametrize("cap", [0, 8, 32])
+def test_radius_graph_cluster_bit_exact(ops, cap):
+    gen = torch.Generator().manual_seed(23 + cap)
+    sizes = [18, 3, 29, 1, 22, 40]
+    ptr = torch.tensor([0] + list(np.cumsum(sizes)))
+    pos = torch.cat([torch.rand(n, 3, generator=gen) * 6.0 for n in sizes])
+    g = ops["ops"].radius_graph(pos.to(DEV), ptr, 3.0, cap, False)
+    src, dst, S, dist, rowptr = ks.radius_graph(pos, ptr, 3.0, cap, False, mode=1)
+    assert torch.equal(g["src"].cpu(), src) and torch.equal(g["dst"].cpu(), dst)
+    assert torch.equal(g["rowptr"].cpu(), rowptr)
+
+
+def test_radius_graph_fesi_full_size_properties(ops):
+    """BASELINE config 5 at full size (8 x 1024-atom BCC cells, r=5): size-independent properties."""
+    gen = torch.Generator().manual_seed(5)
+    a, n = 2.8, 8
+    grid = torch.stack(torch.meshgrid(*[torch.arange(n)] * 3, indexing="ij"), -1).reshape(-1, 3).float()
+    base = torch.cat([grid, grid + 0.5]) * a
+    B = 8
+    pos = torch.cat([base + 0.05 * torch.randn(base.shape, generator=gen) for _ in range(B)])
+    ptr = torch.arange(B + 1) * base.size(0)
+    cell = (torch.eye(3) * a * n).repeat(B, 1, 1)
+    pbc = torch.ones(B, 3, dtype=torch.bool)
+    g = ops["ops"].radius_graph(pos.to(DEV), ptr, 5.0, 64, False, cell=cell, pbc=pbc)
+    src, dst = g["src"].long(), g["dst"].long()
+    deg = torch.bincount(dst, minlength=pos.size(0))
+    assert int(deg.min()) == 58 and int(deg.max()) == 58           # shells 8+6+12+24+8
+    assert torch.equal(dst, torch.sort(dst).values)                # grouped by destination
+    assert bool(((src // 1024) == (dst // 1024)).all())            # never crosses graphs
+    vec = pos.to(DEV)[dst] - pos.to(DEV)[src] + g["edge_shifts"]
+    d = vec.norm(dim=1)
+    assert float(d.max()) < 5.0 + 1e-4
+    # symmetry: (i, j, S) present  <=>  (j, i, -S) present
+    key = lambda s, t, S: ((s * 8192 + t) * 27 + (S[:, 0] + 1) * 9 + (S[:, 1] + 1) * 3 + (S[:, 2] + 1))
+    S = g["shift_int"].long()
+    assert torch.equal(torch.sort(key(src, dst, S)).values, torch.sort(key(dst, src, -S)).values)
