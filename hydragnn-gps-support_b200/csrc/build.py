@@ -42,7 +42,7 @@ def _digest():
     )
     names.append(os.path.join(os.path.dirname(PKG), "include", "hgk.h"))
     for n in names:
-        h.update(n.encode())
+        h.update(os.path.basename(n).encode())   # location-independent: the .so travels
         with open(n, "rb") as fh:
             h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())

@@ -367,6 +367,13 @@ extern "C" int hgk_contract_node(float* out, int64_t ldo, int32_t CO, const floa
               (long long)N, (long long)E, F);
   if (N == 0) return HGK_OK;
   HGK_REQUIRE(out && rowptr, "contract_node: out/rowptr is NULL");
+  if (E == 0) {  // every segment is empty: zeros (gidx / W / U may be NULL-sized)
+    HGK_REQUIRE(CO >= 1 && ldo >= (int64_t)CO * F, "contract_node: bad ldo/CO");
+    cudaError_t err = cudaMemset2DAsync(out, sizeof(float) * ldo, 0, sizeof(float) * CO * F, N,
+                                        (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "contract_node: memset: %s", cudaGetErrorString(err));
+    return HGK_OK;
+  }
   HGK_REQUIRE(C == 1 || C == 3, "contract_node: C must be 1 or 3 (got %d)", C);
   HGK_REQUIRE(channels_ok(CO, C), "contract_node: CO=%d incompatible with C=%d", CO, C);
   HGK_REQUIRE(!A || channels_ok(CA, C), "contract_node: CA=%d incompatible with C=%d", CA, C);

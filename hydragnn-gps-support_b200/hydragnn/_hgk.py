@@ -111,6 +111,66 @@ def check(status, what):
         raise HgkError(f"{what} failed with status {status}: {msg.decode() if msg else ''}")
 
 
+# CUDA kernels enqueued by one call of each entry point (for bench.py's gpu_launches count)
+KERNELS_PER_CALL = {
+    "hgk_csr_build": 4, "hgk_contract_node": 1, "hgk_contract_edge_w": 1, "hgk_contract_edge_u": 1,
+    "hgk_edge_gather_add": 1, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
+    "hgk_radius_graph_count": 8, "hgk_radius_graph_fill": 1, "hgk_attn_varlen_fwd": 1,
+    "hgk_attn_varlen_bwd": 3,
+}
+
+
+class Stats:
+    """Call counters and (optionally) CUDA-event timing of every C-ABI call.
+
+    `cost` is the ALGORITHMIC work of the call -- (bytes, flops) from the formulas in DESIGN.md --
+    so that achieved GB/s or TFLOP/s = sum(cost) / sum(event time) per entry point."""
+
+    def __init__(self):
+        self.reset()
+        self.timing = False
+
+    def reset(self):
+        self.calls = {}
+        self.cost = {}
+        self.events = []
+
+    def launches(self):
+        return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in self.calls.items())
+
+    def summary(self):
+        """name -> dict(calls, ms, bytes, flops); call after torch.cuda.synchronize()."""
+        out = {}
+        for name, n in self.calls.items():
+            b, f = self.cost.get(name, (0, 0))
+            out[name] = dict(calls=n, ms=0.0, bytes=b, flops=f)
+        for name, e0, e1 in self.events:
+            out[name]["ms"] += e0.elapsed_time(e1)
+        return out
+
+
+stats = Stats()
+
+
+def call(name, *args, cost=(0, 0)):
+    """Invoke entry point `name` on torch's current stream; count it, optionally time it."""
+    fn = getattr(lib(), name)
+    stats.calls[name] = stats.calls.get(name, 0) + 1
+    if cost != (0, 0):
+        b, f = stats.cost.get(name, (0, 0))
+        stats.cost[name] = (b + cost[0], f + cost[1])
+    if stats.timing:
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        status = fn(*args, stream_ptr())
+        e1.record()
+        stats.events.append((name, e0, e1))
+    else:
+        status = fn(*args, stream_ptr())
+    check(status, name)
+
+
 def stream_ptr():
     return _c_ptr(torch.cuda.current_stream().cuda_stream)
 

@@ -12,8 +12,20 @@ import torch
 from .. import _hgk
 
 
+def _sum_sq(cu_seqlens):
+    """sum of squared segment lengths (host value cached on the tensor: no sync in the hot loop)."""
+    v = getattr(cu_seqlens, "_hgk_sum_sq", None)
+    if v is None:
+        lens = (cu_seqlens[1:] - cu_seqlens[:-1]).to(torch.int64)
+        v = int((lens * lens).sum())
+        try:
+            cu_seqlens._hgk_sum_sq = v
+        except Exception:
+            pass
+    return v
+
+
 def _attn_fwd_raw(q, k, v, cu_seqlens, H, scale):
-    L = _hgk.lib()
     N, HD = q.shape
     D = HD // H
     q_t, ldq = _hgk.rows(q)
@@ -22,17 +34,13 @@ def _attn_fwd_raw(q, k, v, cu_seqlens, H, scale):
     o = torch.empty((N, HD), dtype=torch.float32, device=q.device)
     lse = torch.empty((N, H), dtype=torch.float32, device=q.device)
     S = cu_seqlens.numel() - 1
-    _hgk.check(
-        L.hgk_attn_varlen_fwd(_hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
-                              _hgk.ptr(v_t), ldv, _hgk.ptr(cu_seqlens), S, N, H, D, float(scale),
-                              _hgk.stream_ptr()),
-        "hgk_attn_varlen_fwd",
-    )
+    _hgk.call("hgk_attn_varlen_fwd", _hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
+              _hgk.ptr(v_t), ldv, _hgk.ptr(cu_seqlens), S, N, H, D, float(scale),
+              cost=(4 * (4 * N * HD + N * H), 4 * HD * _sum_sq(cu_seqlens)))
     return o, lse, q_t, k_t, v_t
 
 
 def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
-    L = _hgk.lib()
     N, HD = o.shape
     D = HD // H
     do_t, lddo = _hgk.rows(do)
@@ -43,14 +51,10 @@ def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
     _, ldq = _hgk.rows(q)
     _, ldk = _hgk.rows(k)
     _, ldv = _hgk.rows(v)
-    _hgk.check(
-        L.hgk_attn_varlen_bwd(_hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
-                              _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse),
-                              _hgk.ptr(q), ldq, _hgk.ptr(k), ldk, _hgk.ptr(v), ldv,
-                              _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(scale),
-                              _hgk.stream_ptr()),
-        "hgk_attn_varlen_bwd",
-    )
+    _hgk.call("hgk_attn_varlen_bwd", _hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
+              _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q), ldq, _hgk.ptr(k), ldk,
+              _hgk.ptr(v), ldv, _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(scale),
+              cost=(4 * (8 * N * HD + 2 * N * H), 10 * HD * _sum_sq(cu)))
     return dq, dk, dv
 
 

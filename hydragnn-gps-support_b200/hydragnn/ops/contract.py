@@ -24,7 +24,6 @@ def _channels(t):
 
 
 def _node_raw(topo, side_out, A, side_a, W, U, C, CO, F):
-    L = _hgk.lib()
     N = topo.num_rows[side_out]
     rowptr, perm = topo.csr(side_out)
     dev = rowptr.device
@@ -36,20 +35,18 @@ def _node_raw(topo, side_out, A, side_a, W, U, C, CO, F):
     w_t, ldw = (None, 0) if W is None else _hgk.rows(W)
     u_t = None if U is None else U.contiguous()
     gidx = topo.idx[side_a] if A is not None else None
-    _hgk.check(
-        L.hgk_contract_node(
-            _hgk.ptr(out), CO * F, CO, _hgk.ptr(a_t), lda, ca, _hgk.ptr(w_t), ldw,
-            _hgk.ptr(u_t), _hgk.ptr(rowptr), _hgk.ptr(perm), _hgk.ptr(gidx), N, topo.E, F, C,
-            _hgk.stream_ptr()),
-        "hgk_contract_node",
-    )
+    E = topo.E
+    # algorithmic bytes: gathered A rows + W rows + U + indices per edge, output rows + rowptr per node
+    nbytes = E * (4 * F * (ca if A is not None else 0) + (4 * F if W is not None else 0)
+                  + (4 * C if U is not None else 0) + (4 if A is not None else 0)
+                  + (4 if perm is not None else 0)) + N * (4 * CO * F + 4)
+    _hgk.call("hgk_contract_node", _hgk.ptr(out), CO * F, CO, _hgk.ptr(a_t), lda, ca, _hgk.ptr(w_t), ldw,
+              _hgk.ptr(u_t), _hgk.ptr(rowptr), _hgk.ptr(perm), _hgk.ptr(gidx), N, E, F, C,
+              cost=(nbytes, 0))
     return out
 
 
-def _edge_w_raw(topo, G, side_g, X, side_x, U, C, F):
-    L = _hgk.lib()
-    dev = topo.device
-    out = torch.empty((topo.E, F), dtype=torch.float32, device=dev)
+def _edge_operands(topo, G, side_g, X, side_x):
     g_t, ldg, cg = None, 0, 1
     if G is not None:
         g_t, ldg = _hgk.rows(G)
@@ -58,39 +55,32 @@ def _edge_w_raw(topo, G, side_g, X, side_x, U, C, F):
     if X is not None:
         x_t, ldx = _hgk.rows(X)
         cx = _channels(X)
+    gi = topo.idx[side_g] if G is not None else None
+    xi = topo.idx[side_x] if X is not None else None
+    return g_t, ldg, cg, gi, x_t, ldx, cx, xi
+
+
+def _edge_w_raw(topo, G, side_g, X, side_x, U, C, F):
+    out = torch.empty((topo.E, F), dtype=torch.float32, device=topo.device)
+    g_t, ldg, cg, gi, x_t, ldx, cx, xi = _edge_operands(topo, G, side_g, X, side_x)
     u_t = None if U is None else U.contiguous()
-    _hgk.check(
-        L.hgk_contract_edge_w(
-            _hgk.ptr(out), F, _hgk.ptr(g_t), ldg, cg,
-            _hgk.ptr(topo.idx[side_g] if G is not None else None),
-            _hgk.ptr(x_t), ldx, cx, _hgk.ptr(topo.idx[side_x] if X is not None else None),
-            _hgk.ptr(u_t), topo.E, F, C, _hgk.stream_ptr()),
-        "hgk_contract_edge_w",
-    )
+    E = topo.E
+    nbytes = E * (4 * F * ((cg if G is not None else 0) + (cx if X is not None else 0)) + 4 * F
+                  + (4 * C if U is not None else 0) + 4 * ((G is not None) + (X is not None)))
+    _hgk.call("hgk_contract_edge_w", _hgk.ptr(out), F, _hgk.ptr(g_t), ldg, cg, _hgk.ptr(gi),
+              _hgk.ptr(x_t), ldx, cx, _hgk.ptr(xi), _hgk.ptr(u_t), E, F, C, cost=(nbytes, 0))
     return out
 
 
 def _edge_u_raw(topo, G, side_g, X, side_x, W, C, F):
-    L = _hgk.lib()
-    dev = topo.device
-    out = torch.empty((topo.E, C), dtype=torch.float32, device=dev)
-    g_t, ldg, cg = None, 0, 1
-    if G is not None:
-        g_t, ldg = _hgk.rows(G)
-        cg = _channels(G)
-    x_t, ldx, cx = None, 0, 1
-    if X is not None:
-        x_t, ldx = _hgk.rows(X)
-        cx = _channels(X)
+    out = torch.empty((topo.E, C), dtype=torch.float32, device=topo.device)
+    g_t, ldg, cg, gi, x_t, ldx, cx, xi = _edge_operands(topo, G, side_g, X, side_x)
     w_t, ldw = (None, 0) if W is None else _hgk.rows(W)
-    _hgk.check(
-        L.hgk_contract_edge_u(
-            _hgk.ptr(out), _hgk.ptr(g_t), ldg, cg,
-            _hgk.ptr(topo.idx[side_g] if G is not None else None),
-            _hgk.ptr(x_t), ldx, cx, _hgk.ptr(topo.idx[side_x] if X is not None else None),
-            _hgk.ptr(w_t), ldw, topo.E, F, C, _hgk.stream_ptr()),
-        "hgk_contract_edge_u",
-    )
+    E = topo.E
+    nbytes = E * (4 * F * ((cg if G is not None else 0) + (cx if X is not None else 0))
+                  + (4 * F if W is not None else 0) + 4 * C + 4 * ((G is not None) + (X is not None)))
+    _hgk.call("hgk_contract_edge_u", _hgk.ptr(out), _hgk.ptr(g_t), ldg, cg, _hgk.ptr(gi),
+              _hgk.ptr(x_t), ldx, cx, _hgk.ptr(xi), _hgk.ptr(w_t), ldw, E, F, C, cost=(nbytes, 0))
     return out
 
 
@@ -219,17 +209,13 @@ def gather_mul_segment_sum(x, W, topo, side_out=1, side_in=0):
 
 
 def _edge_gather_add_raw(topo, P, side_p, Q, side_q):
-    L = _hgk.lib()
     F = P.size(-1)
     out = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
     p_t, ldp = _hgk.rows(P)
     q_t, ldq = _hgk.rows(Q)
-    _hgk.check(
-        L.hgk_edge_gather_add(_hgk.ptr(out), F, _hgk.ptr(p_t), ldp, _hgk.ptr(topo.idx[side_p]),
-                              _hgk.ptr(q_t), ldq, _hgk.ptr(topo.idx[side_q]), topo.E, F,
-                              _hgk.stream_ptr()),
-        "hgk_edge_gather_add",
-    )
+    _hgk.call("hgk_edge_gather_add", _hgk.ptr(out), F, _hgk.ptr(p_t), ldp, _hgk.ptr(topo.idx[side_p]),
+              _hgk.ptr(q_t), ldq, _hgk.ptr(topo.idx[side_q]), topo.E, F,
+              cost=(topo.E * (3 * 4 * F + 8), 0))
     return out
 
 

@@ -12,33 +12,28 @@ from .contract import segment_sum
 
 
 def _pna_fwd_raw(P, Q, R, topo):
-    L = _hgk.lib()
     N, F = P.shape
     rowptr, perm = topo.csr(1)  # segments = destination (edge_index[1])
     out = torch.empty((N, 4 * F), dtype=torch.float32, device=P.device)
     cmin = torch.empty((N, F), dtype=torch.int32, device=P.device)
     cmax = torch.empty((N, F), dtype=torch.int32, device=P.device)
-    _hgk.check(
-        L.hgk_pna_aggregate_fwd(_hgk.ptr(out), _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P),
-                                _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(perm),
-                                _hgk.ptr(topo.idx[0]), N, topo.E, F, _hgk.stream_ptr()),
-        "hgk_pna_aggregate_fwd",
-    )
+    E = topo.E
+    nbytes = E * (4 * F + (4 * F if R is not None else 0) + 8) + N * (4 * F + 6 * 4 * F + 4)
+    _hgk.call("hgk_pna_aggregate_fwd", _hgk.ptr(out), _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P),
+              _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(perm), _hgk.ptr(topo.idx[0]),
+              N, E, F, cost=(nbytes, 0))
     return out, cmin, cmax
 
 
 def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo):
-    L = _hgk.lib()
     N, F = P.shape
     rowptr, _ = topo.csr(1)
     gh = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
-    _hgk.check(
-        L.hgk_pna_aggregate_bwd(_hgk.ptr(gh), _hgk.ptr(gout.contiguous()), _hgk.ptr(out),
-                                _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P), _hgk.ptr(Q),
-                                _hgk.ptr(R), _hgk.ptr(rowptr), _hgk.ptr(topo.idx[0]),
-                                _hgk.ptr(topo.idx[1]), N, topo.E, F, _hgk.stream_ptr()),
-        "hgk_pna_aggregate_bwd",
-    )
+    E = topo.E
+    nbytes = E * (4 * F * (3 + (R is not None)) + 8) + N * (4 * F * 10)
+    _hgk.call("hgk_pna_aggregate_bwd", _hgk.ptr(gh), _hgk.ptr(gout.contiguous()), _hgk.ptr(out),
+              _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P), _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr),
+              _hgk.ptr(topo.idx[0]), _hgk.ptr(topo.idx[1]), N, E, F, cost=(nbytes, 0))
     return gh
 
 

@@ -43,13 +43,9 @@ def radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=No
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     deg_raw = torch.empty(N, dtype=torch.int32, device=dev)
     deg = torch.empty(N, dtype=torch.int32, device=dev)
-    st = _hgk.stream_ptr()
-    _hgk.check(
-        L.hgk_radius_graph_count(_hgk.ptr(pos), _hgk.ptr(ptr32), _hgk.ptr(cell_t), _hgk.ptr(pbc_t),
-                                 N, B, float(r), int(max_num_neighbors or 0), int(bool(loop)), mode,
-                                 _hgk.ptr(deg_raw), _hgk.ptr(deg), _hgk.ptr(ws), ws_bytes, st),
-        "hgk_radius_graph_count",
-    )
+    _hgk.call("hgk_radius_graph_count", _hgk.ptr(pos), _hgk.ptr(ptr32), _hgk.ptr(cell_t), _hgk.ptr(pbc_t),
+              N, B, float(r), int(max_num_neighbors or 0), int(bool(loop)), mode,
+              _hgk.ptr(deg_raw), _hgk.ptr(deg), _hgk.ptr(ws), ws_bytes, cost=(N * 56, 0))
     rowptr_raw = torch.zeros(N + 1, dtype=torch.int32, device=dev)
     rowptr = torch.zeros(N + 1, dtype=torch.int32, device=dev)
     rowptr_raw[1:] = torch.cumsum(deg_raw, 0)
@@ -61,14 +57,11 @@ def radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=No
     shift = torch.empty((E, 3), dtype=torch.int32, device=dev)
     dist = torch.empty(E, dtype=torch.float64, device=dev)
     cand = torch.empty(max(E_raw, 1) * 24, dtype=torch.uint8, device=dev)
-    _hgk.check(
-        L.hgk_radius_graph_fill(_hgk.ptr(pos), _hgk.ptr(ptr32), _hgk.ptr(cell_t), _hgk.ptr(pbc_t),
-                                N, B, float(r), int(max_num_neighbors or 0), int(bool(loop)), mode,
-                                _hgk.ptr(rowptr_raw), _hgk.ptr(rowptr), _hgk.ptr(src), _hgk.ptr(dst),
-                                _hgk.ptr(shift), _hgk.ptr(dist), _hgk.ptr(cand), cand.numel(),
-                                _hgk.ptr(ws), ws_bytes, st),
-        "hgk_radius_graph_fill",
-    )
+    _hgk.call("hgk_radius_graph_fill", _hgk.ptr(pos), _hgk.ptr(ptr32), _hgk.ptr(cell_t), _hgk.ptr(pbc_t),
+              N, B, float(r), int(max_num_neighbors or 0), int(bool(loop)), mode,
+              _hgk.ptr(rowptr_raw), _hgk.ptr(rowptr), _hgk.ptr(src), _hgk.ptr(dst),
+              _hgk.ptr(shift), _hgk.ptr(dist), _hgk.ptr(cand), cand.numel(), _hgk.ptr(ws), ws_bytes,
+              cost=(N * 24 + E * 28 + E_raw * 48, 0))
     out = {
         "edge_index": torch.stack([src, dst]).to(torch.int64),
         "src": src,

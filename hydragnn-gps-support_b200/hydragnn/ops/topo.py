@@ -22,11 +22,9 @@ def build_csr(key, num_rows):
     perm = torch.empty(max(E, 1), dtype=torch.int32, device=key.device)
     ws_bytes = L.hgk_csr_build_workspace_bytes(E, num_rows)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=key.device)
-    _hgk.check(
-        L.hgk_csr_build(_hgk.ptr(key), E, num_rows, _hgk.ptr(rowptr), _hgk.ptr(perm),
-                        _hgk.ptr(ws), ws_bytes, _hgk.stream_ptr()),
-        "hgk_csr_build",
-    )
+    # key read twice, slot + tmp written and read, perm written; counters + rowptr per row
+    _hgk.call("hgk_csr_build", _hgk.ptr(key), E, num_rows, _hgk.ptr(rowptr), _hgk.ptr(perm),
+              _hgk.ptr(ws), ws_bytes, cost=(E * 28 + num_rows * 12, 0))
     return rowptr, perm[:E]
 
 

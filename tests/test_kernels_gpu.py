@@ -253,7 +253,7 @@ def test_radius_graph_pbc_vs_reference_golden(ops, golden, case):
     ref_S = np.rint(ref_shift @ np.linalg.inv(c["cell"].numpy().astype(np.float64))).astype(np.int64)
     rs, rd, rS = _canon(c["edge_index"][0].numpy(), c["edge_index"][1].numpy(), ref_S)
     assert np.array_equal(src, rs) and np.array_equal(dst, rd) and np.array_equal(S, rS)
-    assert torch.allclose(g["edge_shifts"].cpu(), torch.from_numpy(S).float() @ c["cell"], atol=1e-5)
+    assert torch.allclose(g["edge_shifts"].cpu(), g["shift_int"].cpu().float() @ c["cell"], atol=1e-5)
 
 
 def _random_cells(gen, B):
@@ -312,7 +312,17 @@ def test_radius_graph_fesi_full_size_properties(ops):
     g = ops["ops"].radius_graph(pos.to(DEV), ptr, 5.0, 64, False, cell=cell, pbc=pbc)
     src, dst = g["src"].long(), g["dst"].long()
     deg = torch.bincount(dst, minlength=pos.size(0))
-    assert int(deg.min()) == 58 and int(deg.max()) == 58           # shells 8+6+12+24+8
+    # BCC shells 8+6+12+24+8 = 58 inside 5 A; the 0.05 A jitter pushes a few 5th-shell pairs (4.85 A) out
+    assert int(deg.max()) <= 58 and int(deg.min()) >= 48 and float(deg.float().mean()) > 56.5
+    # completeness: brute force over the 27 images in fp64 for the first crystal
+    p64 = pos[:1024].double().to(DEV)
+    shifts = torch.stack(torch.meshgrid(*[torch.arange(-1, 2)] * 3, indexing="ij"), -1).reshape(-1, 3).double().to(DEV) * (a * n)
+    D = (p64[None, :, None, :] - p64[:, None, None, :]) + shifts[None, None, :, :]     # [i, j, S, 3]
+    dist = torch.sqrt(D[..., 0] * D[..., 0] + D[..., 1] * D[..., 1] + D[..., 2] * D[..., 2])
+    hit = dist < 5.0
+    hit[torch.arange(1024), torch.arange(1024), 13] = False                            # i == j, S == 0
+    assert int(hit.sum()) == int((dst < 1024).sum())
+    assert torch.equal(hit.sum(dim=(0, 2)).to(torch.int64), deg[:1024])
     assert torch.equal(dst, torch.sort(dst).values)                # grouped by destination
     assert bool(((src // 1024) == (dst // 1024)).all())            # never crosses graphs
     vec = pos.to(DEV)[dst] - pos.to(DEV)[src] + g["edge_shifts"]
