@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--graphs-per-gpu", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
 
@@ -164,3 +165,291 @@ def to_data(batch, device, data_cls, non_blocking=False):
     fields = {k: batch[k].to(device, non_blocking=non_blocking) for k in TENSOR_FIELDS if k in batch}
     fields["num_graphs"] = batch["num_graphs"]
     return data_cls(**fields)
+
+
+# ------------------------------------------------------------------- the B200 arm ---
+ROOFLINE_KIND = {  # which roof bounds each entry point ("kernels")
+    "hgk_attn_varlen_fwd": "tensor", "hgk_attn_varlen_bwd": "tensor",
+}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            p = json.load(fh)
+        return {"hbm_gbs": p["hbm_gbs"], "tflops": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops": 1590.0, "source": "fallback"}
+
+
+def kernel_table(summary, steps, peaks):
+    rows = []
+    for name, s in summary.items():
+        if s["calls"] == 0 or s["ms"] <= 0:
+            continue
+        sec = s["ms"] * 1e-3
+        kind = ROOFLINE_KIND.get(name, "hbm")
+        row = {"entry": name, "calls_per_step": s["calls"] / steps, "ms_per_step": s["ms"] / steps,
+               "bound": kind, "gbs": s["bytes"] / sec / 1e9, "tflops": s["flops"] / sec / 1e12}
+        if kind == "hbm":
+            row.update(achieved=row["gbs"], peak=peaks["hbm_gbs"], unit="GB/s")
+        else:
+            row.update(achieved=row["tflops"], peak=peaks["tflops"], unit="TFLOP/s")
+        row["frac"] = row["achieved"] / row["peak"]
+        row["bytes_per_launch"] = s["bytes"] / s["calls"]
+        rows.append(row)
+    rows.sort(key=lambda r: -r["ms_per_step"])
+    return rows
+
+
+def run_b200(args):
+    import __graft_entry__
+    from hydragnn import _hgk
+    from hydragnn.graph import Data
+    from hydragnn.models import create_model
+    from hydragnn.train import train_step
+    from hydragnn.utils import synthetic as syn
+    from hydragnn.utils.distributed import get_distributed_model, setup_ddp
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    world, rank = setup_ddp()
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    torch.backends.cuda.matmul.allow_tf32 = False      # fp32 parity with the reference (rel 1e-5)
+    torch.backends.cudnn.allow_tf32 = False
+    if rank == 0:
+        __graft_entry__.build()
+    if world > 1:
+        dist.barrier()
+    _hgk.lib()
+
+    spec = syn.WORKLOADS[args.workload]
+    per_gpu = args.graphs_per_gpu or spec["graphs_per_gpu"]
+    graphs = syn.sample_graphs(args.workload, per_gpu, rank=rank)
+    host = build_batch_gpu(args.workload, graphs, device)
+    pinned = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in host.items()}
+    forces = spec["forces"]
+
+    model = create_model(**spec["arch"])
+    model = get_distributed_model(model)
+    if args.gps_segments == "graph":
+        for m in model.modules():
+            if m.__class__.__name__ == "GPSConv":
+                m.segments = "graph"
+    optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3)
+    model.train()
+
+    resident = to_data(host, device, Data)
+    torch.cuda.synchronize()
+
+    def fresh(data):
+        """New batch object around the resident tensors: the CSR / topology caches hang off the
+        tensor objects, so every step rebuilds them as it would for a new mini-batch."""
+        out = Data(**{k: (v.detach().clone() if k in ("edge_index", "pos") else v)
+                      for k, v in data.__dict__.items()})
+        return out
+
+    def step_resident():
+        return train_step(model, optimizer, fresh(resident), compute_grad_energy=forces)[0]
+
+    def step_e2e():
+        data = to_data(pinned, device, Data, non_blocking=True)
+        loss = train_step(model, optimizer, data, compute_grad_energy=forces)[0]
+        return float(loss)          # device -> host read of the step's result
+
+    for _ in range(args.warmup):
+        step_resident()
+    torch.cuda.synchronize()
+
+    # per-step working set: the [E, F] edge tensors (filters, messages, their gradients) dominate
+    n_edges = int(host["edge_index"].size(1)) if "edge_index" in host else 0
+    working_set = batch_bytes(host) + 6 * n_edges * spec["arch"]["hidden_dim"] * 4
+    flush = None
+    if working_set < 2 * L2_BYTES:
+        flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.float32, device=device)
+
+    _hgk.stats.reset()
+    _hgk.stats.timing = not args.no_kernel_timing
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    stops = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        for i in range(args.steps):
+            if flush is not None:
+                flush.fill_(float(i))        # evict L2 between timed steps (not timed)
+            starts[i].record()
+            loss = step_resident()
+            stops[i].record()
+        torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    _hgk.stats.timing = False
+    if flush is None:
+        total_ms = starts[0].elapsed_time(stops[-1])      # one bracket around exactly K steps
+    else:
+        total_ms = sum(a.elapsed_time(b) for a, b in zip(starts, stops))
+    launches = _hgk.stats.launches()
+    summary = _hgk.stats.summary()
+    t = torch.tensor([total_ms], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    final_loss = float(loss)
+
+    # end to end: pinned host batch -> device, step, loss back to the host, every step
+    e2e_steps = 0 if args.no_e2e else args.steps
+    for _ in range(0 if args.no_e2e else 2):
+        step_e2e()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(e2e_steps):
+        step_e2e()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+
+    peaks = measured_peaks()
+    table = kernel_table(summary, args.steps, peaks)
+    graphs_total = per_gpu * world
+    result = {
+        "metric": "train graphs/sec", "value": graphs_total * args.steps / (total_ms * 1e-3),
+        "unit": "graphs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "graphs_per_gpu": per_gpu, "global_batch": graphs_total,
+                   "nodes_per_gpu": int(host["pos"].size(0)),
+                   "edges_per_gpu": int(host["edge_index"].size(1)) if "edge_index" in host else None,
+                   "gps_segments": args.gps_segments if spec["arch"]["global_attn_engine"] else None,
+                   "parallelism": f"dp{world}", "optimizer": "AdamW", "tf32": False,
+                   "l2": ("flushed between steps" if flush is not None
+                          else f"per-step working set ~{working_set / 1e9:.1f} GB of [E,F] edge tensors exceeds the 126 MB L2")},
+        "e2e": {"value": (graphs_total * e2e_steps / (e2e_ms * 1e-3)) if e2e_steps else None, "unit": "graphs/s",
+                "h2d_bytes_per_step": batch_bytes(host), "d2h_bytes_per_step": 4},
+        "gpu_launches": launches,
+        "clocks": clocks.summary(),
+        "final_loss": final_loss,
+    }
+    if table:
+        top = table[0]
+        result["roofline"] = {"kernel": top["entry"], "bound": top["bound"], "achieved": top["achieved"],
+                              "peak": top["peak"], "unit": top["unit"], "frac": top["frac"],
+                              "peak_source": peaks["source"], "traffic": None,
+                              "bytes_per_launch": top["bytes_per_launch"]}
+        result["kernels"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()
+                              if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs", "tflops", "frac")}
+                             for r in table]
+        result["hgk_ms_per_step"] = sum(r["ms_per_step"] for r in table)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        state = {k: v.detach().cpu() for k, v in model.module.state_dict().items()}
+        result["cpu_baseline"] = cpu_baseline(args, spec, host, state, args.cpu_seconds, per_gpu)
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# -------------------------------------------------------------- the CPU (oracle) arm ---
+def oracle_step_fn(spec, host, state=None):
+    """The reference's training step restated on CPU (oracle/hydragnn_ref.py) on `host`."""
+    from oracle import hydragnn_ref as ora
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as mg
+
+    torch.set_num_threads(os.cpu_count())
+    model = ora.create_model(**spec["arch"])
+    if state is not None:
+        model.load_state_dict(state, strict=True)
+    model.train()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    forces = spec["forces"]
+
+    def step():
+        data = mg.Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in host.items()})
+        opt.zero_grad()
+        if forces:
+            data.pos.requires_grad_(True)
+            pred = model(data)
+            loss = model.energy_force_loss(pred, data)[0]
+        else:
+            pred = model(data)
+            loss = model.loss(pred, data.y, [torch.arange(data.y.shape[0])])[0]
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+
+    return step
+
+
+def cpu_baseline(args, spec, host, state, budget_s, graphs):
+    step = oracle_step_fn(spec, host, state)
+    t0 = time.perf_counter()
+    first_loss = step()                       # warm-up (allocations, thread pools)
+    warm = time.perf_counter() - t0
+    n, t0 = 0, time.perf_counter()
+    while n == 0 or (time.perf_counter() - t0 < budget_s and n < args.steps):
+        step()
+        n += 1
+    dt = time.perf_counter() - t0
+    return {"value": graphs * n / dt, "unit": "graphs/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{n} step(s) of the same {graphs}-graph batch after 1 warm-up step ({warm:.1f} s); "
+                      f"oracle/hydragnn_ref.py, torch CPU fp32, {os.cpu_count()} threads",
+            "first_step_loss": first_loss}
+
+
+def run_reference(args):
+    """CPU restatement of the reference on the host cores; each step a bounded sample."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    from hydragnn.utils import synthetic as syn
+
+    spec = syn.WORKLOADS[args.workload]
+    per_gpu = args.graphs_per_gpu or spec["graphs_per_gpu"]
+    sample_graphs = per_gpu
+    if args.workload == "schnet_gps_fesi1024" and not args.graphs_per_gpu:
+        sample_graphs = 2          # bounded sample: 2 of the 8 crystals per step (whole-batch attention)
+    graphs = syn.sample_graphs(args.workload, sample_graphs, rank=0)
+    host = build_batch_cpu(args.workload, graphs)
+    step = oracle_step_fn(spec, host)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        loss = step()
+    dt = time.perf_counter() - t0
+    value = sample_graphs * args.steps / dt
+    sample = (f"{sample_graphs} of {per_gpu} graphs per step, {args.steps} steps + {args.warmup} warm-up; "
+              f"oracle/hydragnn_ref.py on torch CPU fp32, {os.cpu_count()} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": "train graphs/sec", "value": value, "unit": "graphs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "graphs_per_step": sample_graphs, "parallelism": "cpu"},
+        "cpu_baseline": {"value": value, "unit": "graphs/s", "cores": os.cpu_count(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "graphs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "final_loss": loss,
+    }))
+
+
+if __name__ == "__main__":
+    cli = parse_args()
+    if cli.impl == "reference":
+        run_reference(cli)
+    else:
+        run_b200(cli)

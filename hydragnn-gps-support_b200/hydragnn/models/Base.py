@@ -268,13 +268,34 @@ class Base(Module):
         return total / count
 
     def _run_node_conv_head(self, chain, x, equiv, conv_args):
+        conv_args = {k: v for k, v in conv_args.items() if k != "cu_seqlens"}
         for conv, bn in zip(chain[0::2], chain[1::2]):
             x, equiv = conv(inv_node_feat=x, equiv_node_feat=equiv, **conv_args)
             x = self.activation_function(bn(x))
         return x
 
+    # "batch": all nodes of the mini-batch attend to each other, which is what the reference
+    # computes (its GPSConv never receives graph_batch); "graph": per-graph segments.
+    gps_segments = "batch"
+
+    def _attention_segments(self, data, num_nodes, device):
+        """cu_seqlens for the GPS layers, built once per forward (with the host-side sum of
+        squared segment lengths attached for the kernel's flop accounting -- no device sync)."""
+        if self.gps_segments == "graph" and getattr(data, "ptr", None) is not None:
+            cu = data.ptr.to(device=device, dtype=torch.int32)
+            sum_sq = getattr(data, "sum_sq_nodes", None)
+        else:
+            cu = torch.tensor([0, num_nodes], dtype=torch.int32, device=device)
+            sum_sq = num_nodes * num_nodes
+        if sum_sq is not None:
+            cu._hgk_sum_sq = int(sum_sq)
+        return cu
+
     def forward(self, data):
         inv_node_feat, equiv_node_feat, conv_args = self._embedding(data)
+        if self.use_global_attn:
+            conv_args["cu_seqlens"] = self._attention_segments(
+                data, inv_node_feat.size(0), inv_node_feat.device)
         for conv, feat_layer in zip(self.graph_convs, self.feature_layers):
             if self.conv_checkpointing:
                 from torch.utils.checkpoint import checkpoint

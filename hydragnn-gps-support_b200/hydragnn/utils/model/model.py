@@ -1,5 +1,8 @@
 """Selectors and segment helpers with the reference's names
 (hydragnn/utils/model/model.py:29-62, 152-187, 279-286)."""
+import os
+from collections import OrderedDict
+
 import torch
 
 from ...graph import topo_of
@@ -59,3 +62,97 @@ def update_multibranch_heads(output_heads):
         else:
             raise ValueError("Unknown output_heads config!")
     return updated
+
+
+# ---------------------------------------------------------------- checkpoints ---
+def _checkpoint_file(name, path, epoch=None):
+    stem = name if epoch is None else f"{name}_epoch_{epoch}"
+    return os.path.join(path, name, stem + ".pk")
+
+
+def save_model(model, optimizer, name, path="./logs/", use_deepspeed=False):
+    """Rank 0 writes {"model_state_dict", "optimizer_state_dict"} to ./logs/<name>/<name>.pk
+    (the reference's file layout, utils/model/model.py:63-106; HYDRAGNN_EPOCH adds a per-epoch
+    file plus a `<name>.pk` symlink).  Keys carry the `module.` prefix of a wrapped model."""
+    from ..distributed import get_comm_size_and_rank
+
+    if get_comm_size_and_rank()[1] != 0:
+        return
+    if hasattr(optimizer, "consolidate_state_dict"):
+        optimizer.consolidate_state_dict()
+    epoch = os.getenv("HYDRAGNN_EPOCH")
+    target = _checkpoint_file(name, path, epoch)
+    os.makedirs(os.path.dirname(target), exist_ok=True)
+    state = model.state_dict()
+    if not next(iter(state), "module.").startswith("module."):
+        state = OrderedDict(("module." + k, v) for k, v in state.items())
+    torch.save({"model_state_dict": state, "optimizer_state_dict": optimizer.state_dict()}, target)
+    if epoch is not None:
+        link = _checkpoint_file(name, path)
+        if os.path.lexists(link):
+            os.remove(link)
+        os.symlink(os.path.basename(target), link)
+
+
+def load_existing_model(model, model_name, path="./logs/", optimizer=None, use_deepspeed=False):
+    """Inverse of save_model; accepts checkpoints written with or without the `module.` prefix,
+    into a wrapped or a bare model."""
+    checkpoint = torch.load(_checkpoint_file(model_name, path), map_location="cpu", weights_only=False)
+    state = checkpoint["model_state_dict"]
+    wants_prefix = hasattr(model, "module")
+    has_prefix = next(iter(state), "").startswith("module.")
+    if wants_prefix and not has_prefix:
+        state = OrderedDict(("module." + k, v) for k, v in state.items())
+    elif has_prefix and not wants_prefix:
+        state = OrderedDict((k[len("module."):], v) for k, v in state.items())
+    model.load_state_dict(state)
+    if optimizer is not None and "optimizer_state_dict" in checkpoint:
+        optimizer.load_state_dict(checkpoint["optimizer_state_dict"])
+
+
+def load_existing_model_config(model, config, path="./logs/", optimizer=None, use_deepspeed=False):
+    if config.get("continue"):
+        load_existing_model(model, config["startfrom"], path, optimizer)
+
+
+def get_summary_writer(name, path="./logs/"):
+    from ..distributed import get_comm_size_and_rank
+
+    if get_comm_size_and_rank()[1] != 0:
+        return None
+    try:
+        from torch.utils.tensorboard import SummaryWriter
+    except Exception:
+        return None
+    return SummaryWriter(os.path.join(path, name))
+
+
+class EarlyStopping:
+    """Stop when the validation loss has not improved for `patience` epochs."""
+
+    def __init__(self, patience=10, min_delta=0.0):
+        self.patience, self.min_delta = patience, min_delta
+        self.val_loss_min, self.count = float("inf"), 0
+
+    def __call__(self, val_loss):
+        if val_loss > self.val_loss_min + self.min_delta:
+            self.count += 1
+            return self.count >= self.patience
+        self.val_loss_min, self.count = val_loss, 0
+        return False
+
+
+class Checkpoint:
+    """Save model + optimizer whenever the metric improves, after `warmup` epochs."""
+
+    def __init__(self, name, warmup=0, path="./logs/", use_deepspeed=False):
+        self.name, self.warmup, self.path = name, warmup, path
+        self.count, self.min_perf_metric, self.min_delta = 1, float("inf"), 0
+
+    def __call__(self, model, optimizer, perf_metric):
+        if perf_metric > self.min_perf_metric + self.min_delta or self.count < self.warmup:
+            self.count += 1
+            return False
+        self.min_perf_metric = perf_metric
+        save_model(model, optimizer, name=self.name, path=self.path)
+        return True

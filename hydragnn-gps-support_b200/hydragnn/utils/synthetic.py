@@ -109,7 +109,7 @@ WORKLOADS = {
     "schnet_qm9": dict(
         arch=_arch("SchNet", num_gaussians=50, num_filters=128, radius=5.0, max_neighbours=32),
         sample=_qm9_molecule, graphs_per_gpu=64, radius=5.0, max_neighbours=32, pbc=False,
-        edges="in_model", forces=False, seed=1236),
+        edges="radius", forces=False, seed=1236),
     # configs[2]
     "egnn_gps_zinc": dict(
         arch=_arch("EGNN", pe_dim=8, global_attn_engine="GPS", global_attn_type="multihead",
