@@ -15,6 +15,7 @@
 //   k_attn_bwd_kv : CTA owns a key/value tile, loops over query tiles -> dK,dV
 //   k_attn_bwd_q  : CTA owns a query tile, loops over key tiles      -> dQ
 #include "hgk_common.cuh"
+#include <stdlib.h>
 
 namespace hgk {
 
@@ -393,6 +394,17 @@ int set_smem(K kernel, size_t bytes) {
 
 }  // namespace hgk
 
+namespace hgk {
+int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, const float* k,
+                int64_t ldk, const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N,
+                int32_t H, int32_t D, float scale, cudaStream_t st);
+// HGK_ATTN_SIMT=1 forces the SIMT kernels (A/B runs); read once.
+static bool attn_force_simt() {
+  static const bool v = [] { const char* e = getenv("HGK_ATTN_SIMT"); return e && e[0] == '1'; }();
+  return v;
+}
+}  // namespace hgk
+
 using namespace hgk;
 
 static int attn_check(const char* what, const void* q, const void* k, const void* v,
@@ -413,6 +425,10 @@ extern "C" int hgk_attn_varlen_fwd(float* o, int64_t ldo, float* lse, const floa
   if (rc) return rc;
   if (N == 0) return HGK_OK;
   HGK_REQUIRE(o && lse, "attn_varlen_fwd: o/lse NULL");
+  if (!attn_force_simt()) {
+    rc = attn_fwd_tc(o, ldo, lse, q, ldq, k, ldk, v, ldv, cu_seqlens, S, N, H, D, scale, (cudaStream_t)stream);
+    if (rc <= 0) return rc;   // handled (or failed) on the tensor-core path; 1 = shape not covered
+  }
   const int Dp = (D + 3) / 4 * 4;
   AttnArgs a{q, ldq, k, ldk, v, ldv, cu_seqlens, (int32_t)S, N, H, D, Dp, scale};
   const size_t smem = sizeof(float) * (3 * kTile * (Dp + 4) + kTile * kPS);
