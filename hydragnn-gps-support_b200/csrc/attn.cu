@@ -398,6 +398,10 @@ namespace hgk {
 int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, const float* k,
                 int64_t ldk, const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N,
                 int32_t H, int32_t D, float scale, cudaStream_t st);
+int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float* dout, int64_t lddo,
+                const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
+                const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
+                int32_t D, float scale, cudaStream_t st);
 // HGK_ATTN_SIMT=1 forces the SIMT kernels (A/B runs); read once.
 static bool attn_force_simt() {
   static const bool v = [] { const char* e = getenv("HGK_ATTN_SIMT"); return e && e[0] == '1'; }();
@@ -457,6 +461,10 @@ extern "C" int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta
   AttnBwdArgs b{dout, lddo, lse, delta};
   cudaStream_t st = (cudaStream_t)stream;
   k_attn_delta<<<(unsigned)ceil_div(N * H, 256), 256, 0, st>>>(dout, lddo, o, ldo, delta, N, H, D);
+  if (!attn_force_simt()) {
+    rc = attn_bwd_tc(dq, dk, dv, delta, dout, lddo, lse, q, ldq, k, ldk, v, ldv, cu_seqlens, S, N, H, D, scale, st);
+    if (rc <= 0) return rc;
+  }
   dim3 grid((unsigned)(ceil_div(N, kTile) + S), (unsigned)H);
   const size_t smem_kv = sizeof(float) * (4 * kTile * (Dp + 4) + 2 * kTile * kPS);
   const size_t smem_q = sizeof(float) * (4 * kTile * (Dp + 4) + kTile * kPS);

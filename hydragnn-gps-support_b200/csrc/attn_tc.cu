@@ -251,6 +251,354 @@ int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N
   return check_launch("attn_varlen_fwd(tcgen05)");
 }
 
+
+// =============================================================================== backward ===
+// Two deterministic kernels (no float atomics), both recomputing the probabilities from lse:
+//   k_attn_bwd_q_tc  : CTA owns 128 queries, loops over 64-key tiles          -> dQ
+//   k_attn_bwd_kv_tc : CTA owns 128 keys (TMEM lane = key), loops over 64-query tiles -> dK, dV
+// With s = (q.k) scale log2(e)  (Q is staged pre-multiplied), lse2 = lse log2(e):
+//   P = 2^(s - lse2),  dP = dO V^T,  dS = P (dP - delta),  delta = rowsum(dO O)
+//   dQ = scale dS K,   dK = scale dS^T Q,   dV = P^T dO
+struct AttnTcBwdArgs {
+  const float* dout; int64_t lddo;
+  const float* lse; const float* delta;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads)
+k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dq) {
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  int32_t seg_beg, seg_end, row0;
+  if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
+  const int h = blockIdx.y;
+  const int tid = threadIdx.x, warp = tid >> 5;
+
+  float* Qhi = smem;             float* Qlo = Qhi + BM * D;
+  float* Ghi = Qlo + BM * D;     float* Glo = Ghi + BM * D;      // dO tile
+  float* Khi = Glo + BM * D;     float* Klo = Khi + BN * D;
+  float* Vhi = Klo + BN * D;     float* Vlo = Vhi + BN * D;
+  float* KThi = Vlo + BN * D;    float* KTlo = KThi + BN * D;    // K^T tile [D x BN]
+
+  constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;       // dS_hi -> S region, dS_lo -> dP region
+  if (warp == 0) tmem_alloc(&tmem_slot, 256);
+  if (tid == 0) mbar_init(&bar, 1);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+  constexpr float kLog2e = 1.4426950408889634f;
+  stage_rows<BM, D>(Qhi, Qlo, p.q + h * D, p.ldq, row0, seg_end, p.scale * kLog2e);
+  stage_rows<BM, D>(Ghi, Glo, b.dout + h * D, b.lddo, row0, seg_end, 1.f);
+  const int32_t row = row0 + tid;
+  const bool row_ok = row < seg_end;
+  const float lse2 = row_ok ? b.lse[(int64_t)row * p.H + h] * kLog2e : 0.f;
+  const float delta = row_ok ? b.delta[(int64_t)row * p.H + h] : 0.f;
+
+  constexpr uint32_t kLbo = 128;
+  constexpr uint32_t kSboD = (D / 4) * 128;            // tiles whose K dim is the feature dim
+  constexpr uint32_t kSboT = (BN / 4) * 128;           // transposed tiles (K dim = 64 keys)
+  constexpr uint32_t kIdescS = idesc_tf32(BM, BN);
+  constexpr uint32_t kIdescQ = idesc_tf32(BM, D);
+  uint32_t parity = 0;
+  bool first = true;
+
+  for (int32_t k0 = seg_beg; k0 < seg_end; k0 += BN) {
+    stage_rows<BN, D>(Khi, Klo, p.k + h * D, p.ldk, k0, seg_end, 1.f);
+    stage_rows<BN, D>(Vhi, Vlo, p.v + h * D, p.ldv, k0, seg_end, 1.f);
+    stage_transposed<BN, D>(KThi, KTlo, p.k + h * D, p.ldk, k0, seg_end);
+    fence_smem_to_async();
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      const uint32_t qh = smem_u32(Qhi), ql = smem_u32(Qlo), gh = smem_u32(Ghi), gl = smem_u32(Glo);
+      const uint32_t kh = smem_u32(Khi), kl = smem_u32(Klo), vh = smem_u32(Vhi), vl = smem_u32(Vlo);
+#pragma unroll
+      for (int j = 0; j < D / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        mma_tf32_ss(tmem + kColS, smem_desc(ql + adv, kLbo, kSboD), smem_desc(kh + adv, kLbo, kSboD), kIdescS, j > 0);
+        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboD), smem_desc(kl + adv, kLbo, kSboD), kIdescS, 1);
+        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboD), smem_desc(kh + adv, kLbo, kSboD), kIdescS, 1);
+      }
+#pragma unroll
+      for (int j = 0; j < D / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        mma_tf32_ss(tmem + kColDP, smem_desc(gl + adv, kLbo, kSboD), smem_desc(vh + adv, kLbo, kSboD), kIdescS, j > 0);
+        mma_tf32_ss(tmem + kColDP, smem_desc(gh + adv, kLbo, kSboD), smem_desc(vl + adv, kLbo, kSboD), kIdescS, 1);
+        mma_tf32_ss(tmem + kColDP, smem_desc(gh + adv, kLbo, kSboD), smem_desc(vh + adv, kLbo, kSboD), kIdescS, 1);
+      }
+      mma_commit(&bar);
+    }
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+
+    const int32_t nvalid = seg_end - k0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t sv[32], dv[32];
+      tmem_ld32(tmem + lane_base + kColS + 32 * half, sv);
+      tmem_ld32(tmem + lane_base + kColDP + 32 * half, dv);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float pj = exp2f(__uint_as_float(sv[j]) - lse2);
+        float ds = pj * (__uint_as_float(dv[j]) - delta);
+        if (j + 32 * half >= nvalid) ds = 0.f;
+        float hi, lo;
+        split_tf32(ds, hi, lo);
+        sv[j] = __float_as_uint(hi);
+        dv[j] = __float_as_uint(lo);
+      }
+      tmem_st32(tmem + lane_base + kColS + 32 * half, sv);
+      tmem_st32(tmem + lane_base + kColDP + 32 * half, dv);
+    }
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      const uint32_t th = smem_u32(KThi), tl = smem_u32(KTlo);
+#pragma unroll
+      for (int j = 0; j < BN / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        const uint32_t pc = j * 8;
+        mma_tf32_ts(tmem + kColDQ, tmem + kColDP + pc, smem_desc(th + adv, kLbo, kSboT), kIdescQ, !(first && j == 0));
+        mma_tf32_ts(tmem + kColDQ, tmem + kColS + pc, smem_desc(tl + adv, kLbo, kSboT), kIdescQ, 1);
+        mma_tf32_ts(tmem + kColDQ, tmem + kColS + pc, smem_desc(th + adv, kLbo, kSboT), kIdescQ, 1);
+      }
+      mma_commit(&bar);
+    }
+    first = false;
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+  }
+
+  // tcgen05.ld is warp-collective (.sync.aligned): every thread loads, valid rows store
+  float* drow = dq + ((int64_t)row * p.H + h) * D;
+#pragma unroll
+  for (int c0 = 0; c0 < D; c0 += 16) {
+    uint32_t t[16];
+    tmem_ld16(tmem + lane_base + kColDQ + c0, t);
+    tmem_ld_wait();
+    if (row_ok) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<float4*>(drow + c0 + j) =
+            make_float4(__uint_as_float(t[j]) * p.scale, __uint_as_float(t[j + 1]) * p.scale,
+                        __uint_as_float(t[j + 2]) * p.scale, __uint_as_float(t[j + 3]) * p.scale);
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+template <int D>
+__global__ void __launch_bounds__(kThreads)
+k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv) {
+  constexpr int BQ = 64;                                // queries per iteration
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ float lse2_s[BQ], delta_s[BQ];
+  int32_t seg_beg, seg_end, key0;
+  if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
+  const int h = blockIdx.y;
+  const int tid = threadIdx.x, warp = tid >> 5;
+
+  float* Khi = smem;             float* Klo = Khi + BM * D;
+  float* Vhi = Klo + BM * D;     float* Vlo = Vhi + BM * D;
+  float* Qhi = Vlo + BM * D;     float* Qlo = Qhi + BQ * D;      // rows = queries (B of S^T)
+  float* Ghi = Qlo + BQ * D;     float* Glo = Ghi + BQ * D;      // dO rows        (B of dP^T)
+  float* QThi = Glo + BQ * D;    float* QTlo = QThi + BQ * D;    // Q^T [D x BQ]   (B of dK)
+  float* GThi = QTlo + BQ * D;   float* GTlo = GThi + BQ * D;    // dO^T [D x BQ]  (B of dV)
+
+  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
+  constexpr uint32_t kCols = 512;
+  if (warp == 0) tmem_alloc(&tmem_slot, kCols);
+  if (tid == 0) mbar_init(&bar, 1);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+
+  constexpr float kLog2e = 1.4426950408889634f;
+  stage_rows<BM, D>(Khi, Klo, p.k + h * D, p.ldk, key0, seg_end, 1.f);
+  stage_rows<BM, D>(Vhi, Vlo, p.v + h * D, p.ldv, key0, seg_end, 1.f);
+
+  constexpr uint32_t kLbo = 128;
+  constexpr uint32_t kSboD = (D / 4) * 128;
+  constexpr uint32_t kSboT = (BQ / 4) * 128;
+  constexpr uint32_t kIdescS = idesc_tf32(BM, BQ);
+  constexpr uint32_t kIdescD = idesc_tf32(BM, D);
+  uint32_t parity = 0;
+  bool first = true;
+
+  for (int32_t q0 = seg_beg; q0 < seg_end; q0 += BQ) {
+    const float qmul = p.scale * kLog2e;
+    stage_rows<BQ, D>(Qhi, Qlo, p.q + h * D, p.ldq, q0, seg_end, qmul);
+    stage_rows<BQ, D>(Ghi, Glo, b.dout + h * D, b.lddo, q0, seg_end, 1.f);
+    // transposed copies (scaled like the row copy)
+    {
+      constexpr int CH = D / 4;
+      constexpr int SBO = (BQ / 4) * 32;
+      for (int idx = tid; idx < BQ * CH; idx += kThreads) {
+        const int r = idx / CH, c = idx - r * CH;
+        float4 xq = make_float4(0.f, 0.f, 0.f, 0.f), xg = xq;
+        if (q0 + r < seg_end) {
+          xq = __ldg(reinterpret_cast<const float4*>(p.q + h * D + (int64_t)(q0 + r) * p.ldq + 4 * c));
+          xg = __ldg(reinterpret_cast<const float4*>(b.dout + h * D + (int64_t)(q0 + r) * b.lddo + 4 * c));
+        }
+        const float qv[4] = {xq.x * qmul, xq.y * qmul, xq.z * qmul, xq.w * qmul};
+        const float gv[4] = {xg.x, xg.y, xg.z, xg.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int off = core_off(4 * c + i, r >> 2, SBO) + (r & 3);
+          float hi, lo;
+          split_tf32(qv[i], hi, lo); QThi[off] = hi; QTlo[off] = lo;
+          split_tf32(gv[i], hi, lo); GThi[off] = hi; GTlo[off] = lo;
+        }
+      }
+    }
+    if (tid < BQ) {
+      const int32_t qrow = q0 + tid;
+      const bool ok = qrow < seg_end;
+      lse2_s[tid] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
+      delta_s[tid] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
+    }
+    fence_smem_to_async();
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      const uint32_t kh = smem_u32(Khi), kl = smem_u32(Klo), vh = smem_u32(Vhi), vl = smem_u32(Vlo);
+      const uint32_t qh = smem_u32(Qhi), ql = smem_u32(Qlo), gh = smem_u32(Ghi), gl = smem_u32(Glo);
+#pragma unroll
+      for (int j = 0; j < D / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        mma_tf32_ss(tmem + kColST, smem_desc(kl + adv, kLbo, kSboD), smem_desc(qh + adv, kLbo, kSboD), kIdescS, j > 0);
+        mma_tf32_ss(tmem + kColST, smem_desc(kh + adv, kLbo, kSboD), smem_desc(ql + adv, kLbo, kSboD), kIdescS, 1);
+        mma_tf32_ss(tmem + kColST, smem_desc(kh + adv, kLbo, kSboD), smem_desc(qh + adv, kLbo, kSboD), kIdescS, 1);
+      }
+#pragma unroll
+      for (int j = 0; j < D / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        mma_tf32_ss(tmem + kColDPT, smem_desc(vl + adv, kLbo, kSboD), smem_desc(gh + adv, kLbo, kSboD), kIdescS, j > 0);
+        mma_tf32_ss(tmem + kColDPT, smem_desc(vh + adv, kLbo, kSboD), smem_desc(gl + adv, kLbo, kSboD), kIdescS, 1);
+        mma_tf32_ss(tmem + kColDPT, smem_desc(vh + adv, kLbo, kSboD), smem_desc(gh + adv, kLbo, kSboD), kIdescS, 1);
+      }
+      mma_commit(&bar);
+    }
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+
+    const int32_t nvalid = seg_end - q0;                 // query columns [0, nvalid) exist
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t sv[32], dp[32], plo[32], dslo[32];
+      tmem_ld32(tmem + lane_base + kColST + 32 * half, sv);
+      tmem_ld32(tmem + lane_base + kColDPT + 32 * half, dp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = j + 32 * half;
+        float pj = exp2f(__uint_as_float(sv[j]) - lse2_s[col]);
+        if (col >= nvalid) pj = 0.f;
+        const float ds = pj * (__uint_as_float(dp[j]) - delta_s[col]);
+        float hi, lo;
+        split_tf32(pj, hi, lo);
+        sv[j] = __float_as_uint(hi); plo[j] = __float_as_uint(lo);
+        split_tf32(ds, hi, lo);
+        dp[j] = __float_as_uint(hi); dslo[j] = __float_as_uint(lo);
+      }
+      tmem_st32(tmem + lane_base + kColST + 32 * half, sv);
+      tmem_st32(tmem + lane_base + kColPlo + 32 * half, plo);
+      tmem_st32(tmem + lane_base + kColDPT + 32 * half, dp);
+      tmem_st32(tmem + lane_base + kColDSlo + 32 * half, dslo);
+    }
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      const uint32_t qth = smem_u32(QThi), qtl = smem_u32(QTlo), gth = smem_u32(GThi), gtl = smem_u32(GTlo);
+#pragma unroll
+      for (int j = 0; j < BQ / 8; ++j) {
+        const uint32_t adv = j * 2 * kLbo;
+        const uint32_t pc = j * 8;
+        const uint32_t acc0 = !(first && j == 0);
+        mma_tf32_ts(tmem + kColDV, tmem + kColPlo + pc, smem_desc(gth + adv, kLbo, kSboT), kIdescD, acc0);
+        mma_tf32_ts(tmem + kColDV, tmem + kColST + pc, smem_desc(gtl + adv, kLbo, kSboT), kIdescD, 1);
+        mma_tf32_ts(tmem + kColDV, tmem + kColST + pc, smem_desc(gth + adv, kLbo, kSboT), kIdescD, 1);
+        mma_tf32_ts(tmem + kColDK, tmem + kColDSlo + pc, smem_desc(qth + adv, kLbo, kSboT), kIdescD, acc0);
+        mma_tf32_ts(tmem + kColDK, tmem + kColDPT + pc, smem_desc(qtl + adv, kLbo, kSboT), kIdescD, 1);
+        mma_tf32_ts(tmem + kColDK, tmem + kColDPT + pc, smem_desc(qth + adv, kLbo, kSboT), kIdescD, 1);
+      }
+      mma_commit(&bar);
+    }
+    first = false;
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+  }
+
+  const int32_t krow = key0 + tid;
+  const bool ok = krow < seg_end;
+  constexpr float kLn2 = 0.6931471805599453f;
+#pragma unroll
+  for (int c0 = 0; c0 < D; c0 += 16) {
+    uint32_t tv[16], tk[16];
+    tmem_ld16(tmem + lane_base + kColDV + c0, tv);
+    tmem_ld16(tmem + lane_base + kColDK + c0, tk);
+    tmem_ld_wait();
+    if (ok) {
+      float* vrow = dv + ((int64_t)krow * p.H + h) * D + c0;
+      float* krow_p = dk + ((int64_t)krow * p.H + h) * D + c0;
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) {
+        *reinterpret_cast<float4*>(vrow + j) = make_float4(__uint_as_float(tv[j]), __uint_as_float(tv[j + 1]),
+                                                           __uint_as_float(tv[j + 2]), __uint_as_float(tv[j + 3]));
+        *reinterpret_cast<float4*>(krow_p + j) =
+            make_float4(__uint_as_float(tk[j]) * kLn2, __uint_as_float(tk[j + 1]) * kLn2,
+                        __uint_as_float(tk[j + 2]) * kLn2, __uint_as_float(tk[j + 3]) * kLn2);
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, kCols);
+}
+
+template <typename K>
+int opt_in_smem(K kernel, size_t bytes, const char* what) {
+  cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "%s: smem opt-in (%zu B) failed: %s", what, bytes, cudaGetErrorString(err));
+  return HGK_OK;
+}
+
+template <int D>
+int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk, float* dv, int64_t N,
+               cudaStream_t st) {
+  dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
+  const size_t smem_kv = sizeof(float) * (4 * BM * D + 8 * 64 * D);
+  int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
+  if (rc) return rc;
+  k_attn_bwd_kv_tc<D><<<grid, kThreads, smem_kv, st>>>(a, b, dk, dv);
+  const size_t smem_q = sizeof(float) * (4 * BM * D + 6 * BN * D);
+  rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
+  if (rc) return rc;
+  k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
+  return check_launch("attn_varlen_bwd(tcgen05)");
+}
+
 }  // namespace tc
 
 // Called by hgk_attn_varlen_fwd.  Returns 1 if this shape is not handled here (caller falls back
@@ -267,6 +615,22 @@ int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, 
     case 32: return tc::launch_fwd<32>(a, o, ldo, lse, N, st);
     default: return tc::launch_fwd<64>(a, o, ldo, lse, N, st);
   }
+}
+
+// Called by hgk_attn_varlen_bwd after delta = rowsum(dO * O) has been enqueued.  Same return
+// convention as attn_fwd_tc.  dq, dk, dv are contiguous [N, H, D].
+int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float* dout, int64_t lddo,
+                const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
+                const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
+                int32_t D, float scale, cudaStream_t st) {
+  auto ok16 = [](const void* ptr, int64_t ld) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ld % 4 == 0; };
+  if (!(D == 16 || D == 32)) return 1;     // D = 64 would need 224+ KB of shared memory in the kv kernel
+  if (!ok16(q, ldq) || !ok16(k, ldk) || !ok16(v, ldv) || !ok16(dout, lddo) || !ok16(dq, 4) || !ok16(dk, 4) || !ok16(dv, 4))
+    return 1;
+  AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
+  tc::AttnTcBwdArgs b{dout, lddo, lse, delta};
+  if (D == 16) return tc::launch_bwd<16>(a, b, dq, dk, dv, N, st);
+  return tc::launch_bwd<32>(a, b, dq, dk, dv, N, st);
 }
 
 }  // namespace hgk

@@ -40,7 +40,9 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= static_cast<uint64_t>(1) << 46;
   return d;
 }
-// 32-bit instruction descriptor: tf32 x tf32 -> f32, both operands K-major, dense.
+// 32-bit instruction descriptor: tf32 x tf32 -> f32, dense, A and B K-major.
+// (An MN-major B view of a K-major staged tile was tried for the transposed operands and did not
+// reproduce the reference with SWIZZLE_NONE; transposed operands are staged explicitly instead.)
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
   return (1u << 4)            // D format  = F32
        | (2u << 7)            // A format  = TF32
@@ -79,11 +81,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
   return ok != 0;
 }
-// Bounded spin: a barrier that never completes (a descriptor or phase bug) traps the kernel
-// instead of hanging the GPU.
+// Bounded wait: a barrier that never completes (a descriptor or phase bug) traps the kernel after
+// ~2 s of wall time instead of hanging the GPU.
+__device__ __forceinline__ uint64_t global_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-    if (spins > (1u << 26)) __trap();
+  if (mbar_try_wait(bar, parity)) return;
+  const uint64_t t0 = global_ns();
+  while (!mbar_try_wait(bar, parity)) {
+    if (global_ns() - t0 > 2000000000ull) __trap();
   }
 }
 
