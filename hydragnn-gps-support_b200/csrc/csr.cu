@@ -13,6 +13,8 @@
 // stable order a sequential CPU loop over e = 0..E-1 would produce.
 #include "hgk_common.cuh"
 
+#include <mutex>
+
 namespace hgk {
 
 thread_local char g_err[512] = {0};
@@ -176,4 +178,69 @@ extern "C" int hgk_csr_build(const int32_t* key, int64_t E, int64_t N,
                 (long long)workspace_bytes,
                 (long long)hgk_csr_build_workspace_bytes(E, N));
   return csr_build_impl(key, E, N, rowptr, perm, workspace, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// hgk_csr_build_static: the same grouping for callers that may not allocate device memory.
+//
+// Who that is: a caller that has handed the whole GPU to another allocator (a serving process that
+// pre-reserves all device memory for its own pool, so a plain cudaMalloc would fail), or one that
+// runs in a latency-critical enqueue callback where cudaMalloc / cudaFree are off limits because
+// they synchronise the device.  Such a caller cannot provide the workspace hgk_csr_build asks for,
+// so the workspace lives here, in a fixed array that is part of the library image: every GPU that
+// loads libhgk.so carries these bytes until the process exits.  The price is a size limit
+// (HGK_CSR_STATIC_MAX_EDGES / _MAX_ROWS) and no concurrency: all calls on a device share the one
+// array, so two calls whose kernels can overlap on the GPU (different streams, different host
+// threads) corrupt each other.  Serialise them.
+namespace hgk {
+
+constexpr int64_t kStaticScratchBytes =
+    ((4 * (int64_t)HGK_CSR_STATIC_MAX_ROWS + 255) / 256) * 256 +
+    2 * (((4 * (int64_t)HGK_CSR_STATIC_MAX_EDGES + 255) / 256) * 256) + 256;
+
+static __device__ __align__(256) unsigned char g_csr_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_csr_static_addr[kMaxDevices] = {nullptr};
+static std::mutex g_csr_static_mutex;
+
+// In host code `g_csr_static_scratch` is only a handle for the runtime, not an address a kernel can
+// use: the device address has to be asked for, once per device, with that device current.
+static int csr_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "csr_build_static: cudaGetDevice: %s", cudaGetErrorString(err));
+  if (dev < 0 || dev >= kMaxDevices) return fail(HGK_ERR_UNSUPPORTED, "csr_build_static: device %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_csr_static_mutex);
+  if (g_csr_static_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    err = cudaGetSymbolAddress(&ptr, g_csr_static_scratch);
+    if (err != cudaSuccess || ptr == nullptr)
+      return fail(HGK_ERR_CUDA, "csr_build_static: cudaGetSymbolAddress: %s", cudaGetErrorString(err));
+    g_csr_static_addr[dev] = ptr;
+  }
+  *out = g_csr_static_addr[dev];
+  return HGK_OK;
+}
+
+}  // namespace hgk
+
+extern "C" int hgk_csr_build_static(const int32_t* key, int64_t E, int64_t N, int32_t* rowptr,
+                                    int32_t* perm, void* stream) {
+  HGK_REQUIRE(E >= 0 && N >= 0, "csr_build_static: negative size (E=%lld N=%lld)", (long long)E, (long long)N);
+  if (E > HGK_CSR_STATIC_MAX_EDGES || N > HGK_CSR_STATIC_MAX_ROWS)
+    return fail(HGK_ERR_UNSUPPORTED,
+                "csr_build_static: E=%lld N=%lld exceeds the built-in scratch (max %lld edges, %lld rows); "
+                "use hgk_csr_build with a caller-provided workspace",
+                (long long)E, (long long)N, (long long)HGK_CSR_STATIC_MAX_EDGES, (long long)HGK_CSR_STATIC_MAX_ROWS);
+  HGK_REQUIRE(rowptr != nullptr, "csr_build_static: rowptr is NULL");
+  HGK_REQUIRE(E == 0 || (key && perm), "csr_build_static: key/perm is NULL with E>0");
+  HGK_REQUIRE(E == 0 || N > 0, "csr_build_static: E>0 needs N>0");
+  void* scratch = nullptr;
+  int rc = csr_static_scratch(&scratch);
+  if (rc) return rc;
+  // The array keeps whatever the previous call left in it.  The only part that must start at zero
+  // is the per-row counter block, which csr_build_impl clears on `stream` before the histogram;
+  // slot[] and tmp[] are fully rewritten for the E edges of this call before they are read.
+  return csr_build_impl(key, E, N, rowptr, perm, scratch, (cudaStream_t)stream);
 }

@@ -60,6 +60,27 @@ int hgk_csr_build(const int32_t* key, int64_t E, int64_t N, int32_t* rowptr,
                   int32_t* perm, void* workspace, int64_t workspace_bytes,
                   void* stream);
 
+/* hgk_csr_build_static -- no counterpart in the reference.  Same output as
+ * hgk_csr_build, for callers that cannot allocate device memory and therefore
+ * cannot supply a workspace: a process whose GPU memory is entirely owned by
+ * another allocator (a raw cudaMalloc would fail), or an enqueue path in which
+ * cudaMalloc/cudaFree are forbidden because they synchronise the device.  The
+ * scratch is a fixed array inside libhgk.so (about 9.3 MB, resident on every
+ * GPU that loads the library until the process exits), which bounds the size:
+ * E <= HGK_CSR_STATIC_MAX_EDGES and N <= HGK_CSR_STATIC_MAX_ROWS, larger
+ * inputs return HGK_ERR_UNSUPPORTED.  Neither this call nor anything it
+ * invokes allocates or frees memory.
+ *   - The first call on each device looks up the array's device address (with
+ *     that device current); make that first call outside any stream capture.
+ *   - All calls on a device share the one array: calls that can overlap on the
+ *     GPU (different streams or host threads) race.  Serialise them.
+ *   - The array keeps the previous call's contents; the call itself clears the
+ *     part that has to start at zero, on `stream`. */
+#define HGK_CSR_STATIC_MAX_EDGES 1048576
+#define HGK_CSR_STATIC_MAX_ROWS 262144
+int hgk_csr_build_static(const int32_t* key, int64_t E, int64_t N,
+                         int32_t* rowptr, int32_t* perm, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * The contraction family.  All four gather/scatter convolutions of the
  * reference (SchNet CFConv SCFStack.py:285-293, E_GCL EGCLStack.py:240-271,
