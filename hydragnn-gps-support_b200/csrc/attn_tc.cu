@@ -52,48 +52,72 @@ __device__ __forceinline__ bool locate_tile128(const int32_t* cu, int32_t S, int
   return false;
 }
 
-// rows [row0, row0+ROWS) x D of a [*, ld] matrix -> hi / lo K-major core-matrix tiles
-// (row = MN index, feature = K index), each value multiplied by `mul`; rows >= row_end are zero.
+// ---- tile staging: global -> registers (prefetchable) -> shared memory --------------------------
+// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks; thread t owns chunks t, t+128, ...
+// chunk idx -> row r = idx / (D/4), 16-byte column c = idx % (D/4).
 template <int ROWS, int D>
-__device__ __forceinline__ void stage_rows(float* hi, float* lo, const float* src, int64_t ld,
-                                           int32_t row0, int32_t row_end, float mul) {
-  constexpr int CH = D / 4;                 // 16-byte chunks per row
-  constexpr int SBO = CH * 32;              // floats per 8-row group
-  for (int idx = threadIdx.x; idx < ROWS * CH; idx += kThreads) {
-    const int r = idx / CH, c = idx - r * CH;
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < row_end) x = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * ld + 4 * c));
-    float4 h, l;
-    split_tf32(x.x * mul, h.x, l.x); split_tf32(x.y * mul, h.y, l.y);
-    split_tf32(x.z * mul, h.z, l.z); split_tf32(x.w * mul, h.w, l.w);
-    const int off = core_off(r, c, SBO);
-    *reinterpret_cast<float4*>(hi + off) = h;
-    *reinterpret_cast<float4*>(lo + off) = l;
-  }
-}
+struct Tile {
+  static constexpr int CH = D / 4;
+  static constexpr int PER = ROWS * CH / kThreads;
+  static_assert(ROWS * CH % kThreads == 0, "tile must divide evenly over the CTA");
+  float4 v[PER];
 
-// rows [row0, row0+COLS) x D of a [*, ld] matrix -> TRANSPOSED hi / lo tiles: MN index = feature
-// (D rows), K index = source row (COLS columns).  Used for the B operand of P V (reduction over keys).
-template <int COLS, int D>
-__device__ __forceinline__ void stage_transposed(float* hi, float* lo, const float* src, int64_t ld,
-                                                 int32_t row0, int32_t row_end) {
-  constexpr int CH = D / 4;
-  constexpr int SBO = (COLS / 4) * 32;      // floats per 8-feature group
-  for (int idx = threadIdx.x; idx < COLS * CH; idx += kThreads) {
-    const int r = idx / CH, c = idx - r * CH;     // r: source row (key), c: feature chunk
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < row_end) x = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * ld + 4 * c));
-    const float vals[4] = {x.x, x.y, x.z, x.w};
+  __device__ __forceinline__ void load(const float* src, int64_t ld, int32_t row0, int32_t row_end) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      float h, l;
-      split_tf32(vals[i], h, l);
-      const int off = core_off(4 * c + i, r >> 2, SBO) + (r & 3);
-      hi[off] = h;
-      lo[off] = l;
+    for (int it = 0; it < PER; ++it) {
+      const int idx = threadIdx.x + it * kThreads;
+      const int r = idx / CH, c = idx - r * CH;
+      v[it] = make_float4(0.f, 0.f, 0.f, 0.f);          // rows past the segment end are zero
+      if (row0 + r < row_end) v[it] = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * ld + 4 * c));
     }
   }
-}
+  // hi / lo K-major tiles with MN index = row, K index = feature
+  __device__ __forceinline__ void store_rows(float* hi, float* lo, float mul) const {
+    constexpr int SBO = CH * 32;
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      const int idx = threadIdx.x + it * kThreads;
+      const int r = idx / CH, c = idx - r * CH;
+      float4 h, l;
+      split_tf32(v[it].x * mul, h.x, l.x); split_tf32(v[it].y * mul, h.y, l.y);
+      split_tf32(v[it].z * mul, h.z, l.z); split_tf32(v[it].w * mul, h.w, l.w);
+      const int off = core_off(r, c, SBO);
+      *reinterpret_cast<float4*>(hi + off) = h;
+      *reinterpret_cast<float4*>(lo + off) = l;
+    }
+  }
+  // hi / lo K-major tiles of the TRANSPOSE: MN index = feature (D rows), K index = row (ROWS columns).
+  // The 4 lanes that hold the same 16-byte column of 4 consecutive rows exchange their values with
+  // 4 shuffles (a 4x4 register transpose), after which every lane writes one 16-byte chunk.
+  __device__ __forceinline__ void store_transposed(float* hi, float* lo, float mul) const {
+    constexpr int SBO = (ROWS / 4) * 32;
+    const int lane = threadIdx.x & 31;
+    const int rr = (lane / CH) & 3;                    // my row inside its group of 4
+    const int base = lane - rr * CH;                   // lane of row 0 of the group, same column
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      const int idx = threadIdx.x + it * kThreads;
+      const int r = idx / CH, c = idx - r * CH;
+      const float x[4] = {v[it].x * mul, v[it].y * mul, v[it].z * mul, v[it].w * mul};
+      float w[4];
+#pragma unroll
+      for (int s = 0; s < 4; ++s) {
+        const int give = (rr - s) & 3;                 // the partner reading me at step s wants this feature
+        const float send = give == 0 ? x[0] : (give == 1 ? x[1] : (give == 2 ? x[2] : x[3]));
+        const int from = (rr + s) & 3;
+        const float got = __shfl_sync(0xffffffffu, send, base + from * CH);
+        if (from == 0) w[0] = got; else if (from == 1) w[1] = got; else if (from == 2) w[2] = got; else w[3] = got;
+      }
+      // w[j] = value of feature 4c + rr at row (r & ~3) + j
+      float4 h, l;
+      split_tf32(w[0], h.x, l.x); split_tf32(w[1], h.y, l.y);
+      split_tf32(w[2], h.z, l.z); split_tf32(w[3], h.w, l.w);
+      const int off = core_off(4 * c + rr, r >> 2, SBO);
+      *reinterpret_cast<float4*>(hi + off) = h;
+      *reinterpret_cast<float4*>(lo + off) = l;
+    }
+  }
+};
 
 template <int D>
 __global__ void __launch_bounds__(kThreads)
@@ -123,7 +147,14 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
 
   constexpr float kLog2e = 1.4426950408889634f;
-  stage_rows<BM, D>(Qhi, Qlo, p.q + h * D, p.ldq, row0, seg_end, p.scale * kLog2e);
+  {
+    Tile<BM, D> tq;
+    tq.load(p.q + h * D, p.ldq, row0, seg_end);
+    tq.store_rows(Qhi, Qlo, p.scale * kLog2e);
+  }
+  Tile<BN, D> tk, tv;                                  // next key / value tile, prefetched in registers
+  tk.load(p.k + h * D, p.ldk, seg_beg, seg_end);
+  tv.load(p.v + h * D, p.ldv, seg_beg, seg_end);
 
   constexpr uint32_t kLbo = 128;                       // bytes between K chunks
   constexpr uint32_t kSboQK = (D / 4) * 128;           // bytes between 8-row groups (Q, K tiles)
@@ -138,8 +169,8 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
   uint32_t parity = 0;
 
   for (int32_t k0 = seg_beg; k0 < seg_end; k0 += BN) {
-    stage_rows<BN, D>(Khi, Klo, p.k + h * D, p.ldk, k0, seg_end, 1.f);
-    stage_transposed<BN, D>(Vhi, Vlo, p.v + h * D, p.ldv, k0, seg_end);
+    tk.store_rows(Khi, Klo, 1.f);
+    tv.store_transposed(Vhi, Vlo, 1.f);
     fence_smem_to_async();
     fence_before_sync();
     __syncthreads();
@@ -154,6 +185,10 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
         mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboQK), smem_desc(kh + adv, kLbo, kSboQK), kIdescS, 1);
       }
       mma_commit(&bar);
+    }
+    if (k0 + BN < seg_end) {                           // global loads of the next tile fly under the MMAs
+      tk.load(p.k + h * D, p.ldk, k0 + BN, seg_end);
+      tv.load(p.v + h * D, p.ldv, k0 + BN, seg_end);
     }
     mbar_wait(&bar, parity);
     parity ^= 1;
@@ -291,8 +326,16 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
 
   constexpr float kLog2e = 1.4426950408889634f;
-  stage_rows<BM, D>(Qhi, Qlo, p.q + h * D, p.ldq, row0, seg_end, p.scale * kLog2e);
-  stage_rows<BM, D>(Ghi, Glo, b.dout + h * D, b.lddo, row0, seg_end, 1.f);
+  {
+    Tile<BM, D> t;
+    t.load(p.q + h * D, p.ldq, row0, seg_end);
+    t.store_rows(Qhi, Qlo, p.scale * kLog2e);
+    t.load(b.dout + h * D, b.lddo, row0, seg_end);
+    t.store_rows(Ghi, Glo, 1.f);
+  }
+  Tile<BN, D> tk, tv;
+  tk.load(p.k + h * D, p.ldk, seg_beg, seg_end);
+  tv.load(p.v + h * D, p.ldv, seg_beg, seg_end);
   const int32_t row = row0 + tid;
   const bool row_ok = row < seg_end;
   const float lse2 = row_ok ? b.lse[(int64_t)row * p.H + h] * kLog2e : 0.f;
@@ -307,9 +350,9 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
   bool first = true;
 
   for (int32_t k0 = seg_beg; k0 < seg_end; k0 += BN) {
-    stage_rows<BN, D>(Khi, Klo, p.k + h * D, p.ldk, k0, seg_end, 1.f);
-    stage_rows<BN, D>(Vhi, Vlo, p.v + h * D, p.ldv, k0, seg_end, 1.f);
-    stage_transposed<BN, D>(KThi, KTlo, p.k + h * D, p.ldk, k0, seg_end);
+    tk.store_rows(Khi, Klo, 1.f);
+    tk.store_transposed(KThi, KTlo, 1.f);
+    tv.store_rows(Vhi, Vlo, 1.f);
     fence_smem_to_async();
     fence_before_sync();
     __syncthreads();
@@ -332,6 +375,10 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
         mma_tf32_ss(tmem + kColDP, smem_desc(gh + adv, kLbo, kSboD), smem_desc(vh + adv, kLbo, kSboD), kIdescS, 1);
       }
       mma_commit(&bar);
+    }
+    if (k0 + BN < seg_end) {
+      tk.load(p.k + h * D, p.ldk, k0 + BN, seg_end);
+      tv.load(p.v + h * D, p.ldv, k0 + BN, seg_end);
     }
     mbar_wait(&bar, parity);
     parity ^= 1;
@@ -430,8 +477,16 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
 
   constexpr float kLog2e = 1.4426950408889634f;
-  stage_rows<BM, D>(Khi, Klo, p.k + h * D, p.ldk, key0, seg_end, 1.f);
-  stage_rows<BM, D>(Vhi, Vlo, p.v + h * D, p.ldv, key0, seg_end, 1.f);
+  {
+    Tile<BM, D> t;
+    t.load(p.k + h * D, p.ldk, key0, seg_end);
+    t.store_rows(Khi, Klo, 1.f);
+    t.load(p.v + h * D, p.ldv, key0, seg_end);
+    t.store_rows(Vhi, Vlo, 1.f);
+  }
+  Tile<BQ, D> tq, tg;                                  // next query / dO tile, prefetched in registers
+  tq.load(p.q + h * D, p.ldq, seg_beg, seg_end);
+  tg.load(b.dout + h * D, b.lddo, seg_beg, seg_end);
 
   constexpr uint32_t kLbo = 128;
   constexpr uint32_t kSboD = (D / 4) * 128;
@@ -443,30 +498,10 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
 
   for (int32_t q0 = seg_beg; q0 < seg_end; q0 += BQ) {
     const float qmul = p.scale * kLog2e;
-    stage_rows<BQ, D>(Qhi, Qlo, p.q + h * D, p.ldq, q0, seg_end, qmul);
-    stage_rows<BQ, D>(Ghi, Glo, b.dout + h * D, b.lddo, q0, seg_end, 1.f);
-    // transposed copies (scaled like the row copy)
-    {
-      constexpr int CH = D / 4;
-      constexpr int SBO = (BQ / 4) * 32;
-      for (int idx = tid; idx < BQ * CH; idx += kThreads) {
-        const int r = idx / CH, c = idx - r * CH;
-        float4 xq = make_float4(0.f, 0.f, 0.f, 0.f), xg = xq;
-        if (q0 + r < seg_end) {
-          xq = __ldg(reinterpret_cast<const float4*>(p.q + h * D + (int64_t)(q0 + r) * p.ldq + 4 * c));
-          xg = __ldg(reinterpret_cast<const float4*>(b.dout + h * D + (int64_t)(q0 + r) * b.lddo + 4 * c));
-        }
-        const float qv[4] = {xq.x * qmul, xq.y * qmul, xq.z * qmul, xq.w * qmul};
-        const float gv[4] = {xg.x, xg.y, xg.z, xg.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int off = core_off(4 * c + i, r >> 2, SBO) + (r & 3);
-          float hi, lo;
-          split_tf32(qv[i], hi, lo); QThi[off] = hi; QTlo[off] = lo;
-          split_tf32(gv[i], hi, lo); GThi[off] = hi; GTlo[off] = lo;
-        }
-      }
-    }
+    tq.store_rows(Qhi, Qlo, qmul);
+    tq.store_transposed(QThi, QTlo, qmul);
+    tg.store_rows(Ghi, Glo, 1.f);
+    tg.store_transposed(GThi, GTlo, 1.f);
     if (tid < BQ) {
       const int32_t qrow = q0 + tid;
       const bool ok = qrow < seg_end;
@@ -495,6 +530,10 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
         mma_tf32_ss(tmem + kColDPT, smem_desc(vh + adv, kLbo, kSboD), smem_desc(gh + adv, kLbo, kSboD), kIdescS, 1);
       }
       mma_commit(&bar);
+    }
+    if (q0 + BQ < seg_end) {
+      tq.load(p.q + h * D, p.ldq, q0 + BQ, seg_end);
+      tg.load(b.dout + h * D, b.lddo, q0 + BQ, seg_end);
     }
     mbar_wait(&bar, parity);
     parity ^= 1;

@@ -20,7 +20,7 @@ from torch.nn import Linear, Module, ModuleDict, ModuleList, Sequential
 
 from ..globalAtt.gps import GPSConv
 from ..graph import pool_topo
-from ..nn import BatchNorm
+from ..nn import BatchNorm, FactoredEdgeAttr
 from ..ops import segment_sum
 from ..utils.model import activation_function_selection, loss_function_selection
 
@@ -143,10 +143,16 @@ class Base(Module):
         if self.input_dim:
             x = self.node_lin(torch.cat((self.node_emb(data.x.float()), x), 1))
         if self.is_edge_model:
-            e = self.rel_pos_emb(data.rel_pe)
+            # e = rel_pos_emb(rel_pe)  [or edge_lin(cat(edge_emb(edge_attr), rel_pos_emb(rel_pe)))],
+            # all bias-free Linears: handed to the convs in factored form (see nn.FactoredEdgeAttr)
             if self.use_edge_attr:
-                e = self.edge_lin(torch.cat((self.edge_emb(conv_args["edge_attr"]), e), 1))
-            conv_args["edge_attr"] = e
+                c = self.hidden_dim
+                w = self.edge_lin.weight
+                raw = torch.cat((conv_args["edge_attr"].float(), data.rel_pe), 1)
+                matrix = torch.cat((w[:, :c] @ self.edge_emb.weight, w[:, c:] @ self.rel_pos_emb.weight), 1)
+            else:
+                raw, matrix = data.rel_pe, self.rel_pos_emb.weight
+            conv_args["edge_attr"] = FactoredEdgeAttr(raw, matrix)
         return x
 
     def _embedding(self, data):

@@ -18,7 +18,7 @@ import torch.nn.functional as F
 from torch import nn
 
 from ..graph import topo_of
-from ..nn import Sequential
+from ..nn import Sequential, edge_linear
 from ..ops import edge_gather_add, segment_mean, segment_sum
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
@@ -66,7 +66,7 @@ class E_GCL(nn.Module):
         q = F.linear(x, w[:, C:2 * C])                # rows gathered at edge_index[1]
         h = edge_gather_add(p, q, topo, 0, 1) + radial * w[:, 2 * C]
         if edge_attr is not None:
-            h = h + F.linear(edge_attr, w[:, 2 * C + 1:])
+            h = h + edge_linear(edge_attr, w[:, 2 * C + 1:])
         for layer in list(self.edge_mlp)[1:]:
             h = layer(h)
         return h

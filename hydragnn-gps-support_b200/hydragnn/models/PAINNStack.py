@@ -18,7 +18,7 @@ import torch
 from torch import nn
 
 from ..graph import topo_of
-from ..nn import Sequential
+from ..nn import Sequential, edge_linear
 from ..ops import contract_node
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
@@ -62,7 +62,11 @@ class PainnMessage(nn.Module):
         fw = self.filter_layer(sinc_expansion(edge_dist, self.edge_size, self.cutoff))
         fw = fw * cosine_cutoff(edge_dist, self.cutoff)
         if edge_attr is not None and self.edge_dim is not None:
-            fw = fw * self.edge_filter(edge_attr)
+            first = self.edge_filter[0]
+            gate = edge_linear(edge_attr, first.weight, first.bias)
+            for layer in list(self.edge_filter)[1:]:
+                gate = layer(gate)
+            fw = fw * gate
         phi = self.scalar_message_mlp(node_scalar)                       # [N, 3F]
         fw_sv, fw_ev, fw_s = fw[:, :Fs], fw[:, Fs:2 * Fs], fw[:, 2 * Fs:]
         phi_sv, phi_ev, phi_s = phi[:, :Fs], phi[:, Fs:2 * Fs], phi[:, 2 * Fs:]

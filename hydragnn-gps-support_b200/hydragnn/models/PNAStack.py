@@ -8,14 +8,12 @@ cat[x_i, x_j(, enc(e))] is split into node-level GEMMs and the four aggregations
 one pass of a CSR kernel (ops.pna_aggregate) that forms each message in registers; the
 [E, F] message tensor and its four scatter passes are never materialised.
 """
-import math
-
 import torch
 import torch.nn.functional as F
 from torch import nn
 
 from ..graph import topo_of
-from ..nn import Sequential
+from ..nn import Sequential, edge_linear
 from ..ops import pna_aggregate
 from .Base import Base
 
@@ -74,7 +72,9 @@ class PNAConv(nn.Module):
         q = F.linear(x, pre.weight[:, Fin:2 * Fin])          # x_j = x[src] term
         r = None
         if edge_attr is not None and self.edge_dim is not None:
-            r = F.linear(self.edge_encoder(edge_attr), pre.weight[:, 2 * Fin:])
+            # pre[:, 2F:] (edge_encoder(e)) folded into one map of width edge_dim
+            w_e = pre.weight[:, 2 * Fin:]
+            r = edge_linear(edge_attr, w_e @ self.edge_encoder.weight, w_e @ self.edge_encoder.bias)
         aggr = pna_aggregate(p, q, r, topo)                  # [N, 4F]: mean | min | max | std
         deg = topo.degree(1).to(x.dtype).view(-1, 1)
         out = torch.cat([x] + self._scale(aggr, deg), dim=-1)

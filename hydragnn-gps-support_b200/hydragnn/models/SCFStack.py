@@ -19,7 +19,7 @@ import torch
 from torch import nn
 
 from ..graph import topo_of
-from ..nn import GaussianSmearing, Sequential, ShiftedSoftplus
+from ..nn import FactoredEdgeAttr, GaussianSmearing, Sequential, ShiftedSoftplus
 from ..ops import gather_mul_segment_sum, radius_graph, segment_mean
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
@@ -84,11 +84,24 @@ class CFConv(nn.Module):
         nn.init.xavier_uniform_(self.lin2.weight)
         self.lin2.bias.data.fill_(0)
 
+    def _filter(self, edge_rbf, edge_attr):
+        """Filter-generating network on cat[rbf, edge_attr] (SCFStack.py:269-272).  A factored edge
+        attribute is folded into the first Linear: K = num_gaussians + r instead of + hidden."""
+        if isinstance(edge_attr, FactoredEdgeAttr):
+            first = self.nn[0]
+            G = edge_rbf.size(-1)
+            weight = torch.cat([first.weight[:, :G], first.weight[:, G:] @ edge_attr.matrix], dim=1)
+            h = torch.nn.functional.linear(torch.cat([edge_rbf, edge_attr.raw], dim=-1), weight, first.bias)
+            for layer in list(self.nn)[1:]:
+                h = layer(h)
+            return h
+        feats = edge_rbf if edge_attr is None else torch.cat([edge_rbf, edge_attr], dim=-1)
+        return self.nn(feats)
+
     def forward(self, x, pos, edge_index, edge_weight, edge_rbf, edge_attr=None):
         topo = topo_of(edge_index, x.size(0))
         envelope = 0.5 * (torch.cos(edge_weight * math.pi / self.cutoff) + 1.0)
-        feats = edge_rbf if edge_attr is None else torch.cat([edge_rbf, edge_attr], dim=-1)
-        W = self.nn(feats) * envelope.view(-1, 1)
+        W = self._filter(edge_rbf, edge_attr) * envelope.view(-1, 1)
         x = self.lin1(x)
         if self.equivariant:
             unit, _ = get_edge_vectors_and_lengths(pos, edge_index, None, normalize=True, eps=1.0)

@@ -85,6 +85,43 @@ class GaussianSmearing(nn.Module):
         return torch.exp(self.coeff * torch.pow(dist, 2))
 
 
+class FactoredEdgeAttr:
+    """A per-edge embedding kept in factored form:  e = raw @ matrix.T  (raw [E, r], matrix [C, r]).
+
+    With GPS the reference materialises e = rel_pos_emb(rel_pe) (or edge_lin(cat(edge_emb(edge_attr),
+    rel_pos_emb(rel_pe)))), an [E, hidden] tensor, and every conv layer then feeds it to another
+    Linear (hydragnn/models/Base.py:237-242 -> SCFStack.py:269-272, EGCLStack.py:240-245,
+    PAINNStack.py:233-235).  All of those maps are linear and bias free, so a consumer Linear W
+    applied to e equals raw @ (W @ matrix).T: the [E, hidden] tensor is never built, the E-row GEMM
+    shrinks from K = hidden to K = r (8..9), and no gradient GEMM w.r.t. e is needed (raw is data).
+    """
+
+    def __init__(self, raw, matrix):
+        self.raw, self.matrix = raw, matrix
+
+    def size(self, dim=None):
+        shape = (self.raw.size(0), self.matrix.size(0))
+        return shape if dim is None else shape[dim]
+
+    @property
+    def shape(self):
+        return self.size()
+
+    def project(self, weight, bias=None):
+        """F.linear(e, weight, bias) without forming e."""
+        return torch.nn.functional.linear(self.raw, weight @ self.matrix, bias)
+
+    def materialize(self):
+        return torch.nn.functional.linear(self.raw, self.matrix)
+
+
+def edge_linear(edge_attr, weight, bias=None):
+    """F.linear on a plain or factored edge attribute."""
+    if isinstance(edge_attr, FactoredEdgeAttr):
+        return edge_attr.project(weight, bias)
+    return torch.nn.functional.linear(edge_attr, weight, bias)
+
+
 _ACTS = {"relu": nn.ReLU, "elu": nn.ELU, "gelu": nn.GELU, "silu": nn.SiLU, "tanh": nn.Tanh,
          "leaky_relu": nn.LeakyReLU, "sigmoid": nn.Sigmoid}
 
