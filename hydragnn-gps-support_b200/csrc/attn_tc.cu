@@ -1,18 +1,21 @@
 // GPS global attention on the 5th-generation tensor cores (tcgen05.mma kind::tf32, accumulators
 // in TMEM), fp32-accurate through 3xTF32 operand splitting.  Same contract as the SIMT kernels in
 // attn.cu (reference: hydragnn/globalAtt/gps.py:126-133 -- to_dense_batch + nn.MultiheadAttention
-// core + unpad), selected by hgk_attn_varlen_* when the head dim is a multiple of 16.
+// core + unpad), selected by hgk_attn_varlen_* when the head dim is 16 or 32.
 //
-// Forward, one CTA (128 threads) per (128-query tile, head):
-//   S  = Q K^T      tcgen05.mma SS: A = Q tile [128 x D] (smem, resident), B = K tile [64 x D]
-//   P  = online softmax of S: thread t owns TMEM lane t (= query row t), reads its 64 scores with
-//        tcgen05.ld, keeps running max / sum in registers (exp2 domain), writes P back to TMEM
-//        split in hi / lo parts (tcgen05.st)
-//   Ot = P V        tcgen05.mma TS: A = P (TMEM, lane = query, column = key), B = V^T tile
-//        [D x 64] (smem, K-major = keys contiguous); the [128 x D] product is read back and
-//        folded into the fp32 running output  acc = acc * corr + Ot  in registers.
-// Two CTAs share an SM (256 TMEM columns each) and overlap each other's load / MMA / softmax
-// phases; inside a CTA the phases are serialised by one mbarrier and __syncthreads.
+// Common shape of the three kernels: a CTA of 256 threads owns a 128-row tile (TMEM lane = row) and
+// loops over 64-column tiles of the other sequence.  Warp w works on TMEM lanes 32*(w%4)..+31 (the
+// only lanes the hardware lets it touch) and on column half w/4 of the current [128 x 64] block,
+// i.e. two threads share a row.  One elected thread issues the MMAs; an mbarrier (tcgen05.commit)
+// tells everyone when the accumulators are ready.  Global loads of the next tile are issued into
+// registers before waiting on the MMAs of the current one.
+//
+//   forward   S = Q K^T (SS)  ->  online softmax in registers (exp2 domain)  ->  P (hi, lo) back to
+//             TMEM  ->  O_tile = P V (TS, A = P from TMEM)  ->  acc = acc * corr + O_tile
+//   backward  P = 2^(s - lse2),  dP = dO V^T,  dS = P (dP - delta),  delta = rowsum(dO O)
+//     dQ kernel  : lanes = queries;  S, dP (SS)  ->  dS (hi, lo) to TMEM  ->  dQ += dS K     (TS)
+//     dK/dV kern.: lanes = keys;   S^T, dP^T (SS) -> P^T, dS^T to TMEM -> dV += P^T dO, dK += dS^T Q (TS)
+//   Deterministic: every output element is produced by exactly one CTA, no float atomics.
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
 
@@ -29,13 +32,13 @@ struct AttnTcArgs {
 
 namespace tc {
 
-constexpr int BM = 128;          // queries per CTA (= TMEM lanes)
-constexpr int BN = 64;           // keys per iteration
-constexpr int kThreads = 128;
-constexpr uint32_t kTmemCols = 256;
-constexpr uint32_t kColS = 0;    // S, overwritten in place by P_hi     [128 x 64]
-constexpr uint32_t kColPlo = 64; // P_lo                               [128 x 64]
-constexpr uint32_t kColO = 128;  // per-iteration P V product           [128 x D]
+constexpr int BM = 128;          // rows per CTA (= TMEM lanes)
+constexpr int BN = 64;           // columns per iteration
+constexpr int HALF = BN / 2;     // columns per thread
+constexpr int kThreads = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr uint32_t kLbo = 128;   // bytes between the two 16-byte K chunks of one MMA
 
 __device__ __forceinline__ bool locate_tile128(const int32_t* cu, int32_t S, int32_t tile,
                                                int32_t* seg_beg, int32_t* seg_end, int32_t* row0) {
@@ -53,59 +56,74 @@ __device__ __forceinline__ bool locate_tile128(const int32_t* cu, int32_t S, int
 }
 
 // ---- tile staging: global -> registers (prefetchable) -> shared memory --------------------------
-// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks; thread t owns chunks t, t+128, ...
-// chunk idx -> row r = idx / (D/4), 16-byte column c = idx % (D/4).
+// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks.  Chunk idx (thread t owns t, t+256, ...) maps to
+//   row r = idx % 8 + 8 * (idx / (8 * CH)),   16-byte column c = (idx / 8) % CH,      CH = D / 4
+// so the 32 lanes of a warp cover 8 consecutive rows x 4 columns: global reads are 64-byte runs,
+// and in the core-matrix layout the 8 rows of one column are 128 contiguous bytes -- both the row
+// store and the transposed store below are free of shared-memory bank conflicts.
 template <int ROWS, int D>
 struct Tile {
   static constexpr int CH = D / 4;
   static constexpr int PER = ROWS * CH / kThreads;
   static_assert(ROWS * CH % kThreads == 0, "tile must divide evenly over the CTA");
+  static_assert(CH % 4 == 0, "a warp spans 4 columns");
   float4 v[PER];
 
+  __device__ __forceinline__ static void coord(int it, int& r, int& c) {
+    const int idx = threadIdx.x + it * kThreads;
+    r = (idx & 7) + 8 * (idx / (8 * CH));
+    c = (idx >> 3) % CH;
+  }
   __device__ __forceinline__ void load(const float* src, int64_t ld, int32_t row0, int32_t row_end) {
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
-      const int idx = threadIdx.x + it * kThreads;
-      const int r = idx / CH, c = idx - r * CH;
+      int r, c;
+      coord(it, r, c);
       v[it] = make_float4(0.f, 0.f, 0.f, 0.f);          // rows past the segment end are zero
       if (row0 + r < row_end) v[it] = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * ld + 4 * c));
     }
   }
+  __device__ __forceinline__ void scale(float mul) {
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      v[it].x *= mul; v[it].y *= mul; v[it].z *= mul; v[it].w *= mul;
+    }
+  }
   // hi / lo K-major tiles with MN index = row, K index = feature
-  __device__ __forceinline__ void store_rows(float* hi, float* lo, float mul) const {
+  __device__ __forceinline__ void store_rows(float* hi, float* lo) const {
     constexpr int SBO = CH * 32;
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
-      const int idx = threadIdx.x + it * kThreads;
-      const int r = idx / CH, c = idx - r * CH;
+      int r, c;
+      coord(it, r, c);
       float4 h, l;
-      split_tf32(v[it].x * mul, h.x, l.x); split_tf32(v[it].y * mul, h.y, l.y);
-      split_tf32(v[it].z * mul, h.z, l.z); split_tf32(v[it].w * mul, h.w, l.w);
+      split_tf32(v[it].x, h.x, l.x); split_tf32(v[it].y, h.y, l.y);
+      split_tf32(v[it].z, h.z, l.z); split_tf32(v[it].w, h.w, l.w);
       const int off = core_off(r, c, SBO);
       *reinterpret_cast<float4*>(hi + off) = h;
       *reinterpret_cast<float4*>(lo + off) = l;
     }
   }
   // hi / lo K-major tiles of the TRANSPOSE: MN index = feature (D rows), K index = row (ROWS columns).
-  // The 4 lanes that hold the same 16-byte column of 4 consecutive rows exchange their values with
-  // 4 shuffles (a 4x4 register transpose), after which every lane writes one 16-byte chunk.
-  __device__ __forceinline__ void store_transposed(float* hi, float* lo, float mul) const {
+  // Lanes l, l^1, l^2, l^3 hold the same 16-byte column of 4 consecutive rows; a 4x4 register
+  // transpose (4 shuffles) lets every lane write one 16-byte chunk: feature 4c + (l & 3), 4 rows.
+  __device__ __forceinline__ void store_transposed(float* hi, float* lo) const {
     constexpr int SBO = (ROWS / 4) * 32;
     const int lane = threadIdx.x & 31;
-    const int rr = (lane / CH) & 3;                    // my row inside its group of 4
-    const int base = lane - rr * CH;                   // lane of row 0 of the group, same column
+    const int rr = lane & 3;                           // my row inside its group of 4
+    const int base = lane & ~3;
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
-      const int idx = threadIdx.x + it * kThreads;
-      const int r = idx / CH, c = idx - r * CH;
-      const float x[4] = {v[it].x * mul, v[it].y * mul, v[it].z * mul, v[it].w * mul};
+      int r, c;
+      coord(it, r, c);
+      const float x[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
       float w[4];
 #pragma unroll
       for (int s = 0; s < 4; ++s) {
         const int give = (rr - s) & 3;                 // the partner reading me at step s wants this feature
         const float send = give == 0 ? x[0] : (give == 1 ? x[1] : (give == 2 ? x[2] : x[3]));
         const int from = (rr + s) & 3;
-        const float got = __shfl_sync(0xffffffffu, send, base + from * CH);
+        const float got = __shfl_sync(0xffffffffu, send, base + from);
         if (from == 0) w[0] = got; else if (from == 1) w[1] = got; else if (from == 2) w[2] = got; else w[3] = got;
       }
       // w[j] = value of feature 4c + rr at row (r & ~3) + j
@@ -119,71 +137,135 @@ struct Tile {
   }
 };
 
+// 2^x for x <= 0 (and -inf): one MUFU instruction
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Operand descriptors are loop invariant: build them once, advance the 14-bit start-address field
+// (units of 16 bytes) by a constant per K step.
+struct OperandDesc {
+  uint64_t hi, lo;
+};
+template <int KD>
+__device__ __forceinline__ OperandDesc operand_desc(const float* hi, const float* lo) {
+  constexpr uint32_t sbo = (KD / 4) * 128;
+  return {smem_desc(smem_u32(hi), kLbo, sbo), smem_desc(smem_u32(lo), kLbo, sbo)};
+}
+
+// 3xTF32 product  D (+)= A B^T  with A, B in shared memory ([rows x KD] K-major tiles, hi / lo).
+template <int KD>
+__device__ __forceinline__ void mma3_ss(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                        uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2 * kLbo / 16);   // two 16-byte K chunks per MMA
+    mma_tf32_ss(d_tmem, a.lo + adv, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.lo + adv, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.hi + adv, idesc, 1);
+  }
+}
+// 3xTF32 product  D (+)= A B^T  with A (hi, lo) in TMEM (lane = row, column = k, KD columns) and
+// B = [N x KD] K-major tile in shared memory.
+template <int KD>
+__device__ __forceinline__ void mma3_ts(uint32_t d_tmem, uint32_t a_hi_tmem, uint32_t a_lo_tmem,
+                                        const OperandDesc& b, uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2 * kLbo / 16);
+    const uint32_t col = j * 8;                        // 8 k values = 8 TMEM columns per MMA
+    mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.hi + adv, idesc, 1);
+  }
+}
+
+struct CtaSetup {
+  uint32_t tmem;        // base of this CTA's TMEM allocation
+  uint32_t lane_base;   // this warp's lane quarter, in the address's lane field
+  int row_local;        // TMEM lane (= tile row) of this thread
+  int half;             // which 32-column half of a 64-column block this thread owns
+};
+
+__device__ __forceinline__ CtaSetup cta_setup(uint64_t* bar, uint32_t* tmem_slot, uint32_t ncols) {
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) tmem_alloc(tmem_slot, ncols);
+  if (threadIdx.x == 0) mbar_init(bar, 1);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  CtaSetup s;
+  s.tmem = *tmem_slot;
+  s.lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  s.row_local = (warp & 3) * 32 + (threadIdx.x & 31);
+  s.half = warp >> 2;
+  return s;
+}
+__device__ __forceinline__ void cta_teardown(uint32_t tmem, uint32_t ncols) {
+  fence_before_sync();
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0) tmem_dealloc(tmem, ncols);
+}
+// everyone's shared-memory / TMEM writes done -> the elected thread may issue MMAs
+__device__ __forceinline__ void publish_operands() {
+  fence_smem_to_async();
+  fence_before_sync();
+  __syncthreads();
+}
+
+// ================================================================================= forward ===
 template <int D>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __restrict__ lse) {
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
+  __shared__ float xchg[2][BM];                        // row max / row sum exchange between halves
 
   int32_t seg_beg, seg_end, row0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x;
 
-  float* Qhi = smem;
-  float* Qlo = Qhi + BM * D;
-  float* Khi = Qlo + BM * D;
-  float* Klo = Khi + BN * D;
-  float* Vhi = Klo + BN * D;     // V^T tile [D x BN]
-  float* Vlo = Vhi + BN * D;
+  float* Qhi = smem;             float* Qlo = Qhi + BM * D;
+  float* Khi = Qlo + BM * D;     float* Klo = Khi + BN * D;
+  float* Vhi = Klo + BN * D;     float* Vlo = Vhi + BN * D;      // V^T tile [D x BN]
 
-  if (warp == 0) tmem_alloc(&tmem_slot, kTmemCols);
-  if (tid == 0) mbar_init(&bar, 1);
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
-  const uint32_t tmem = tmem_slot;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  constexpr uint32_t kCols = 256;
+  constexpr uint32_t kColS = 0, kColPlo = 64, kColO = 128;       // P_hi overwrites S in place
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
 
-  constexpr float kLog2e = 1.4426950408889634f;
   {
     Tile<BM, D> tq;
     tq.load(p.q + h * D, p.ldq, row0, seg_end);
-    tq.store_rows(Qhi, Qlo, p.scale * kLog2e);
+    tq.scale(p.scale * kLog2e);                        // scores come out in the log2 domain
+    tq.store_rows(Qhi, Qlo);
   }
+  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dK = operand_desc<D>(Khi, Klo);
+  const OperandDesc dVt = operand_desc<BN>(Vhi, Vlo);
   Tile<BN, D> tk, tv;                                  // next key / value tile, prefetched in registers
   tk.load(p.k + h * D, p.ldk, seg_beg, seg_end);
   tv.load(p.v + h * D, p.ldv, seg_beg, seg_end);
 
-  constexpr uint32_t kLbo = 128;                       // bytes between K chunks
-  constexpr uint32_t kSboQK = (D / 4) * 128;           // bytes between 8-row groups (Q, K tiles)
-  constexpr uint32_t kSboV = (BN / 4) * 128;           // ... of the V^T tile
   constexpr uint32_t kIdescS = idesc_tf32(BM, BN);
   constexpr uint32_t kIdescO = idesc_tf32(BM, D);
-
-  float acc[D];
+  constexpr int DH = D / 2;                            // output columns per thread
+  float acc[DH];
 #pragma unroll
-  for (int d = 0; d < D; ++d) acc[d] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
+  for (int d = 0; d < DH; ++d) acc[d] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;                // l_run: this thread's half of the row sum
   uint32_t parity = 0;
 
   for (int32_t k0 = seg_beg; k0 < seg_end; k0 += BN) {
-    tk.store_rows(Khi, Klo, 1.f);
-    tv.store_transposed(Vhi, Vlo, 1.f);
-    fence_smem_to_async();
-    fence_before_sync();
-    __syncthreads();
+    tk.store_rows(Khi, Klo);
+    tv.store_transposed(Vhi, Vlo);
+    publish_operands();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t qh = smem_u32(Qhi), ql = smem_u32(Qlo), kh = smem_u32(Khi), kl = smem_u32(Klo);
-#pragma unroll
-      for (int j = 0; j < D / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;             // one MMA consumes two 16-byte K chunks
-        mma_tf32_ss(tmem + kColS, smem_desc(ql + adv, kLbo, kSboQK), smem_desc(kh + adv, kLbo, kSboQK), kIdescS, j > 0);
-        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboQK), smem_desc(kl + adv, kLbo, kSboQK), kIdescS, 1);
-        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboQK), smem_desc(kh + adv, kLbo, kSboQK), kIdescS, 1);
-      }
+      mma3_ss<D>(tmem + kColS, dQ, dK, kIdescS, false);
       mma_commit(&bar);
     }
     if (k0 + BN < seg_end) {                           // global loads of the next tile fly under the MMAs
@@ -194,52 +276,42 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
     parity ^= 1;
     fence_after_sync();
 
-    // ---- online softmax on this thread's row (scores are already in the log2 domain) ----
-    uint32_t s0[32], s1[32];
-    tmem_ld32(tmem + lane_base + kColS, s0);
-    tmem_ld32(tmem + lane_base + kColS + 32, s1);
+    uint32_t s[HALF];
+    tmem_ld32(tmem + cs.lane_base + kColS + cs.half * HALF, s);
     tmem_ld_wait();
-    const int32_t nvalid = seg_end - k0;               // keys [0, nvalid) of this tile exist
+    const int32_t nvalid = seg_end - k0 - cs.half * HALF;   // my columns [0, nvalid) exist
+    if (nvalid < HALF) {                               // last tile of the segment only (warp uniform)
+#pragma unroll
+      for (int j = 0; j < HALF; ++j)
+        if (j >= nvalid) s[j] = 0xff800000u;           // -inf
+    }
     float mx = -INFINITY;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (j >= nvalid) s0[j] = 0xff800000u;            // -inf
-      if (j + 32 >= nvalid) s1[j] = 0xff800000u;
-      mx = fmaxf(mx, fmaxf(__uint_as_float(s0[j]), __uint_as_float(s1[j])));
-    }
-    const float m_new = fmaxf(m_run, mx);
-    const float corr = exp2f(m_run - m_new);
+    for (int j = 0; j < HALF; ++j) mx = fmaxf(mx, __uint_as_float(s[j]));
+    xchg[cs.half][cs.row_local] = mx;
+    __syncthreads();
+    mx = fmaxf(mx, xchg[cs.half ^ 1][cs.row_local]);
+    const float m_new = fmaxf(m_run, mx);              // finite: every key tile has a valid key
+    const float corr = fast_exp2(m_run - m_new);
     float rs = 0.f;
-    uint32_t lo0[32], lo1[32];
+    uint32_t lo[HALF];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const float p0 = exp2f(__uint_as_float(s0[j]) - m_new);
-      const float p1 = exp2f(__uint_as_float(s1[j]) - m_new);
-      rs += p0 + p1;
-      float h0, l0, h1, l1;
-      split_tf32(p0, h0, l0);
-      split_tf32(p1, h1, l1);
-      s0[j] = __float_as_uint(h0); lo0[j] = __float_as_uint(l0);
-      s1[j] = __float_as_uint(h1); lo1[j] = __float_as_uint(l1);
+    for (int j = 0; j < HALF; ++j) {
+      const float pj = fast_exp2(__uint_as_float(s[j]) - m_new);
+      rs += pj;
+      float hi_, lo_;
+      split_tf32(pj, hi_, lo_);
+      s[j] = __float_as_uint(hi_);
+      lo[j] = __float_as_uint(lo_);
     }
-    tmem_st32(tmem + lane_base + kColS, s0);
-    tmem_st32(tmem + lane_base + kColS + 32, s1);
-    tmem_st32(tmem + lane_base + kColPlo, lo0);
-    tmem_st32(tmem + lane_base + kColPlo + 32, lo1);
+    tmem_st32(tmem + cs.lane_base + kColS + cs.half * HALF, s);
+    tmem_st32(tmem + cs.lane_base + kColPlo + cs.half * HALF, lo);
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t vh = smem_u32(Vhi), vl = smem_u32(Vlo);
-#pragma unroll
-      for (int j = 0; j < BN / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        const uint32_t pc = j * 8;                     // 8 keys = 8 TMEM columns per MMA
-        mma_tf32_ts(tmem + kColO, tmem + kColPlo + pc, smem_desc(vh + adv, kLbo, kSboV), kIdescO, j > 0);
-        mma_tf32_ts(tmem + kColO, tmem + kColS + pc, smem_desc(vl + adv, kLbo, kSboV), kIdescO, 1);
-        mma_tf32_ts(tmem + kColO, tmem + kColS + pc, smem_desc(vh + adv, kLbo, kSboV), kIdescO, 1);
-      }
+      mma3_ts<BN>(tmem + kColO, tmem + kColS, tmem + kColPlo, dVt, kIdescO, false);
       mma_commit(&bar);
     }
     mbar_wait(&bar, parity);
@@ -248,59 +320,44 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
 
     l_run = l_run * corr + rs;
     m_run = m_new;
+    uint32_t ot[16];
 #pragma unroll
-    for (int c0 = 0; c0 < D; c0 += 16) {
-      uint32_t ot[16];
-      tmem_ld16(tmem + lane_base + kColO + c0, ot);
+    for (int c0 = 0; c0 < DH; c0 += 16) {
+      tmem_ld16(tmem + cs.lane_base + kColO + cs.half * DH + c0, ot);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 16; ++j) acc[c0 + j] = fmaf(acc[c0 + j], corr, __uint_as_float(ot[j]));
+      for (int j = 0; j < 16; ++j)
+        if (c0 + j < DH) acc[c0 + j] = fmaf(acc[c0 + j], corr, __uint_as_float(ot[j]));
     }
   }
 
-  const int32_t row = row0 + tid;
+  // full row sum = sum of the two halves (both carry the same running max)
+  __syncthreads();
+  xchg[cs.half][cs.row_local] = l_run;
+  __syncthreads();
+  const float l_tot = l_run + xchg[cs.half ^ 1][cs.row_local];
+  const int32_t row = row0 + cs.row_local;
   if (row < seg_end) {
-    const float inv = 1.f / l_run;
-    float* orow = o + (int64_t)row * ldo + h * D;
+    const float inv = 1.f / l_tot;
+    float* orow = o + (int64_t)row * ldo + h * D + cs.half * DH;
 #pragma unroll
-    for (int d = 0; d < D; d += 4)
+    for (int d = 0; d < DH; d += 4)
       *reinterpret_cast<float4*>(orow + d) =
           make_float4(acc[d] * inv, acc[d + 1] * inv, acc[d + 2] * inv, acc[d + 3] * inv);
-    constexpr float kLn2 = 0.6931471805599453f;
-    lse[(int64_t)row * p.H + h] = (m_run + log2f(l_run)) * kLn2;
+    if (cs.half == 0) lse[(int64_t)row * p.H + h] = (m_run + log2f(l_tot)) * kLn2;
   }
-  fence_before_sync();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+  cta_teardown(tmem, kCols);
 }
 
-template <int D>
-int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
-  // 2 CTAs per SM: 256 TMEM columns each; the shared-memory request (>= 1/3 of the SM) enforces it
-  size_t smem = sizeof(float) * (2 * BM * D + 4 * BN * D);
-  if (smem < 80 * 1024) smem = 80 * 1024;
-  cudaError_t err = cudaFuncSetAttribute(k_attn_fwd_tc<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "attn_fwd_tc: smem opt-in failed: %s", cudaGetErrorString(err));
-  dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
-  k_attn_fwd_tc<D><<<grid, kThreads, smem, st>>>(a, o, ldo, lse);
-  return check_launch("attn_varlen_fwd(tcgen05)");
-}
-
-
-// =============================================================================== backward ===
-// Two deterministic kernels (no float atomics), both recomputing the probabilities from lse:
-//   k_attn_bwd_q_tc  : CTA owns 128 queries, loops over 64-key tiles          -> dQ
-//   k_attn_bwd_kv_tc : CTA owns 128 keys (TMEM lane = key), loops over 64-query tiles -> dK, dV
-// With s = (q.k) scale log2(e)  (Q is staged pre-multiplied), lse2 = lse log2(e):
-//   P = 2^(s - lse2),  dP = dO V^T,  dS = P (dP - delta),  delta = rowsum(dO O)
-//   dQ = scale dS K,   dK = scale dS^T Q,   dV = P^T dO
+// ================================================================================ backward ===
 struct AttnTcBwdArgs {
   const float* dout; int64_t lddo;
   const float* lse; const float* delta;
 };
 
+// ---- dQ: CTA owns 128 queries, loops over 64-key tiles ---------------------------------------
 template <int D>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dq) {
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
@@ -308,7 +365,7 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
   int32_t seg_beg, seg_end, row0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x;
 
   float* Qhi = smem;             float* Qlo = Qhi + BM * D;
   float* Ghi = Qlo + BM * D;     float* Glo = Ghi + BM * D;      // dO tile
@@ -316,64 +373,44 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
   float* Vhi = Klo + BN * D;     float* Vlo = Vhi + BN * D;
   float* KThi = Vlo + BN * D;    float* KTlo = KThi + BN * D;    // K^T tile [D x BN]
 
+  constexpr uint32_t kCols = 256;
   constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;       // dS_hi -> S region, dS_lo -> dP region
-  if (warp == 0) tmem_alloc(&tmem_slot, 256);
-  if (tid == 0) mbar_init(&bar, 1);
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
-  const uint32_t tmem = tmem_slot;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
 
-  constexpr float kLog2e = 1.4426950408889634f;
   {
     Tile<BM, D> t;
     t.load(p.q + h * D, p.ldq, row0, seg_end);
-    t.store_rows(Qhi, Qlo, p.scale * kLog2e);
+    t.scale(p.scale * kLog2e);
+    t.store_rows(Qhi, Qlo);
     t.load(b.dout + h * D, b.lddo, row0, seg_end);
-    t.store_rows(Ghi, Glo, 1.f);
+    t.store_rows(Ghi, Glo);
   }
+  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dG = operand_desc<D>(Ghi, Glo);
+  const OperandDesc dK = operand_desc<D>(Khi, Klo), dV = operand_desc<D>(Vhi, Vlo);
+  const OperandDesc dKt = operand_desc<BN>(KThi, KTlo);
   Tile<BN, D> tk, tv;
   tk.load(p.k + h * D, p.ldk, seg_beg, seg_end);
   tv.load(p.v + h * D, p.ldv, seg_beg, seg_end);
-  const int32_t row = row0 + tid;
+  const int32_t row = row0 + cs.row_local;
   const bool row_ok = row < seg_end;
   const float lse2 = row_ok ? b.lse[(int64_t)row * p.H + h] * kLog2e : 0.f;
   const float delta = row_ok ? b.delta[(int64_t)row * p.H + h] : 0.f;
 
-  constexpr uint32_t kLbo = 128;
-  constexpr uint32_t kSboD = (D / 4) * 128;            // tiles whose K dim is the feature dim
-  constexpr uint32_t kSboT = (BN / 4) * 128;           // transposed tiles (K dim = 64 keys)
   constexpr uint32_t kIdescS = idesc_tf32(BM, BN);
   constexpr uint32_t kIdescQ = idesc_tf32(BM, D);
   uint32_t parity = 0;
   bool first = true;
 
   for (int32_t k0 = seg_beg; k0 < seg_end; k0 += BN) {
-    tk.store_rows(Khi, Klo, 1.f);
-    tk.store_transposed(KThi, KTlo, 1.f);
-    tv.store_rows(Vhi, Vlo, 1.f);
-    fence_smem_to_async();
-    fence_before_sync();
-    __syncthreads();
+    tk.store_rows(Khi, Klo);
+    tk.store_transposed(KThi, KTlo);
+    tv.store_rows(Vhi, Vlo);
+    publish_operands();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t qh = smem_u32(Qhi), ql = smem_u32(Qlo), gh = smem_u32(Ghi), gl = smem_u32(Glo);
-      const uint32_t kh = smem_u32(Khi), kl = smem_u32(Klo), vh = smem_u32(Vhi), vl = smem_u32(Vlo);
-#pragma unroll
-      for (int j = 0; j < D / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        mma_tf32_ss(tmem + kColS, smem_desc(ql + adv, kLbo, kSboD), smem_desc(kh + adv, kLbo, kSboD), kIdescS, j > 0);
-        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboD), smem_desc(kl + adv, kLbo, kSboD), kIdescS, 1);
-        mma_tf32_ss(tmem + kColS, smem_desc(qh + adv, kLbo, kSboD), smem_desc(kh + adv, kLbo, kSboD), kIdescS, 1);
-      }
-#pragma unroll
-      for (int j = 0; j < D / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        mma_tf32_ss(tmem + kColDP, smem_desc(gl + adv, kLbo, kSboD), smem_desc(vh + adv, kLbo, kSboD), kIdescS, j > 0);
-        mma_tf32_ss(tmem + kColDP, smem_desc(gh + adv, kLbo, kSboD), smem_desc(vl + adv, kLbo, kSboD), kIdescS, 1);
-        mma_tf32_ss(tmem + kColDP, smem_desc(gh + adv, kLbo, kSboD), smem_desc(vh + adv, kLbo, kSboD), kIdescS, 1);
-      }
+      mma3_ss<D>(tmem + kColS, dQ, dK, kIdescS, false);                  // S  = Q K^T
+      mma3_ss<D>(tmem + kColDP, dG, dV, kIdescS, false);                 // dP = dO V^T
       mma_commit(&bar);
     }
     if (k0 + BN < seg_end) {
@@ -384,72 +421,66 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
     parity ^= 1;
     fence_after_sync();
 
-    const int32_t nvalid = seg_end - k0;
+    const int32_t nvalid = seg_end - k0 - cs.half * HALF;
+    uint32_t sv[HALF], dv[HALF];
+    tmem_ld32(tmem + cs.lane_base + kColS + cs.half * HALF, sv);
+    tmem_ld32(tmem + cs.lane_base + kColDP + cs.half * HALF, dv);
+    tmem_ld_wait();
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      uint32_t sv[32], dv[32];
-      tmem_ld32(tmem + lane_base + kColS + 32 * half, sv);
-      tmem_ld32(tmem + lane_base + kColDP + 32 * half, dv);
-      tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float pj = exp2f(__uint_as_float(sv[j]) - lse2);
-        float ds = pj * (__uint_as_float(dv[j]) - delta);
-        if (j + 32 * half >= nvalid) ds = 0.f;
-        float hi, lo;
-        split_tf32(ds, hi, lo);
-        sv[j] = __float_as_uint(hi);
-        dv[j] = __float_as_uint(lo);
-      }
-      tmem_st32(tmem + lane_base + kColS + 32 * half, sv);
-      tmem_st32(tmem + lane_base + kColDP + 32 * half, dv);
+    for (int j = 0; j < HALF; ++j) {
+      const float pj = fast_exp2(__uint_as_float(sv[j]) - lse2);
+      const float ds = pj * (__uint_as_float(dv[j]) - delta);
+      float hi_, lo_;
+      split_tf32(ds, hi_, lo_);
+      sv[j] = __float_as_uint(hi_);
+      dv[j] = __float_as_uint(lo_);
     }
+    if (nvalid < HALF) {                               // keys past the segment end contribute nothing
+#pragma unroll
+      for (int j = 0; j < HALF; ++j)
+        if (j >= nvalid) { sv[j] = 0u; dv[j] = 0u; }
+    }
+    tmem_st32(tmem + cs.lane_base + kColS + cs.half * HALF, sv);
+    tmem_st32(tmem + cs.lane_base + kColDP + cs.half * HALF, dv);
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t th = smem_u32(KThi), tl = smem_u32(KTlo);
-#pragma unroll
-      for (int j = 0; j < BN / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        const uint32_t pc = j * 8;
-        mma_tf32_ts(tmem + kColDQ, tmem + kColDP + pc, smem_desc(th + adv, kLbo, kSboT), kIdescQ, !(first && j == 0));
-        mma_tf32_ts(tmem + kColDQ, tmem + kColS + pc, smem_desc(tl + adv, kLbo, kSboT), kIdescQ, 1);
-        mma_tf32_ts(tmem + kColDQ, tmem + kColS + pc, smem_desc(th + adv, kLbo, kSboT), kIdescQ, 1);
-      }
+      mma3_ts<BN>(tmem + kColDQ, tmem + kColS, tmem + kColDP, dKt, kIdescQ, !first);           // dQ += dS K
       mma_commit(&bar);
     }
     first = false;
-    mbar_wait(&bar, parity);
+    mbar_wait(&bar, parity);                           // K / K^T / V tiles and S / dP are free again
     parity ^= 1;
     fence_after_sync();
   }
 
   // tcgen05.ld is warp-collective (.sync.aligned): every thread loads, valid rows store
-  float* drow = dq + ((int64_t)row * p.H + h) * D;
+  constexpr int DH = D / 2;
+  float* drow = dq + ((int64_t)row * p.H + h) * D + cs.half * DH;
+  uint32_t t[16];
 #pragma unroll
-  for (int c0 = 0; c0 < D; c0 += 16) {
-    uint32_t t[16];
-    tmem_ld16(tmem + lane_base + kColDQ + c0, t);
+  for (int c0 = 0; c0 < DH; c0 += 16) {
+    tmem_ld16(tmem + cs.lane_base + kColDQ + cs.half * DH + c0, t);
     tmem_ld_wait();
     if (row_ok) {
 #pragma unroll
       for (int j = 0; j < 16; j += 4)
-        *reinterpret_cast<float4*>(drow + c0 + j) =
-            make_float4(__uint_as_float(t[j]) * p.scale, __uint_as_float(t[j + 1]) * p.scale,
-                        __uint_as_float(t[j + 2]) * p.scale, __uint_as_float(t[j + 3]) * p.scale);
+        if (c0 + j < DH)
+          *reinterpret_cast<float4*>(drow + c0 + j) =
+              make_float4(__uint_as_float(t[j]) * p.scale, __uint_as_float(t[j + 1]) * p.scale,
+                          __uint_as_float(t[j + 2]) * p.scale, __uint_as_float(t[j + 3]) * p.scale);
     }
   }
-  fence_before_sync();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 256);
+  cta_teardown(tmem, kCols);
 }
 
+// ---- dK, dV: CTA owns 128 keys (TMEM lane = key), loops over 64-query tiles -------------------
 template <int D>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 1)
 k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv) {
-  constexpr int BQ = 64;                                // queries per iteration
+  constexpr int BQ = BN;                               // queries per iteration
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -457,7 +488,7 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   int32_t seg_beg, seg_end, key0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x;
 
   float* Khi = smem;             float* Klo = Khi + BM * D;
   float* Vhi = Klo + BM * D;     float* Vlo = Vhi + BM * D;
@@ -466,69 +497,48 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   float* QThi = Glo + BQ * D;    float* QTlo = QThi + BQ * D;    // Q^T [D x BQ]   (B of dK)
   float* GThi = QTlo + BQ * D;   float* GTlo = GThi + BQ * D;    // dO^T [D x BQ]  (B of dV)
 
-  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
   constexpr uint32_t kCols = 512;
-  if (warp == 0) tmem_alloc(&tmem_slot, kCols);
-  if (tid == 0) mbar_init(&bar, 1);
-  fence_before_sync();
-  __syncthreads();
-  fence_after_sync();
-  const uint32_t tmem = tmem_slot;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
 
-  constexpr float kLog2e = 1.4426950408889634f;
   {
     Tile<BM, D> t;
     t.load(p.k + h * D, p.ldk, key0, seg_end);
-    t.store_rows(Khi, Klo, 1.f);
+    t.store_rows(Khi, Klo);
     t.load(p.v + h * D, p.ldv, key0, seg_end);
-    t.store_rows(Vhi, Vlo, 1.f);
+    t.store_rows(Vhi, Vlo);
   }
+  const OperandDesc dK = operand_desc<D>(Khi, Klo), dV = operand_desc<D>(Vhi, Vlo);
+  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dG = operand_desc<D>(Ghi, Glo);
+  const OperandDesc dQt = operand_desc<BQ>(QThi, QTlo), dGt = operand_desc<BQ>(GThi, GTlo);
   Tile<BQ, D> tq, tg;                                  // next query / dO tile, prefetched in registers
   tq.load(p.q + h * D, p.ldq, seg_beg, seg_end);
   tg.load(b.dout + h * D, b.lddo, seg_beg, seg_end);
 
-  constexpr uint32_t kLbo = 128;
-  constexpr uint32_t kSboD = (D / 4) * 128;
-  constexpr uint32_t kSboT = (BQ / 4) * 128;
   constexpr uint32_t kIdescS = idesc_tf32(BM, BQ);
   constexpr uint32_t kIdescD = idesc_tf32(BM, D);
+  const float qmul = p.scale * kLog2e;
   uint32_t parity = 0;
   bool first = true;
 
   for (int32_t q0 = seg_beg; q0 < seg_end; q0 += BQ) {
-    const float qmul = p.scale * kLog2e;
-    tq.store_rows(Qhi, Qlo, qmul);
-    tq.store_transposed(QThi, QTlo, qmul);
-    tg.store_rows(Ghi, Glo, 1.f);
-    tg.store_transposed(GThi, GTlo, 1.f);
+    tq.scale(qmul);
+    tq.store_rows(Qhi, Qlo);
+    tq.store_transposed(QThi, QTlo);
+    tg.store_rows(Ghi, Glo);
+    tg.store_transposed(GThi, GTlo);
     if (tid < BQ) {
       const int32_t qrow = q0 + tid;
       const bool ok = qrow < seg_end;
       lse2_s[tid] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
       delta_s[tid] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
     }
-    fence_smem_to_async();
-    fence_before_sync();
-    __syncthreads();
+    publish_operands();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t kh = smem_u32(Khi), kl = smem_u32(Klo), vh = smem_u32(Vhi), vl = smem_u32(Vlo);
-      const uint32_t qh = smem_u32(Qhi), ql = smem_u32(Qlo), gh = smem_u32(Ghi), gl = smem_u32(Glo);
-#pragma unroll
-      for (int j = 0; j < D / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        mma_tf32_ss(tmem + kColST, smem_desc(kl + adv, kLbo, kSboD), smem_desc(qh + adv, kLbo, kSboD), kIdescS, j > 0);
-        mma_tf32_ss(tmem + kColST, smem_desc(kh + adv, kLbo, kSboD), smem_desc(ql + adv, kLbo, kSboD), kIdescS, 1);
-        mma_tf32_ss(tmem + kColST, smem_desc(kh + adv, kLbo, kSboD), smem_desc(qh + adv, kLbo, kSboD), kIdescS, 1);
-      }
-#pragma unroll
-      for (int j = 0; j < D / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        mma_tf32_ss(tmem + kColDPT, smem_desc(vl + adv, kLbo, kSboD), smem_desc(gh + adv, kLbo, kSboD), kIdescS, j > 0);
-        mma_tf32_ss(tmem + kColDPT, smem_desc(vh + adv, kLbo, kSboD), smem_desc(gl + adv, kLbo, kSboD), kIdescS, 1);
-        mma_tf32_ss(tmem + kColDPT, smem_desc(vh + adv, kLbo, kSboD), smem_desc(gh + adv, kLbo, kSboD), kIdescS, 1);
-      }
+      mma3_ss<D>(tmem + kColST, dK, dQ, kIdescS, false);                 // S^T  = K Q^T
+      mma3_ss<D>(tmem + kColDPT, dV, dG, kIdescS, false);                // dP^T = V dO^T
       mma_commit(&bar);
     }
     if (q0 + BQ < seg_end) {
@@ -539,48 +549,34 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     parity ^= 1;
     fence_after_sync();
 
-    const int32_t nvalid = seg_end - q0;                 // query columns [0, nvalid) exist
+    const int col0 = cs.half * HALF;
+    const int32_t nvalid = seg_end - q0 - col0;        // my query columns [0, nvalid) exist
+    uint32_t sv[HALF], dp[HALF], plo[HALF], dslo[HALF];
+    tmem_ld32(tmem + cs.lane_base + kColST + col0, sv);
+    tmem_ld32(tmem + cs.lane_base + kColDPT + col0, dp);
+    tmem_ld_wait();
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      uint32_t sv[32], dp[32], plo[32], dslo[32];
-      tmem_ld32(tmem + lane_base + kColST + 32 * half, sv);
-      tmem_ld32(tmem + lane_base + kColDPT + 32 * half, dp);
-      tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int col = j + 32 * half;
-        float pj = exp2f(__uint_as_float(sv[j]) - lse2_s[col]);
-        if (col >= nvalid) pj = 0.f;
-        const float ds = pj * (__uint_as_float(dp[j]) - delta_s[col]);
-        float hi, lo;
-        split_tf32(pj, hi, lo);
-        sv[j] = __float_as_uint(hi); plo[j] = __float_as_uint(lo);
-        split_tf32(ds, hi, lo);
-        dp[j] = __float_as_uint(hi); dslo[j] = __float_as_uint(lo);
-      }
-      tmem_st32(tmem + lane_base + kColST + 32 * half, sv);
-      tmem_st32(tmem + lane_base + kColPlo + 32 * half, plo);
-      tmem_st32(tmem + lane_base + kColDPT + 32 * half, dp);
-      tmem_st32(tmem + lane_base + kColDSlo + 32 * half, dslo);
+    for (int j = 0; j < HALF; ++j) {
+      float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[col0 + j]);
+      if (j >= nvalid) pj = 0.f;
+      const float ds = pj * (__uint_as_float(dp[j]) - delta_s[col0 + j]);
+      float hi_, lo_;
+      split_tf32(pj, hi_, lo_);
+      sv[j] = __float_as_uint(hi_); plo[j] = __float_as_uint(lo_);
+      split_tf32(ds, hi_, lo_);
+      dp[j] = __float_as_uint(hi_); dslo[j] = __float_as_uint(lo_);
     }
+    tmem_st32(tmem + cs.lane_base + kColST + col0, sv);
+    tmem_st32(tmem + cs.lane_base + kColPlo + col0, plo);
+    tmem_st32(tmem + cs.lane_base + kColDPT + col0, dp);
+    tmem_st32(tmem + cs.lane_base + kColDSlo + col0, dslo);
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (tid == 0) {
       fence_after_sync();
-      const uint32_t qth = smem_u32(QThi), qtl = smem_u32(QTlo), gth = smem_u32(GThi), gtl = smem_u32(GTlo);
-#pragma unroll
-      for (int j = 0; j < BQ / 8; ++j) {
-        const uint32_t adv = j * 2 * kLbo;
-        const uint32_t pc = j * 8;
-        const uint32_t acc0 = !(first && j == 0);
-        mma_tf32_ts(tmem + kColDV, tmem + kColPlo + pc, smem_desc(gth + adv, kLbo, kSboT), kIdescD, acc0);
-        mma_tf32_ts(tmem + kColDV, tmem + kColST + pc, smem_desc(gtl + adv, kLbo, kSboT), kIdescD, 1);
-        mma_tf32_ts(tmem + kColDV, tmem + kColST + pc, smem_desc(gth + adv, kLbo, kSboT), kIdescD, 1);
-        mma_tf32_ts(tmem + kColDK, tmem + kColDSlo + pc, smem_desc(qth + adv, kLbo, kSboT), kIdescD, acc0);
-        mma_tf32_ts(tmem + kColDK, tmem + kColDPT + pc, smem_desc(qtl + adv, kLbo, kSboT), kIdescD, 1);
-        mma_tf32_ts(tmem + kColDK, tmem + kColDPT + pc, smem_desc(qth + adv, kLbo, kSboT), kIdescD, 1);
-      }
+      mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, dGt, kIdescD, !first);           // dV += P^T dO
+      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, dQt, kIdescD, !first);         // dK += dS^T Q
       mma_commit(&bar);
     }
     first = false;
@@ -589,49 +585,68 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     fence_after_sync();
   }
 
-  const int32_t krow = key0 + tid;
+  constexpr int DH = D / 2;
+  const int32_t krow = key0 + cs.row_local;
   const bool ok = krow < seg_end;
-  constexpr float kLn2 = 0.6931471805599453f;
+  uint32_t tv_[16], tk_[16];
 #pragma unroll
-  for (int c0 = 0; c0 < D; c0 += 16) {
-    uint32_t tv[16], tk[16];
-    tmem_ld16(tmem + lane_base + kColDV + c0, tv);
-    tmem_ld16(tmem + lane_base + kColDK + c0, tk);
+  for (int c0 = 0; c0 < DH; c0 += 16) {
+    tmem_ld16(tmem + cs.lane_base + kColDV + cs.half * DH + c0, tv_);
+    tmem_ld16(tmem + cs.lane_base + kColDK + cs.half * DH + c0, tk_);
     tmem_ld_wait();
     if (ok) {
-      float* vrow = dv + ((int64_t)krow * p.H + h) * D + c0;
-      float* krow_p = dk + ((int64_t)krow * p.H + h) * D + c0;
+      float* vrow = dv + ((int64_t)krow * p.H + h) * D + cs.half * DH + c0;
+      float* krow_p = dk + ((int64_t)krow * p.H + h) * D + cs.half * DH + c0;
 #pragma unroll
       for (int j = 0; j < 16; j += 4) {
-        *reinterpret_cast<float4*>(vrow + j) = make_float4(__uint_as_float(tv[j]), __uint_as_float(tv[j + 1]),
-                                                           __uint_as_float(tv[j + 2]), __uint_as_float(tv[j + 3]));
-        *reinterpret_cast<float4*>(krow_p + j) =
-            make_float4(__uint_as_float(tk[j]) * kLn2, __uint_as_float(tk[j + 1]) * kLn2,
-                        __uint_as_float(tk[j + 2]) * kLn2, __uint_as_float(tk[j + 3]) * kLn2);
+        if (c0 + j < DH) {
+          *reinterpret_cast<float4*>(vrow + j) =
+              make_float4(__uint_as_float(tv_[j]), __uint_as_float(tv_[j + 1]),
+                          __uint_as_float(tv_[j + 2]), __uint_as_float(tv_[j + 3]));
+          // Q was staged as q * scale * log2(e):  dK = scale * dS^T Q = (dS^T Q_staged) * ln 2
+          *reinterpret_cast<float4*>(krow_p + j) =
+              make_float4(__uint_as_float(tk_[j]) * kLn2, __uint_as_float(tk_[j + 1]) * kLn2,
+                          __uint_as_float(tk_[j + 2]) * kLn2, __uint_as_float(tk_[j + 3]) * kLn2);
+        }
       }
     }
   }
-  fence_before_sync();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, kCols);
+  cta_teardown(tmem, kCols);
 }
 
+// ---------------------------------------------------------------------------------- launch ---
 template <typename K>
 int opt_in_smem(K kernel, size_t bytes, const char* what) {
   cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "%s: smem opt-in (%zu B) failed: %s", what, bytes, cudaGetErrorString(err));
+  if (err != cudaSuccess)
+    return fail(HGK_ERR_CUDA, "%s: smem opt-in (%zu B) failed: %s", what, bytes, cudaGetErrorString(err));
   return HGK_OK;
+}
+
+template <int D>
+int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
+  // 2 CTAs per SM: 256 TMEM columns each; the shared-memory request (> 1/3 of the SM) enforces it
+  size_t smem = sizeof(float) * (2 * BM * D + 4 * BN * D);
+  if (smem < 80 * 1024) smem = 80 * 1024;
+  int rc = opt_in_smem(k_attn_fwd_tc<D>, smem, "attn_fwd_tc");
+  if (rc) return rc;
+  dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
+  k_attn_fwd_tc<D><<<grid, kThreads, smem, st>>>(a, o, ldo, lse);
+  return check_launch("attn_varlen_fwd(tcgen05)");
 }
 
 template <int D>
 int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk, float* dv, int64_t N,
                cudaStream_t st) {
   dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
-  const size_t smem_kv = sizeof(float) * (4 * BM * D + 8 * 64 * D);
+  // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
+  size_t smem_kv = sizeof(float) * (4 * BM * D + 8 * BN * D);
+  if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
   int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
   if (rc) return rc;
   k_attn_bwd_kv_tc<D><<<grid, kThreads, smem_kv, st>>>(a, b, dk, dv);
-  const size_t smem_q = sizeof(float) * (4 * BM * D + 6 * BN * D);
+  size_t smem_q = sizeof(float) * (4 * BM * D + 6 * BN * D);
+  if (smem_q < 80 * 1024) smem_q = 80 * 1024;
   rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
   if (rc) return rc;
   k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
@@ -640,20 +655,20 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
 
 }  // namespace tc
 
+static bool tc_aligned(const void* ptr, int64_t ld) {
+  return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ld % 4 == 0;
+}
+
 // Called by hgk_attn_varlen_fwd.  Returns 1 if this shape is not handled here (caller falls back
 // to the SIMT kernel), 0 on success, a negative hgk_status on error.
 int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, const float* k,
                 int64_t ldk, const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N,
                 int32_t H, int32_t D, float scale, cudaStream_t st) {
-  auto ok16 = [](const void* ptr, int64_t ld) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ld % 4 == 0; };
-  if (!(D == 16 || D == 32 || D == 64)) return 1;
-  if (!ok16(q, ldq) || !ok16(k, ldk) || !ok16(v, ldv) || !ok16(o, ldo)) return 1;
+  if (!(D == 16 || D == 32)) return 1;
+  if (!tc_aligned(q, ldq) || !tc_aligned(k, ldk) || !tc_aligned(v, ldv) || !tc_aligned(o, ldo)) return 1;
   AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
-  switch (D) {
-    case 16: return tc::launch_fwd<16>(a, o, ldo, lse, N, st);
-    case 32: return tc::launch_fwd<32>(a, o, ldo, lse, N, st);
-    default: return tc::launch_fwd<64>(a, o, ldo, lse, N, st);
-  }
+  if (D == 16) return tc::launch_fwd<16>(a, o, ldo, lse, N, st);
+  return tc::launch_fwd<32>(a, o, ldo, lse, N, st);
 }
 
 // Called by hgk_attn_varlen_bwd after delta = rowsum(dO * O) has been enqueued.  Same return
@@ -662,9 +677,9 @@ int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float
                 const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
                 const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
                 int32_t D, float scale, cudaStream_t st) {
-  auto ok16 = [](const void* ptr, int64_t ld) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ld % 4 == 0; };
-  if (!(D == 16 || D == 32)) return 1;     // D = 64 would need 224+ KB of shared memory in the kv kernel
-  if (!ok16(q, ldq) || !ok16(k, ldk) || !ok16(v, ldv) || !ok16(dout, lddo) || !ok16(dq, 4) || !ok16(dk, 4) || !ok16(dv, 4))
+  if (!(D == 16 || D == 32)) return 1;
+  if (!tc_aligned(q, ldq) || !tc_aligned(k, ldk) || !tc_aligned(v, ldv) || !tc_aligned(dout, lddo) ||
+      !tc_aligned(dq, 4) || !tc_aligned(dk, 4) || !tc_aligned(dv, 4))
     return 1;
   AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
   tc::AttnTcBwdArgs b{dout, lddo, lse, delta};
