@@ -80,7 +80,13 @@ struct Tile {
       int r, c;
       coord(it, r, c);
       v[it] = make_float4(0.f, 0.f, 0.f, 0.f);          // rows past the segment end are zero
-      if (row0 + r < row_end) v[it] = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * ld + 4 * c));
+      // volatile asm: the load is issued HERE (a plain __ldg may be sunk to its first use, which
+      // would put the whole L2 latency back on the critical path of the next iteration)
+      if (row0 + r < row_end) {
+        const float* ptr = src + (int64_t)(row0 + r) * ld + 4 * c;
+        asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v[it].x), "=f"(v[it].y), "=f"(v[it].z), "=f"(v[it].w) : "l"(ptr));
+      }
     }
   }
   __device__ __forceinline__ void scale(float mul) {
@@ -111,20 +117,26 @@ struct Tile {
     constexpr int SBO = (ROWS / 4) * 32;
     const int lane = threadIdx.x & 31;
     const int rr = lane & 3;                           // my row inside its group of 4
-    const int base = lane & ~3;
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
       int r, c;
       coord(it, r, c);
-      const float x[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
-      float w[4];
-#pragma unroll
-      for (int s = 0; s < 4; ++s) {
-        const int give = (rr - s) & 3;                 // the partner reading me at step s wants this feature
-        const float send = give == 0 ? x[0] : (give == 1 ? x[1] : (give == 2 ? x[2] : x[3]));
-        const int from = (rr + s) & 3;
-        const float got = __shfl_sync(0xffffffffu, send, base + from);
-        if (from == 0) w[0] = got; else if (from == 1) w[1] = got; else if (from == 2) w[2] = got; else w[3] = got;
+      // 4x4 transpose across lanes l, l^1, l^2, l^3 in two butterfly stages; only selects (no
+      // lane-dependent register indexing, which the compiler would turn into divergent branches)
+      float w[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+      {
+        const bool odd = (lane & 1) != 0;
+        const float r0 = __shfl_xor_sync(0xffffffffu, odd ? w[0] : w[1], 1);
+        const float r1 = __shfl_xor_sync(0xffffffffu, odd ? w[2] : w[3], 1);
+        w[0] = odd ? r0 : w[0]; w[1] = odd ? w[1] : r0;
+        w[2] = odd ? r1 : w[2]; w[3] = odd ? w[3] : r1;
+      }
+      {
+        const bool up = (lane & 2) != 0;
+        const float r0 = __shfl_xor_sync(0xffffffffu, up ? w[0] : w[2], 2);
+        const float r1 = __shfl_xor_sync(0xffffffffu, up ? w[1] : w[3], 2);
+        w[0] = up ? r0 : w[0]; w[2] = up ? w[2] : r0;
+        w[1] = up ? r1 : w[1]; w[3] = up ? w[3] : r1;
       }
       // w[j] = value of feature 4c + rr at row (r & ~3) + j
       float4 h, l;
@@ -182,6 +194,35 @@ __device__ __forceinline__ void mma3_ts(uint32_t d_tmem, uint32_t a_hi_tmem, uin
   }
 }
 
+// This thread's half (D/2 features) of row `row` of a [*, ld] matrix, times `mul`, split and written
+// to TMEM as the A operand of later MMAs (lane = row, column = feature).  Warp-collective.
+template <int D>
+__device__ __forceinline__ void row_to_tmem(uint32_t t_hi, uint32_t t_lo, const float* src, int64_t ld,
+                                            int64_t row, bool ok, int half, float mul) {
+  constexpr int DH = D / 2;
+  const float* ptr = src + row * ld + half * DH;
+#pragma unroll
+  for (int c0 = 0; c0 < DH; c0 += 8) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (ok) {
+      a = __ldg(reinterpret_cast<const float4*>(ptr + c0));
+      b = __ldg(reinterpret_cast<const float4*>(ptr + c0 + 4));
+    }
+    const float x[8] = {a.x * mul, a.y * mul, a.z * mul, a.w * mul, b.x * mul, b.y * mul, b.z * mul, b.w * mul};
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float h_, l_;
+      split_tf32(x[j], h_, l_);
+      hi[j] = __float_as_uint(h_);
+      lo[j] = __float_as_uint(l_);
+    }
+    tmem_st8(t_hi + half * DH + c0, hi);
+    tmem_st8(t_lo + half * DH + c0, lo);
+  }
+  tmem_st_wait();
+}
+
 struct CtaSetup {
   uint32_t tmem;        // base of this CTA's TMEM allocation
   uint32_t lane_base;   // this warp's lane quarter, in the address's lane field
@@ -227,24 +268,22 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
   int32_t seg_beg, seg_end, row0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x;
+  const int warp_u = warp_id_uniform();
 
-  float* Qhi = smem;             float* Qlo = Qhi + BM * D;
-  float* Khi = Qlo + BM * D;     float* Klo = Khi + BN * D;
+  float* Khi = smem;             float* Klo = Khi + BN * D;
   float* Vhi = Klo + BN * D;     float* Vlo = Vhi + BN * D;      // V^T tile [D x BN]
 
   constexpr uint32_t kCols = 256;
-  constexpr uint32_t kColS = 0, kColPlo = 64, kColO = 128;       // P_hi overwrites S in place
+  // P_hi overwrites S in place; Q (hi, lo) lives in TMEM for the whole kernel as the A operand of S
+  constexpr uint32_t kColS = 0, kColPlo = 64, kColO = 128, kColQhi = 128 + D, kColQlo = 128 + 2 * D;
+  static_assert(128 + 3 * D <= 256, "TMEM budget");
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
 
-  {
-    Tile<BM, D> tq;
-    tq.load(p.q + h * D, p.ldq, row0, seg_end);
-    tq.scale(p.scale * kLog2e);                        // scores come out in the log2 domain
-    tq.store_rows(Qhi, Qlo);
-  }
-  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dK = operand_desc<D>(Khi, Klo);
+  // scores come out in the log2 domain: Q is pre-multiplied by scale * log2(e)
+  row_to_tmem<D>(tmem + cs.lane_base + kColQhi, tmem + cs.lane_base + kColQlo, p.q + h * D, p.ldq,
+                 row0 + cs.row_local, row0 + cs.row_local < seg_end, cs.half, p.scale * kLog2e);
+  const OperandDesc dK = operand_desc<D>(Khi, Klo);
   const OperandDesc dVt = operand_desc<BN>(Vhi, Vlo);
   Tile<BN, D> tk, tv;                                  // next key / value tile, prefetched in registers
   tk.load(p.k + h * D, p.ldk, seg_beg, seg_end);
@@ -263,9 +302,9 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
     tk.store_rows(Khi, Klo);
     tv.store_transposed(Vhi, Vlo);
     publish_operands();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<D>(tmem + kColS, dQ, dK, kIdescS, false);
+      mma3_ts<D>(tmem + kColS, tmem + kColQhi, tmem + kColQlo, dK, kIdescS, false);
       mma_commit(&bar);
     }
     if (k0 + BN < seg_end) {                           // global loads of the next tile fly under the MMAs
@@ -309,7 +348,7 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
       mma3_ts<BN>(tmem + kColO, tmem + kColS, tmem + kColPlo, dVt, kIdescO, false);
       mma_commit(&bar);
@@ -365,28 +404,27 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
   int32_t seg_beg, seg_end, row0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x;
+  const int warp_u = warp_id_uniform();
 
-  float* Qhi = smem;             float* Qlo = Qhi + BM * D;
-  float* Ghi = Qlo + BM * D;     float* Glo = Ghi + BM * D;      // dO tile
+  float* Ghi = smem;             float* Glo = Ghi + BM * D;      // dO tile
   float* Khi = Glo + BM * D;     float* Klo = Khi + BN * D;
   float* Vhi = Klo + BN * D;     float* Vlo = Vhi + BN * D;
   float* KThi = Vlo + BN * D;    float* KTlo = KThi + BN * D;    // K^T tile [D x BN]
 
   constexpr uint32_t kCols = 256;
-  constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;       // dS_hi -> S region, dS_lo -> dP region
+  // dS_hi -> S region, dS_lo -> dP region; Q (hi, lo) resident in TMEM as the A operand of S
+  constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128, kColQhi = 128 + D, kColQlo = 128 + 2 * D;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
 
+  row_to_tmem<D>(tmem + cs.lane_base + kColQhi, tmem + cs.lane_base + kColQlo, p.q + h * D, p.ldq,
+                 row0 + cs.row_local, row0 + cs.row_local < seg_end, cs.half, p.scale * kLog2e);
   {
     Tile<BM, D> t;
-    t.load(p.q + h * D, p.ldq, row0, seg_end);
-    t.scale(p.scale * kLog2e);
-    t.store_rows(Qhi, Qlo);
     t.load(b.dout + h * D, b.lddo, row0, seg_end);
     t.store_rows(Ghi, Glo);
   }
-  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dG = operand_desc<D>(Ghi, Glo);
+  const OperandDesc dG = operand_desc<D>(Ghi, Glo);
   const OperandDesc dK = operand_desc<D>(Khi, Klo), dV = operand_desc<D>(Vhi, Vlo);
   const OperandDesc dKt = operand_desc<BN>(KThi, KTlo);
   Tile<BN, D> tk, tv;
@@ -407,9 +445,9 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
     tk.store_transposed(KThi, KTlo);
     tv.store_rows(Vhi, Vlo);
     publish_operands();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<D>(tmem + kColS, dQ, dK, kIdescS, false);                  // S  = Q K^T
+      mma3_ts<D>(tmem + kColS, tmem + kColQhi, tmem + kColQlo, dK, kIdescS, false);   // S  = Q K^T
       mma3_ss<D>(tmem + kColDP, dG, dV, kIdescS, false);                 // dP = dO V^T
       mma_commit(&bar);
     }
@@ -445,7 +483,7 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
       mma3_ts<BN>(tmem + kColDQ, tmem + kColS, tmem + kColDP, dKt, kIdescQ, !first);           // dQ += dS K
       mma_commit(&bar);
@@ -488,28 +526,27 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   int32_t seg_beg, seg_end, key0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
   const int h = blockIdx.y;
-  const int tid = threadIdx.x;
+  const int warp_u = warp_id_uniform();
 
-  float* Khi = smem;             float* Klo = Khi + BM * D;
-  float* Vhi = Klo + BM * D;     float* Vlo = Vhi + BM * D;
-  float* Qhi = Vlo + BM * D;     float* Qlo = Qhi + BQ * D;      // rows = queries (B of S^T)
+  float* Qhi = smem;             float* Qlo = Qhi + BQ * D;      // rows = queries (B of S^T)
   float* Ghi = Qlo + BQ * D;     float* Glo = Ghi + BQ * D;      // dO rows        (B of dP^T)
   float* QThi = Glo + BQ * D;    float* QTlo = QThi + BQ * D;    // Q^T [D x BQ]   (B of dK)
   float* GThi = QTlo + BQ * D;   float* GTlo = GThi + BQ * D;    // dO^T [D x BQ]  (B of dV)
 
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
+  // this CTA's K and V rows (hi, lo) stay in TMEM as the A operands of S^T and dP^T
+  constexpr uint32_t kColKhi = 256 + 2 * D, kColKlo = 256 + 3 * D, kColVhi = 256 + 4 * D, kColVlo = 256 + 5 * D;
+  static_assert(256 + 6 * D <= 512, "TMEM budget");
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
 
   {
-    Tile<BM, D> t;
-    t.load(p.k + h * D, p.ldk, key0, seg_end);
-    t.store_rows(Khi, Klo);
-    t.load(p.v + h * D, p.ldv, key0, seg_end);
-    t.store_rows(Vhi, Vlo);
+    const int64_t krow_ld = key0 + cs.row_local;
+    const bool kok = krow_ld < seg_end;
+    row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, cs.half, 1.f);
+    row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, cs.half, 1.f);
   }
-  const OperandDesc dK = operand_desc<D>(Khi, Klo), dV = operand_desc<D>(Vhi, Vlo);
   const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dG = operand_desc<D>(Ghi, Glo);
   const OperandDesc dQt = operand_desc<BQ>(QThi, QTlo), dGt = operand_desc<BQ>(GThi, GTlo);
   Tile<BQ, D> tq, tg;                                  // next query / dO tile, prefetched in registers
@@ -528,17 +565,17 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     tq.store_transposed(QThi, QTlo);
     tg.store_rows(Ghi, Glo);
     tg.store_transposed(GThi, GTlo);
-    if (tid < BQ) {
-      const int32_t qrow = q0 + tid;
+    if (threadIdx.x < BQ) {
+      const int32_t qrow = q0 + (int32_t)threadIdx.x;
       const bool ok = qrow < seg_end;
-      lse2_s[tid] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
-      delta_s[tid] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
+      lse2_s[threadIdx.x] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
+      delta_s[threadIdx.x] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
     }
     publish_operands();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<D>(tmem + kColST, dK, dQ, kIdescS, false);                 // S^T  = K Q^T
-      mma3_ss<D>(tmem + kColDPT, dV, dG, kIdescS, false);                // dP^T = V dO^T
+      mma3_ts<D>(tmem + kColST, tmem + kColKhi, tmem + kColKlo, dQ, kIdescS, false);    // S^T  = K Q^T
+      mma3_ts<D>(tmem + kColDPT, tmem + kColVhi, tmem + kColVlo, dG, kIdescS, false);   // dP^T = V dO^T
       mma_commit(&bar);
     }
     if (q0 + BQ < seg_end) {
@@ -573,7 +610,7 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
       mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, dGt, kIdescD, !first);           // dV += P^T dO
       mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, dQt, kIdescD, !first);         // dK += dS^T Q
@@ -626,7 +663,7 @@ int opt_in_smem(K kernel, size_t bytes, const char* what) {
 template <int D>
 int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
   // 2 CTAs per SM: 256 TMEM columns each; the shared-memory request (> 1/3 of the SM) enforces it
-  size_t smem = sizeof(float) * (2 * BM * D + 4 * BN * D);
+  size_t smem = sizeof(float) * (4 * BN * D);
   if (smem < 80 * 1024) smem = 80 * 1024;
   int rc = opt_in_smem(k_attn_fwd_tc<D>, smem, "attn_fwd_tc");
   if (rc) return rc;
@@ -640,12 +677,12 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
                cudaStream_t st) {
   dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
   // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
-  size_t smem_kv = sizeof(float) * (4 * BM * D + 8 * BN * D);
+  size_t smem_kv = sizeof(float) * (8 * BN * D);
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
   int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
   if (rc) return rc;
   k_attn_bwd_kv_tc<D><<<grid, kThreads, smem_kv, st>>>(a, b, dk, dv);
-  size_t smem_q = sizeof(float) * (4 * BM * D + 6 * BN * D);
+  size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
   if (smem_q < 80 * 1024) smem_q = 80 * 1024;
   rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
   if (rc) return rc;
