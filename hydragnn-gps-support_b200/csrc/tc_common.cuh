@@ -184,5 +184,214 @@ __device__ __forceinline__ int core_off(int row, int kchunk, int sbo_floats) {
   return (row >> 3) * sbo_floats + kchunk * 32 + (row & 7) * 4;
 }
 
+// ================================================================================================
+// Building blocks shared by the tensor-core kernels (attn_tc.cu, filter_tc.cu): 256-thread CTAs,
+// TMEM lane = tile row, two threads per row.
+constexpr int kThreads = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr uint32_t kLbo = 128;   // bytes between the two 16-byte K chunks of one MMA
+
+// ---- tile staging: global -> registers (prefetchable) -> shared memory --------------------------
+// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks.  Chunk idx (thread t owns t, t+256, ...) maps to
+//   row r = idx % 8 + 8 * (idx / (8 * CH)),   16-byte column c = (idx / 8) % CH,      CH = D / 4
+// so the 32 lanes of a warp cover 8 consecutive rows x 4 columns: global reads are 64-byte runs,
+// and in the core-matrix layout the 8 rows of one column are 128 contiguous bytes -- both the row
+// store and the transposed store below are free of shared-memory bank conflicts.
+template <int ROWS, int D>
+struct Tile {
+  static constexpr int CH = D / 4;
+  static constexpr int PER = ROWS * CH / kThreads;
+  static_assert(ROWS * CH % kThreads == 0, "tile must divide evenly over the CTA");
+  static_assert(CH % 4 == 0, "a warp spans 4 columns");
+  float4 v[PER];
+
+  __device__ __forceinline__ static void coord(int it, int& r, int& c) {
+    const int idx = threadIdx.x + it * kThreads;
+    r = (idx & 7) + 8 * (idx / (8 * CH));
+    c = (idx >> 3) % CH;
+  }
+  __device__ __forceinline__ void load(const float* src, int64_t ld, int32_t row0, int32_t row_end) {
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      int r, c;
+      coord(it, r, c);
+      v[it] = make_float4(0.f, 0.f, 0.f, 0.f);          // rows past the segment end are zero
+      // volatile asm: the load is issued HERE (a plain __ldg may be sunk to its first use, which
+      // would put the whole L2 latency back on the critical path of the next iteration)
+      if (row0 + r < row_end) {
+        const float* ptr = src + (int64_t)(row0 + r) * ld + 4 * c;
+        asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v[it].x), "=f"(v[it].y), "=f"(v[it].z), "=f"(v[it].w) : "l"(ptr));
+      }
+    }
+  }
+  __device__ __forceinline__ void scale(float mul) {
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      v[it].x *= mul; v[it].y *= mul; v[it].z *= mul; v[it].w *= mul;
+    }
+  }
+  // hi / lo K-major tiles with MN index = row, K index = feature
+  __device__ __forceinline__ void store_rows(float* hi, float* lo) const {
+    constexpr int SBO = CH * 32;
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      int r, c;
+      coord(it, r, c);
+      float4 h, l;
+      split_tf32(v[it].x, h.x, l.x); split_tf32(v[it].y, h.y, l.y);
+      split_tf32(v[it].z, h.z, l.z); split_tf32(v[it].w, h.w, l.w);
+      const int off = core_off(r, c, SBO);
+      *reinterpret_cast<float4*>(hi + off) = h;
+      *reinterpret_cast<float4*>(lo + off) = l;
+    }
+  }
+  // hi / lo K-major tiles of the TRANSPOSE: MN index = feature (D rows), K index = row (ROWS columns).
+  // Lanes l, l^1, l^2, l^3 hold the same 16-byte column of 4 consecutive rows; a 4x4 register
+  // transpose (4 shuffles) lets every lane write one 16-byte chunk: feature 4c + (l & 3), 4 rows.
+  __device__ __forceinline__ void store_transposed(float* hi, float* lo) const {
+    constexpr int SBO = (ROWS / 4) * 32;
+    const int lane = threadIdx.x & 31;
+    const int rr = lane & 3;                           // my row inside its group of 4
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      int r, c;
+      coord(it, r, c);
+      // 4x4 transpose across lanes l, l^1, l^2, l^3 in two butterfly stages; only selects (no
+      // lane-dependent register indexing, which the compiler would turn into divergent branches)
+      float w[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+      {
+        const bool odd = (lane & 1) != 0;
+        const float r0 = __shfl_xor_sync(0xffffffffu, odd ? w[0] : w[1], 1);
+        const float r1 = __shfl_xor_sync(0xffffffffu, odd ? w[2] : w[3], 1);
+        w[0] = odd ? r0 : w[0]; w[1] = odd ? w[1] : r0;
+        w[2] = odd ? r1 : w[2]; w[3] = odd ? w[3] : r1;
+      }
+      {
+        const bool up = (lane & 2) != 0;
+        const float r0 = __shfl_xor_sync(0xffffffffu, up ? w[0] : w[2], 2);
+        const float r1 = __shfl_xor_sync(0xffffffffu, up ? w[1] : w[3], 2);
+        w[0] = up ? r0 : w[0]; w[2] = up ? w[2] : r0;
+        w[1] = up ? r1 : w[1]; w[3] = up ? w[3] : r1;
+      }
+      // w[j] = value of feature 4c + rr at row (r & ~3) + j
+      float4 h, l;
+      split_tf32(w[0], h.x, l.x); split_tf32(w[1], h.y, l.y);
+      split_tf32(w[2], h.z, l.z); split_tf32(w[3], h.w, l.w);
+      const int off = core_off(4 * c + rr, r >> 2, SBO);
+      *reinterpret_cast<float4*>(hi + off) = h;
+      *reinterpret_cast<float4*>(lo + off) = l;
+    }
+  }
+};
+
+// 2^x for x <= 0 (and -inf): one MUFU instruction
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Operand descriptors are loop invariant: build them once, advance the 14-bit start-address field
+// (units of 16 bytes) by a constant per K step.
+struct OperandDesc {
+  uint64_t hi, lo;
+};
+template <int KD>
+__device__ __forceinline__ OperandDesc operand_desc(const float* hi, const float* lo) {
+  constexpr uint32_t sbo = (KD / 4) * 128;
+  return {smem_desc(smem_u32(hi), kLbo, sbo), smem_desc(smem_u32(lo), kLbo, sbo)};
+}
+
+// 3xTF32 product  D (+)= A B^T  with A, B in shared memory ([rows x KD] K-major tiles, hi / lo).
+template <int KD>
+__device__ __forceinline__ void mma3_ss(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                        uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2 * kLbo / 16);   // two 16-byte K chunks per MMA
+    mma_tf32_ss(d_tmem, a.lo + adv, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.lo + adv, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.hi + adv, idesc, 1);
+  }
+}
+// 3xTF32 product  D (+)= A B^T  with A (hi, lo) in TMEM (lane = row, column = k, KD columns) and
+// B = [N x KD] K-major tile in shared memory.
+template <int KD>
+__device__ __forceinline__ void mma3_ts(uint32_t d_tmem, uint32_t a_hi_tmem, uint32_t a_lo_tmem,
+                                        const OperandDesc& b, uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2 * kLbo / 16);
+    const uint32_t col = j * 8;                        // 8 k values = 8 TMEM columns per MMA
+    mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.hi + adv, idesc, 1);
+  }
+}
+
+// This thread's half (D/2 features) of row `row` of a [*, ld] matrix, times `mul`, split and written
+// to TMEM as the A operand of later MMAs (lane = row, column = feature).  Warp-collective.
+template <int D>
+__device__ __forceinline__ void row_to_tmem(uint32_t t_hi, uint32_t t_lo, const float* src, int64_t ld,
+                                            int64_t row, bool ok, int half, float mul) {
+  constexpr int DH = D / 2;
+  const float* ptr = src + row * ld + half * DH;
+#pragma unroll
+  for (int c0 = 0; c0 < DH; c0 += 8) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (ok) {
+      a = __ldg(reinterpret_cast<const float4*>(ptr + c0));
+      b = __ldg(reinterpret_cast<const float4*>(ptr + c0 + 4));
+    }
+    const float x[8] = {a.x * mul, a.y * mul, a.z * mul, a.w * mul, b.x * mul, b.y * mul, b.z * mul, b.w * mul};
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float h_, l_;
+      split_tf32(x[j], h_, l_);
+      hi[j] = __float_as_uint(h_);
+      lo[j] = __float_as_uint(l_);
+    }
+    tmem_st8(t_hi + half * DH + c0, hi);
+    tmem_st8(t_lo + half * DH + c0, lo);
+  }
+  tmem_st_wait();
+}
+
+struct CtaSetup {
+  uint32_t tmem;        // base of this CTA's TMEM allocation
+  uint32_t lane_base;   // this warp's lane quarter, in the address's lane field
+  int row_local;        // TMEM lane (= tile row) of this thread
+  int half;             // which 32-column half of a 64-column block this thread owns
+};
+
+__device__ __forceinline__ CtaSetup cta_setup(uint64_t* bar, uint32_t* tmem_slot, uint32_t ncols) {
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) tmem_alloc(tmem_slot, ncols);
+  if (threadIdx.x == 0) mbar_init(bar, 1);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  CtaSetup s;
+  s.tmem = *tmem_slot;
+  s.lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  s.row_local = (warp & 3) * 32 + (threadIdx.x & 31);
+  s.half = warp >> 2;
+  return s;
+}
+__device__ __forceinline__ void cta_teardown(uint32_t tmem, uint32_t ncols) {
+  fence_before_sync();
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 0) tmem_dealloc(tmem, ncols);
+}
+// everyone's shared-memory / TMEM writes done -> the elected thread may issue MMAs
+__device__ __forceinline__ void publish_operands() {
+  fence_smem_to_async();
+  fence_before_sync();
+  __syncthreads();
+}
+
 }  // namespace tc
 }  // namespace hgk

@@ -19,8 +19,9 @@ import torch
 from torch import nn
 
 from ..graph import topo_of
-from ..nn import FactoredEdgeAttr, GaussianSmearing, Sequential, ShiftedSoftplus
+from ..nn import FactoredEdgeAttr, GaussianSmearing, LazyGaussians, Sequential, ShiftedSoftplus
 from ..ops import gather_mul_segment_sum, radius_graph, segment_mean
+from ..ops.filter import fused_filter_ok, schnet_filter
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
 
@@ -85,23 +86,41 @@ class CFConv(nn.Module):
         self.lin2.bias.data.fill_(0)
 
     def _filter(self, edge_rbf, edge_attr):
-        """Filter-generating network on cat[rbf, edge_attr] (SCFStack.py:269-272).  A factored edge
-        attribute is folded into the first Linear: K = num_gaussians + r instead of + hidden."""
+        """Filter-generating network on cat[rbf, edge_attr] times the cosine envelope
+        (SCFStack.py:268-272).  Fast path: one fused tensor-core kernel fed with the raw distances
+        and the un-embedded edge attribute.  Otherwise torch, with a factored edge attribute still
+        folded into the first Linear (K = num_gaussians + r instead of + hidden)."""
+        first, last = self.nn[0], self.nn[2]
+        if isinstance(edge_rbf, LazyGaussians):
+            G = edge_rbf.offset.numel()
+            factored = isinstance(edge_attr, FactoredEdgeAttr)
+            raw = edge_attr.raw if factored else None
+            if (edge_attr is None or factored) and fused_filter_ok(edge_rbf.dist, raw, first.out_features, G) \
+                    and last.in_features == last.out_features == first.out_features:
+                w0r = first.weight[:, G:] @ edge_attr.matrix if factored else None
+                return schnet_filter(edge_rbf.dist, raw, edge_rbf.offset, edge_rbf.coeff, self.cutoff,
+                                     first.weight[:, :G], w0r, first.bias, last.weight, last.bias)
+            dist = edge_rbf.dist
+            edge_rbf = edge_rbf.materialize()
+        else:
+            dist = None
         if isinstance(edge_attr, FactoredEdgeAttr):
-            first = self.nn[0]
             G = edge_rbf.size(-1)
             weight = torch.cat([first.weight[:, :G], first.weight[:, G:] @ edge_attr.matrix], dim=1)
             h = torch.nn.functional.linear(torch.cat([edge_rbf, edge_attr.raw], dim=-1), weight, first.bias)
             for layer in list(self.nn)[1:]:
                 h = layer(h)
-            return h
-        feats = edge_rbf if edge_attr is None else torch.cat([edge_rbf, edge_attr], dim=-1)
-        return self.nn(feats)
+        else:
+            feats = edge_rbf if edge_attr is None else torch.cat([edge_rbf, edge_attr], dim=-1)
+            h = self.nn(feats)
+        return h, dist
 
     def forward(self, x, pos, edge_index, edge_weight, edge_rbf, edge_attr=None):
         topo = topo_of(edge_index, x.size(0))
-        envelope = 0.5 * (torch.cos(edge_weight * math.pi / self.cutoff) + 1.0)
-        W = self._filter(edge_rbf, edge_attr) * envelope.view(-1, 1)
+        W = self._filter(edge_rbf, edge_attr)
+        if isinstance(W, tuple):     # unfused: apply the cosine envelope here (SCFStack.py:268)
+            envelope = 0.5 * (torch.cos(edge_weight * math.pi / self.cutoff) + 1.0)
+            W = W[0] * envelope.view(-1, 1)
         x = self.lin1(x)
         if self.equivariant:
             unit, _ = get_edge_vectors_and_lengths(pos, edge_index, None, normalize=True, eps=1.0)
@@ -129,6 +148,7 @@ class SCFStack(Base):
 
     def _init_conv(self):
         self.distance_expansion = GaussianSmearing(0.0, self.radius, self.num_gaussians)
+        self.distance_expansion.lazy = True     # CFConv expands the distances itself (fused kernel)
         self.interaction_graph = RadiusInteractionGraph(self.radius, self.max_neighbours)
         widths = [self.embed_dim] + [self.hidden_dim] * self.num_conv_layers
         for k, (w_in, w_out) in enumerate(zip(widths[:-1], widths[1:])):

@@ -80,9 +80,28 @@ class GaussianSmearing(nn.Module):
         self.coeff = -0.5 / (offset[1] - offset[0]).item() ** 2
         self.register_buffer("offset", offset)
 
+    lazy = False   # SCFStack sets this: hand the distances on and let the consumer expand them
+
     def forward(self, dist):
-        dist = dist.view(-1, 1) - self.offset.view(1, -1)
-        return torch.exp(self.coeff * torch.pow(dist, 2))
+        if self.lazy:
+            return LazyGaussians(dist, self.offset, self.coeff)
+        return LazyGaussians(dist, self.offset, self.coeff).materialize()
+
+
+class LazyGaussians:
+    """exp(coeff (d - mu_k)^2) not yet evaluated: the fused filter kernel expands the distances in
+    registers, so the [E, G] tensor is only built if a consumer asks for it."""
+
+    def __init__(self, dist, offset, coeff):
+        self.dist, self.offset, self.coeff = dist, offset, coeff
+
+    def size(self, dim=None):
+        shape = (self.dist.numel(), self.offset.numel())
+        return shape if dim is None else shape[dim]
+
+    def materialize(self):
+        delta = self.dist.view(-1, 1) - self.offset.view(1, -1)
+        return torch.exp(self.coeff * torch.pow(delta, 2))
 
 
 class FactoredEdgeAttr:

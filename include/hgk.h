@@ -137,6 +137,25 @@ int hgk_edge_gather_add(float* out, int64_t ldo, const float* P, int64_t ldp,
                         const int32_t* qi, int64_t E, int32_t F, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * SchNet filter-generating network, fused (reference: hydragnn/models/
+ * SCFStack.py:259-272 = PyG GaussianSmearing -> cat with the edge attribute ->
+ * Linear -> ShiftedSoftplus -> Linear -> x cosine envelope).
+ *   X_e = [exp(coeff (d_e - offset_k)^2), k < G | raw_e[0..R)]
+ *   h_e = ssp(X_e W0'^T + b0)         [E, F]   (kept for the backward)
+ *   w_e = (h_e W1^T + b1) * 0.5 (cos(d_e pi / cutoff) + 1)        [E, F]
+ * w0p is [F, 64]: columns [0,G) gaussian weights, [G4, G4+R) raw-attribute
+ * weights (G4 = G rounded up to a multiple of 4), zeros elsewhere.  tcgen05
+ * kernel with 3xTF32 operand splitting (fp32-accurate); built for F = 128,
+ * G = 50, R in {0, 8}; other shapes return HGK_ERR_UNSUPPORTED (callers use
+ * the unfused path).
+ * ------------------------------------------------------------------------- */
+int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const float* raw,
+                          int64_t ldr, int32_t R, const float* offset,
+                          int32_t G, float coeff, float cutoff,
+                          const float* w0p, const float* b0, const float* w1,
+                          const float* b1, int64_t E, int32_t F, void* stream);
+
+/* ------------------------------------------------------------------------- *
  * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
  * DegreeScalerAggregation with aggregators mean,min,max,std).
  * h[e,:] = P[dst(e),:] + Q[src[e],:] (+ R[e,:]) is formed in registers,

@@ -207,3 +207,17 @@ def radius_graph(pos, ptr, r, max_nbr, loop, cell=None, pbc=None, mode=1):
     return (torch.from_numpy(src.astype(np.int32)), torch.from_numpy(dst.astype(np.int32)),
             torch.from_numpy(np.concatenate(shifts).astype(np.int32).reshape(-1, 3)),
             torch.from_numpy(np.concatenate(dists).astype(np.float64)), torch.from_numpy(rowptr))
+
+
+# hgk_schnet_filter_fwd -- GaussianSmearing -> cat -> Linear -> ShiftedSoftplus -> Linear -> cosine
+# envelope, exactly the op sequence of CFConv.forward (SCFStack.py:259-272) on the unfolded inputs
+def schnet_filter_fwd(dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
+    delta = dist.view(-1, 1) - offset.view(1, -1)
+    feats = torch.exp(coeff * torch.pow(delta, 2))
+    weight = w0g
+    if raw is not None:
+        feats = torch.cat([feats, raw], dim=-1)
+        weight = torch.cat([w0g, w0r], dim=1)
+    h = torch.nn.functional.softplus(torch.nn.functional.linear(feats, weight, b0)) - math.log(2.0)
+    env = 0.5 * (torch.cos(dist * math.pi / cutoff) + 1.0)
+    return torch.nn.functional.linear(h, w1, b1) * env.view(-1, 1), h

@@ -332,3 +332,36 @@ def test_radius_graph_fesi_full_size_properties(ops):
     key = lambda s, t, S: ((s * 8192 + t) * 27 + (S[:, 0] + 1) * 9 + (S[:, 1] + 1) * 3 + (S[:, 2] + 1))
     S = g["shift_int"].long()
     assert torch.equal(torch.sort(key(src, dst, S)).values, torch.sort(key(dst, src, -S)).values)
+
+
+# ------------------------------------------------------------- fused SchNet filter ---
+@pytest.mark.parametrize("E,R", [(1, 8), (127, 8), (1000, 0), (40000, 8)])
+def test_schnet_filter_fwd(ops, E, R):
+    """tcgen05 3xTF32 kernel vs the reference op sequence in fp32 on the CPU (and fp64 as the truth):
+    the kernel must be as close to fp64 as the fp32 CPU path is, within rel 1e-5 of it."""
+    from hydragnn.ops import filter as filt
+
+    gen = torch.Generator().manual_seed(E + R)
+    F, G, cutoff = 128, 50, 5.0
+    dist = torch.rand(E, generator=gen) * 4.9 + 0.05
+    raw = torch.rand(E, R, generator=gen) * 0.2 if R else None
+    offset = torch.linspace(0.0, cutoff, G)
+    coeff = -0.5 / float(offset[1] - offset[0]) ** 2
+    w0g = torch.randn(F, G, generator=gen) / G ** 0.5
+    w0r = torch.randn(F, R, generator=gen) if R else None
+    b0, b1 = torch.randn(F, generator=gen) * 0.1, torch.randn(F, generator=gen) * 0.1
+    w1 = torch.randn(F, F, generator=gen) / F ** 0.5
+    dev = lambda t: None if t is None else t.to(DEV)
+    w0p = torch.zeros(F, 64)
+    w0p[:, :G] = w0g
+    if R:
+        w0p[:, 52:52 + R] = w0r
+    w, h = filt._filter_fwd_raw(dev(dist), dev(raw), dev(offset), coeff, cutoff, dev(w0p), dev(b0), dev(w1), dev(b1))
+    w_ref, h_ref = ks.schnet_filter_fwd(dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1)
+    torch.testing.assert_close(h.cpu(), h_ref, rtol=1e-5, atol=2e-6)
+    torch.testing.assert_close(w.cpu(), w_ref, rtol=1e-5, atol=2e-6)
+    dd = lambda t: None if t is None else t.double()
+    w64, _ = ks.schnet_filter_fwd(dd(dist), dd(raw), dd(offset), coeff, cutoff, dd(w0g), dd(w0r), dd(b0), dd(w1), dd(b1))
+    err_kernel = (w.cpu().double() - w64).abs().max().item()
+    err_cpu32 = (w_ref.double() - w64).abs().max().item()
+    assert err_kernel < 4 * err_cpu32 + 1e-6, (err_kernel, err_cpu32)
