@@ -201,6 +201,245 @@ k_schnet_filter_fwd(const FilterArgs p) {
   cta_teardown(tmem, kCols);
 }
 
+
+// ================================================================================== backward ===
+// dZ1 = gW * C(d);  dH = dZ1 W1;  dZ0 = dH * ssp'(Z0),  ssp'(z) = sigmoid(z) = 1 - exp(-(H + ln 2)).
+// One persistent CTA per SM walks 128-edge tiles: dZ1 (hi, lo) goes to TMEM as the A operand,
+// W1^T (hi, lo) is resident in shared memory, dZ0 is written to HBM for the weight-gradient kernel.
+struct FilterBwdArgs {
+  const float* gw;     // [E, 128] gradient of the filter
+  const float* h;      // [E, 128] saved hidden activations
+  const float* d;      // [E]
+  float pi_over_cutoff;
+  const float* w1t;    // [128, 128] = W1^T (row = input feature, column = output filter)
+  float* dz0;          // [E, 128] out
+  int64_t E;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+k_schnet_filter_bwd(const FilterBwdArgs p) {
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  float* Whi = smem;
+  float* Wlo = Whi + kFilt * kFilt;
+  constexpr uint32_t kCols = 512;
+  constexpr uint32_t kColAhi = 0, kColAlo = 128, kColDH = 256;
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
+  const int warp_u = warp_id_uniform();
+  {
+    Tile<kFilt, kFilt> t;
+    t.load(p.w1t, kFilt, 0, kFilt);
+    t.store_rows(Whi, Wlo);
+  }
+  const OperandDesc dW = operand_desc<kFilt>(Whi, Wlo);
+  constexpr uint32_t kIdesc = idesc_tf32(kFilt, kFilt);
+  publish_operands();
+
+  uint32_t parity = 0;
+  const int64_t num_tiles = (p.E + kFilt - 1) / kFilt;
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int64_t e = tile * kFilt + cs.row_local;
+    const bool ok = e < p.E;
+    const float dist = ok ? __ldg(p.d + e) : 0.f;
+    const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);
+    const float* grow = p.gw + e * kFilt + cs.half * 64;
+#pragma unroll
+    for (int part = 0; part < 2; ++part) {
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) g = ld_stream4(grow + part * 32 + j);
+        const float x[4] = {g.x * env, g.y * env, g.z * env, g.w * env};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float h_, l_;
+          split_tf32(x[i], h_, l_);
+          hi[j + i] = __float_as_uint(h_);
+          lo[j + i] = __float_as_uint(l_);
+        }
+      }
+      const int c0 = cs.half * 64 + part * 32;
+      tmem_st32(tmem + cs.lane_base + kColAhi + c0, hi);
+      tmem_st32(tmem + cs.lane_base + kColAlo + c0, lo);
+    }
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+    if (warp_u == 0 && elect_one_sync()) {
+      fence_after_sync();
+      mma3_ts<kFilt>(tmem + kColDH, tmem + kColAhi, tmem + kColAlo, dW, kIdesc, false);   // dH = dZ1 W1
+      mma_commit(&bar);
+    }
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+
+    const float* hrow = p.h + e * kFilt + cs.half * 64;
+    float* orow = p.dz0 + e * kFilt + cs.half * 64;
+#pragma unroll
+    for (int part = 0; part < 2; ++part) {
+      uint32_t dh[32];
+      tmem_ld32(tmem + cs.lane_base + kColDH + cs.half * 64 + part * 32, dh);
+      tmem_ld_wait();
+      if (ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 hv = ld_stream4(hrow + part * 32 + j);
+          float4 o;
+          o.x = __uint_as_float(dh[j]) * (1.f - fast_exp2(-(hv.x + kLn2) * kLog2e));
+          o.y = __uint_as_float(dh[j + 1]) * (1.f - fast_exp2(-(hv.y + kLn2) * kLog2e));
+          o.z = __uint_as_float(dh[j + 2]) * (1.f - fast_exp2(-(hv.z + kLn2) * kLog2e));
+          o.w = __uint_as_float(dh[j + 3]) * (1.f - fast_exp2(-(hv.w + kLn2) * kLog2e));
+          *reinterpret_cast<float4*>(orow + part * 32 + j) = o;
+        }
+      }
+    }
+    // the next tile's barrier after its TMEM stores orders these dH reads before the next MMA
+  }
+  cta_teardown(tmem, kCols);
+}
+
+// ---- weight gradients: dW[n, k] = sum_e A[e, n] B[e, k],  db[n] = sum_e A[e, n] ----------------------
+// A = rows of [E, 128] (optionally scaled per row by the cosine envelope of d_e); B = rows of
+// [E, KB], or, with GAUSS, the filter network's input [gauss(d_e) | raw_e] rebuilt on the fly.
+// Each CTA reduces its share of 64-edge tiles into a TMEM accumulator and writes ONE partial; the
+// partials are summed in a fixed order afterwards (deterministic, no atomics).
+struct WgradArgs {
+  const float* a;            // [E, 128]
+  const float* scale_d;      // [E] or NULL: multiply row e of A by 0.5 (cos(d_e pi / r_c) + 1)
+  float pi_over_cutoff;
+  const float* b; int64_t ldb;                      // [E, KB] (GAUSS == false)
+  const float* d; const float* raw; int64_t ldr;    // GAUSS == true
+  const float* offset; float coeff;
+  float* dw_partial;         // [gridDim.x, 128, KB]
+  float* db_partial;         // [gridDim.x, 128]
+  int64_t E;
+};
+
+template <int KB, bool GAUSS, int G, int R>
+__global__ void __launch_bounds__(kThreads, 1)
+k_wgrad_tn(const WgradArgs p) {
+  constexpr int BE = 64;                               // edges per iteration (the MMA K extent)
+  constexpr int GP = (G + 3) / 4 * 4;
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ float off_s[64];
+  float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
+  float* BThi = ATlo + kFilt * BE;   float* BTlo = BThi + KB * BE;
+  constexpr uint32_t kCols = KB < 32 ? 32 : KB;
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
+  const int warp_u = warp_id_uniform();
+  if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
+  __syncthreads();
+
+  const OperandDesc dA = operand_desc<BE>(AThi, ATlo), dB = operand_desc<BE>(BThi, BTlo);
+  constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB);
+  Tile<BE, kFilt> ta;
+  Tile<BE, KB> tb;
+  float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);     // this thread's 4 columns of A, summed over its rows
+  const float c2 = p.coeff * kLog2e;
+
+  auto fetch = [&](int64_t tile) {
+    const int32_t row0 = (int32_t)(tile * BE);
+    const int32_t row_end = (int32_t)p.E;
+    ta.load(p.a, kFilt, row0, row_end);
+    if (p.scale_d != nullptr) {
+#pragma unroll
+      for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
+        int r, c;
+        Tile<BE, kFilt>::coord(it, r, c);
+        const float dd = (row0 + r < row_end) ? __ldg(p.scale_d + row0 + r) : 0.f;
+        const float env = 0.5f * (__cosf(dd * p.pi_over_cutoff) + 1.0f);
+        ta.v[it].x *= env; ta.v[it].y *= env; ta.v[it].z *= env; ta.v[it].w *= env;
+      }
+    }
+    if (!GAUSS) {
+      tb.load(p.b, p.ldb, row0, row_end);
+    } else {
+#pragma unroll
+      for (int it = 0; it < Tile<BE, KB>::PER; ++it) {
+        int r, c;
+        Tile<BE, KB>::coord(it, r, c);
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t e = (int64_t)row0 + r;
+        if (e < p.E) {
+          const int k0 = 4 * c;
+          if (k0 < G) {
+            const float dd = __ldg(p.d + e);
+            float g[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float t = dd - off_s[k0 + i];
+              g[i] = (k0 + i < G) ? fast_exp2(c2 * (t * t)) : 0.f;
+            }
+            x = make_float4(g[0], g[1], g[2], g[3]);
+          } else if (R > 0 && k0 >= GP && k0 < GP + R) {
+            x = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + (k0 - GP)));
+          }
+        }
+        tb.v[it] = x;
+      }
+    }
+  };
+
+  const int64_t num_tiles = (p.E + BE - 1) / BE;
+  uint32_t parity = 0;
+  bool first = true;
+  if ((int64_t)blockIdx.x < num_tiles) fetch(blockIdx.x);
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+#pragma unroll
+    for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
+      colsum.x += ta.v[it].x; colsum.y += ta.v[it].y; colsum.z += ta.v[it].z; colsum.w += ta.v[it].w;
+    }
+    ta.store_transposed(AThi, ATlo);
+    tb.store_transposed(BThi, BTlo);
+    publish_operands();
+    if (warp_u == 0 && elect_one_sync()) {
+      fence_after_sync();
+      mma3_ss<BE>(tmem, dA, dB, kIdesc, !first);
+      mma_commit(&bar);
+    }
+    first = false;
+    if (tile + gridDim.x < num_tiles) fetch(tile + gridDim.x);
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+  }
+
+  // ---- partial dW: lane n, this thread's KB/2 columns ----
+  float* out = p.dw_partial + ((int64_t)blockIdx.x * kFilt + cs.row_local) * KB + cs.half * (KB / 2);
+  const bool any = (int64_t)blockIdx.x < num_tiles;
+#pragma unroll
+  for (int c0 = 0; c0 < KB / 2; c0 += 32) {
+    uint32_t t[32];
+    tmem_ld32(tmem + cs.lane_base + cs.half * (KB / 2) + c0, t);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+      *reinterpret_cast<float4*>(out + c0 + j) =
+          any ? make_float4(__uint_as_float(t[j]), __uint_as_float(t[j + 1]), __uint_as_float(t[j + 2]), __uint_as_float(t[j + 3]))
+              : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  // ---- partial db: the 8 lanes that share a 16-byte column add up their rows ----
+#pragma unroll
+  for (int off = 1; off < 8; off <<= 1) {
+    colsum.x += __shfl_xor_sync(0xffffffffu, colsum.x, off);
+    colsum.y += __shfl_xor_sync(0xffffffffu, colsum.y, off);
+    colsum.z += __shfl_xor_sync(0xffffffffu, colsum.z, off);
+    colsum.w += __shfl_xor_sync(0xffffffffu, colsum.w, off);
+  }
+  if ((threadIdx.x & 7) == 0) {
+    const int c = (threadIdx.x >> 3) % (kFilt / 4);
+    *reinterpret_cast<float4*>(p.db_partial + (int64_t)blockIdx.x * kFilt + 4 * c) = colsum;
+  }
+  cta_teardown(tmem, kCols);
+}
+
 }  // namespace tc
 }  // namespace hgk
 
@@ -235,4 +474,57 @@ extern "C" int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const f
     tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kThreads, smem, st>>>(a);
   }
   return check_launch("schnet_filter_fwd");
+}
+
+extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h, const float* d,
+                                     float cutoff, const float* w1t, int64_t E, int32_t F, void* stream) {
+  HGK_REQUIRE(E >= 0, "schnet_filter_bwd: negative E");
+  if (E == 0) return HGK_OK;
+  HGK_REQUIRE(dz0 && gw && h && d && w1t, "schnet_filter_bwd: NULL operand");
+  if (F != tc::kFilt) return fail(HGK_ERR_UNSUPPORTED, "schnet_filter_bwd: built for F=128 (got %d)", F);
+  tc::FilterBwdArgs a{gw, h, d, 3.14159265358979323846f / cutoff, w1t, dz0, E};
+  const size_t smem = sizeof(float) * 2 * tc::kFilt * tc::kFilt;
+  cudaError_t err = cudaFuncSetAttribute(tc::k_schnet_filter_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_bwd: smem opt-in: %s", cudaGetErrorString(err));
+  const unsigned grid = (unsigned)imin64(ceil_div(E, tc::kFilt), kNumSM);
+  tc::k_schnet_filter_bwd<<<grid, tc::kThreads, smem, (cudaStream_t)stream>>>(a);
+  return check_launch("schnet_filter_bwd");
+}
+
+extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
+  if (E <= 0) return 0;
+  return imin64(ceil_div(E, 64), kNumSM);
+}
+
+extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, const float* scale_d,
+                            float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
+                            const float* raw, int64_t ldr, int32_t R, const float* offset, int32_t G,
+                            float coeff, int64_t E, int32_t F, void* stream) {
+  HGK_REQUIRE(E >= 0, "wgrad_tn: negative E");
+  if (E == 0) return HGK_OK;
+  HGK_REQUIRE(dw_partial && db_partial && a, "wgrad_tn: NULL operand");
+  if (F != tc::kFilt) return fail(HGK_ERR_UNSUPPORTED, "wgrad_tn: built for 128-wide A (got %d)", F);
+  const bool gauss = (b == nullptr);
+  if (gauss) {
+    HGK_REQUIRE(d && offset && (R == 0 || raw), "wgrad_tn: gaussian input needs d / offset / raw");
+    if (KB != 64 || G != 50 || !(R == 0 || R == 8))
+      return fail(HGK_ERR_UNSUPPORTED, "wgrad_tn: gaussian input built for KB=64, G=50, R in {0,8}");
+  } else {
+    if (KB != 128) return fail(HGK_ERR_UNSUPPORTED, "wgrad_tn: built for KB=128 (got %d)", KB);
+    HGK_REQUIRE(ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0, "wgrad_tn: B rows must be 16-byte aligned");
+  }
+  tc::WgradArgs args{a, scale_d, 3.14159265358979323846f / cutoff, b, ldb, d, raw, ldr, offset, coeff,
+                     dw_partial, db_partial, E};
+  const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
+  cudaStream_t st = (cudaStream_t)stream;
+  auto launch = [&](auto kernel, int kb) -> int {
+    const size_t smem = sizeof(float) * 2 * 64 * (tc::kFilt + kb);
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
+    kernel<<<grid, tc::kThreads, smem, st>>>(args);
+    return check_launch("wgrad_tn");
+  };
+  if (!gauss) return launch(tc::k_wgrad_tn<128, false, 50, 0>, 128);
+  if (R == 8) return launch(tc::k_wgrad_tn<64, true, 50, 8>, 64);
+  return launch(tc::k_wgrad_tn<64, true, 50, 0>, 64);
 }

@@ -39,6 +39,37 @@ def _filter_fwd_raw(dist, raw, offset, coeff, cutoff, w0p, b0, w1, b1):
     return w, h
 
 
+def _filter_bwd_raw(gw, h, dist, cutoff, w1t):
+    E, F = gw.shape
+    dz0 = torch.empty_like(gw)
+    _hgk.call("hgk_schnet_filter_bwd", _hgk.ptr(dz0), _hgk.ptr(gw), _hgk.ptr(h), _hgk.ptr(dist), float(cutoff),
+              _hgk.ptr(w1t), E, F, cost=(E * (12 * F + 4), 2 * E * F * F))
+    return dz0
+
+
+def _wgrad_raw(a, scale_d, cutoff, b=None, gauss=None):
+    """(dW [128, KB], db [128]) = (A^T B, colsum A); gauss = (dist, raw, offset, coeff) rebuilds B =
+    [gauss(d) | raw] on the fly (KB = 64, the padded layout of the forward kernel)."""
+    E, F = a.shape
+    L = _hgk.lib()
+    P = L.hgk_wgrad_tn_partials(E)
+    KB = 64 if b is None else b.size(1)
+    dw = torch.empty((P, F, KB), dtype=torch.float32, device=a.device)
+    db = torch.empty((P, F), dtype=torch.float32, device=a.device)
+    if b is None:
+        dist, raw, offset, coeff = gauss
+        R = 0 if raw is None else raw.size(1)
+        args = (_hgk.ptr(None), 0, KB, _hgk.ptr(dist), _hgk.ptr(raw), 0 if raw is None else raw.stride(0), R,
+                _hgk.ptr(offset), offset.numel(), float(coeff))
+        nbytes = E * (4 * F + 4 + 4 * R)
+    else:
+        args = (_hgk.ptr(b), b.stride(0), KB, _hgk.ptr(None), _hgk.ptr(None), 0, 0, _hgk.ptr(None), 0, 0.0)
+        nbytes = E * 4 * (F + KB)
+    _hgk.call("hgk_wgrad_tn", _hgk.ptr(dw), _hgk.ptr(db), _hgk.ptr(a), _hgk.ptr(scale_d), float(cutoff), *args,
+              E, F, cost=(nbytes, 2 * E * F * KB))
+    return dw.sum(0), db.sum(0)        # fixed-order reduction of the per-CTA partials
+
+
 class SchnetFilter(torch.autograd.Function):
     @staticmethod
     def forward(ctx, dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
@@ -60,15 +91,14 @@ class SchnetFilter(torch.autograd.Function):
     @torch.autograd.function.once_differentiable
     def backward(ctx, gw):
         dist, raw, offset, h, w1 = ctx.saved_tensors
-        env = 0.5 * (torch.cos(dist * math.pi / ctx.cutoff) + 1.0)
-        dz1 = gw * env.view(-1, 1)
-        gb1 = dz1.sum(0)
-        gw1 = dz1.t() @ h
-        dz0 = (dz1 @ w1) * (1.0 - torch.exp(-(h + _LN2)))          # ssp'(z) = sigmoid(z) = 1 - exp(-softplus(z))
-        gb0 = dz0.sum(0)
-        delta = dist.view(-1, 1) - offset.view(1, -1)
-        gw0g = dz0.t() @ torch.exp(ctx.coeff * delta * delta)
-        gw0r = dz0.t() @ raw if raw is not None else None
+        gw = gw.contiguous()
+        G = offset.numel()
+        GP = (G + 3) // 4 * 4
+        dz0 = _filter_bwd_raw(gw, h, dist, ctx.cutoff, w1.t().contiguous())
+        gw1, gb1 = _wgrad_raw(gw, dist, ctx.cutoff, b=h)                        # dZ1 = gw * envelope(d)
+        gw0p, gb0 = _wgrad_raw(dz0, None, ctx.cutoff, gauss=(dist, raw, offset, ctx.coeff))
+        gw0g = gw0p[:, :G]
+        gw0r = gw0p[:, GP:GP + raw.size(1)] if raw is not None else None
         return None, None, None, None, None, gw0g, gw0r, gb0, gw1, gb1
 
 

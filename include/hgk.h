@@ -155,6 +155,28 @@ int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const float* raw,
                           const float* w0p, const float* b0, const float* w1,
                           const float* b1, int64_t E, int32_t F, void* stream);
 
+/* Backward of the fused filter network (reference: autograd through
+ * SCFStack.py:268-272).  Given gw = dL/dw [E,F], the saved h and W1^T:
+ *   dz1 = gw * envelope(d);  dh = dz1 W1;  dz0 = dh * (1 - exp(-(h + ln 2)))
+ * writes dz0 [E,F] (the gradient at the first Linear's output). */
+int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h,
+                          const float* d, float cutoff, const float* w1t,
+                          int64_t E, int32_t F, void* stream);
+/* Weight / bias gradients of an edge-row Linear (reference: autograd of
+ * nn.Linear on [E, .] inputs):  dW[n,k] = sum_e A[e,n] B[e,k],  db[n] =
+ * sum_e A[e,n].  A is [E,128], optionally scaled per row by envelope(scale_d);
+ * B is [E,KB] (KB = 128), or, with b == NULL, the filter network's input
+ * [gauss(d) | raw] in the 64-column layout of hgk_schnet_filter_fwd.
+ * Each of the P = hgk_wgrad_tn_partials(E) CTAs writes one partial:
+ * dw_partial [P,128,KB], db_partial [P,128]; summing the partials over P (in
+ * order) gives the result -- deterministic, no atomics. */
+int64_t hgk_wgrad_tn_partials(int64_t E);
+int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a,
+                 const float* scale_d, float cutoff, const float* b, int64_t ldb,
+                 int32_t KB, const float* d, const float* raw, int64_t ldr,
+                 int32_t R, const float* offset, int32_t G, float coeff,
+                 int64_t E, int32_t F, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
  * DegreeScalerAggregation with aggregators mean,min,max,std).

@@ -365,3 +365,37 @@ def test_schnet_filter_fwd(ops, E, R):
     err_kernel = (w.cpu().double() - w64).abs().max().item()
     err_cpu32 = (w_ref.double() - w64).abs().max().item()
     assert err_kernel < 4 * err_cpu32 + 1e-6, (err_kernel, err_cpu32)
+
+
+@pytest.mark.parametrize("E,R", [(70, 8), (5000, 0), (40000, 8)])
+def test_schnet_filter_backward_kernels(ops, E, R):
+    """hgk_schnet_filter_bwd + hgk_wgrad_tn (through the autograd Function) vs torch autograd of the
+    reference op sequence on the CPU."""
+    from hydragnn.ops import filter as filt
+
+    gen = torch.Generator().manual_seed(E * 3 + R)
+    F, G, cutoff = 128, 50, 5.0
+    dist = torch.rand(E, generator=gen) * 4.9 + 0.05
+    raw = torch.rand(E, R, generator=gen) * 0.2 if R else None
+    offset = torch.linspace(0.0, cutoff, G)
+    coeff = -0.5 / float(offset[1] - offset[0]) ** 2
+    params = [torch.randn(F, G, generator=gen) / G ** 0.5, torch.randn(F, max(R, 1), generator=gen),
+              torch.randn(F, generator=gen) * 0.1, torch.randn(F, F, generator=gen) / F ** 0.5,
+              torch.randn(F, generator=gen) * 0.1]
+    gout = torch.randn(E, F, generator=gen) / E ** 0.5
+
+    cpu = [t.clone().requires_grad_(True) for t in params]
+    w_ref, _ = ks.schnet_filter_fwd(dist, raw, offset, coeff, cutoff, cpu[0], cpu[1][:, :R] if R else None,
+                                    cpu[2], cpu[3], cpu[4])
+    w_ref.backward(gout)
+
+    dev = lambda t: None if t is None else t.to(DEV)
+    gpu = [t.clone().to(DEV).requires_grad_(True) for t in params]
+    w = filt.schnet_filter(dev(dist), dev(raw), dev(offset), coeff, cutoff, gpu[0], gpu[1][:, :R] if R else None,
+                           gpu[2], gpu[3], gpu[4])
+    w.backward(dev(gout))
+    for k, (g, c) in enumerate(zip(gpu, cpu)):
+        if k == 1 and not R:
+            continue
+        scale = float(c.grad.abs().max())
+        torch.testing.assert_close(g.grad.cpu(), c.grad, rtol=1e-4, atol=1e-5 * max(scale, 1.0), msg=lambda m, k=k: f"param {k}: {m}")
