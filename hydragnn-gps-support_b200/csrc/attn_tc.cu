@@ -317,16 +317,23 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
-  __shared__ float lse2_s[BQ], delta_s[BQ];
+  __shared__ float lse2_s[2][BQ], delta_s[2][BQ];
   int32_t seg_beg, seg_end, key0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
   const int h = blockIdx.y;
   const int warp_u = warp_id_uniform();
 
-  float* Qhi = smem;             float* Qlo = Qhi + BQ * D;      // rows = queries (B of S^T)
-  float* Ghi = Qlo + BQ * D;     float* Glo = Ghi + BQ * D;      // dO rows        (B of dP^T)
-  float* QThi = Glo + BQ * D;    float* QTlo = QThi + BQ * D;    // Q^T [D x BQ]   (B of dK)
-  float* GThi = QTlo + BQ * D;   float* GTlo = GThi + BQ * D;    // dO^T [D x BQ]  (B of dV)
+  // two shared-memory stages of the per-iteration operands: stage (it+1) is written while the
+  // second MMA batch of iteration `it` is still running
+  constexpr int kStage = 8 * BQ * D;                   // floats per stage
+  auto Qhi = [&](int st) { return smem + st * kStage; };                 // rows = queries (B of S^T)
+  auto Qlo = [&](int st) { return smem + st * kStage + 1 * BQ * D; };
+  auto Ghi = [&](int st) { return smem + st * kStage + 2 * BQ * D; };    // dO rows        (B of dP^T)
+  auto Glo = [&](int st) { return smem + st * kStage + 3 * BQ * D; };
+  auto QThi = [&](int st) { return smem + st * kStage + 4 * BQ * D; };   // Q^T [D x BQ]   (B of dK)
+  auto QTlo = [&](int st) { return smem + st * kStage + 5 * BQ * D; };
+  auto GThi = [&](int st) { return smem + st * kStage + 6 * BQ * D; };   // dO^T [D x BQ]  (B of dV)
+  auto GTlo = [&](int st) { return smem + st * kStage + 7 * BQ * D; };
 
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
@@ -342,8 +349,10 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, cs.half, 1.f);
     row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, cs.half, 1.f);
   }
-  const OperandDesc dQ = operand_desc<D>(Qhi, Qlo), dG = operand_desc<D>(Ghi, Glo);
-  const OperandDesc dQt = operand_desc<BQ>(QThi, QTlo), dGt = operand_desc<BQ>(GThi, GTlo);
+  const OperandDesc dQ[2] = {operand_desc<D>(Qhi(0), Qlo(0)), operand_desc<D>(Qhi(1), Qlo(1))};
+  const OperandDesc dG[2] = {operand_desc<D>(Ghi(0), Glo(0)), operand_desc<D>(Ghi(1), Glo(1))};
+  const OperandDesc dQt[2] = {operand_desc<BQ>(QThi(0), QTlo(0)), operand_desc<BQ>(QThi(1), QTlo(1))};
+  const OperandDesc dGt[2] = {operand_desc<BQ>(GThi(0), GTlo(0)), operand_desc<BQ>(GThi(1), GTlo(1))};
   Tile<BQ, D> tq, tg;                                  // next query / dO tile, prefetched in registers
   tq.load(p.q + h * D, p.ldq, seg_beg, seg_end);
   tg.load(b.dout + h * D, b.lddo, seg_beg, seg_end);
@@ -354,26 +363,33 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   uint32_t parity = 0;
   bool first = true;
 
-  for (int32_t q0 = seg_beg; q0 < seg_end; q0 += BQ) {
+  // registers (tile starting at query q_at) -> shared-memory stage st
+  auto stage = [&](int st, int32_t q_at) {
     tq.scale(qmul);
-    tq.store_rows(Qhi, Qlo);
-    tq.store_transposed(QThi, QTlo);
-    tg.store_rows(Ghi, Glo);
-    tg.store_transposed(GThi, GTlo);
+    tq.store_rows(Qhi(st), Qlo(st));
+    tq.store_transposed(QThi(st), QTlo(st));
+    tg.store_rows(Ghi(st), Glo(st));
+    tg.store_transposed(GThi(st), GTlo(st));
     if (threadIdx.x < BQ) {
-      const int32_t qrow = q0 + (int32_t)threadIdx.x;
+      const int32_t qrow = q_at + (int32_t)threadIdx.x;
       const bool ok = qrow < seg_end;
-      lse2_s[threadIdx.x] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
-      delta_s[threadIdx.x] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
+      lse2_s[st][threadIdx.x] = ok ? b.lse[(int64_t)qrow * p.H + h] * kLog2e : 0.f;
+      delta_s[st][threadIdx.x] = ok ? b.delta[(int64_t)qrow * p.H + h] : 0.f;
     }
-    publish_operands();
+  };
+  stage(0, seg_beg);
+
+  int st = 0;
+  for (int32_t q0 = seg_beg; q0 < seg_end; q0 += BQ, st ^= 1) {
+    const bool has_next = q0 + BQ < seg_end;
+    publish_operands();                                // stage `st` is complete and visible
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ts<D>(tmem + kColST, tmem + kColKhi, tmem + kColKlo, dQ, kIdescS, false);    // S^T  = K Q^T
-      mma3_ts<D>(tmem + kColDPT, tmem + kColVhi, tmem + kColVlo, dG, kIdescS, false);   // dP^T = V dO^T
+      mma3_ts<D>(tmem + kColST, tmem + kColKhi, tmem + kColKlo, dQ[st], kIdescS, false);    // S^T  = K Q^T
+      mma3_ts<D>(tmem + kColDPT, tmem + kColVhi, tmem + kColVlo, dG[st], kIdescS, false);   // dP^T = V dO^T
       mma_commit(&bar);
     }
-    if (q0 + BQ < seg_end) {
+    if (has_next) {                                    // global loads of the next tile fly under the MMAs
       tq.load(p.q + h * D, p.ldq, q0 + BQ, seg_end);
       tg.load(b.dout + h * D, b.lddo, q0 + BQ, seg_end);
     }
@@ -389,9 +405,9 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     tmem_ld_wait();
 #pragma unroll
     for (int j = 0; j < HALF; ++j) {
-      float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[col0 + j]);
+      float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[st][col0 + j]);
       if (j >= nvalid) pj = 0.f;
-      const float ds = pj * (__uint_as_float(dp[j]) - delta_s[col0 + j]);
+      const float ds = pj * (__uint_as_float(dp[j]) - delta_s[st][col0 + j]);
       float hi_, lo_;
       split_tf32(pj, hi_, lo_);
       sv[j] = __float_as_uint(hi_); plo[j] = __float_as_uint(lo_);
@@ -407,11 +423,12 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     __syncthreads();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, dGt, kIdescD, !first);           // dV += P^T dO
-      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, dQt, kIdescD, !first);         // dK += dS^T Q
+      mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, dGt[st], kIdescD, !first);       // dV += P^T dO
+      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, dQt[st], kIdescD, !first);     // dK += dS^T Q
       mma_commit(&bar);
     }
     first = false;
+    if (has_next) stage(st ^ 1, q0 + BQ);              // overlaps the MMAs just issued
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
@@ -472,7 +489,7 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
                cudaStream_t st) {
   dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
   // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
-  size_t smem_kv = sizeof(float) * (8 * BN * D);
+  size_t smem_kv = sizeof(float) * (2 * 8 * BN * D);
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
   int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
   if (rc) return rc;
