@@ -51,7 +51,7 @@ def parse_args():
 
 # --------------------------------------------------------------------------- clocks ---
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -64,7 +64,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
-                 "--format=csv,noheader,nounits", "-lms", "200"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -345,10 +345,22 @@ def run_b200(args):
     }
     if table:
         top = table[0]
+        measured = {}
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+                measured = json.load(fh).get(args.workload, {}).get(top["entry"], {})
+        except Exception:
+            pass
         result["roofline"] = {"kernel": top["entry"], "bound": top["bound"], "achieved": top["achieved"],
                               "peak": top["peak"], "unit": top["unit"], "frac": top["frac"],
-                              "peak_source": peaks["source"], "traffic": None,
+                              "peak_source": peaks["source"], "traffic": measured.get("traffic_bytes"),
                               "bytes_per_launch": top["bytes_per_launch"]}
+        if top["bound"] == "tensor":
+            # fp32 parity forces 3xTF32: 3 MMAs per algorithmic product on a pipe that runs tf32 at half
+            # the bf16 rate the peak was measured with -> the reachable ceiling is peak / 6
+            result["roofline"]["effective_peak"] = top["peak"] / 6.0
+            result["roofline"]["frac_of_effective_peak"] = top["achieved"] / (top["peak"] / 6.0)
+            result["roofline"]["tensor_pipe_active_pct"] = measured.get("tensor_pipe_active_pct")
         result["kernels"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()
                               if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs", "tflops", "frac")}
                              for r in table]
