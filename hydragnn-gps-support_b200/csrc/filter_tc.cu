@@ -322,14 +322,18 @@ struct WgradArgs {
 template <int KB, bool GAUSS, int G, int R>
 __global__ void __launch_bounds__(kThreads, 1)
 k_wgrad_tn(const WgradArgs p) {
-  constexpr int BE = 64;                               // edges per iteration (the MMA K extent)
+  constexpr int BE = 32;                               // edges per iteration (the MMA K extent)
   constexpr int GP = (G + 3) / 4 * 4;
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float off_s[64];
-  float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
-  float* BThi = ATlo + kFilt * BE;   float* BTlo = BThi + KB * BE;
+  // two stages of transposed operands: stage (it+1) is written while the MMAs of `it` run
+  constexpr int kStage = 2 * BE * (kFilt + KB);
+  auto AThi = [&](int st) { return smem + st * kStage; };
+  auto ATlo = [&](int st) { return smem + st * kStage + kFilt * BE; };
+  auto BThi = [&](int st) { return smem + st * kStage + 2 * kFilt * BE; };
+  auto BTlo = [&](int st) { return smem + st * kStage + 2 * kFilt * BE + KB * BE; };
   constexpr uint32_t kCols = KB < 32 ? 32 : KB;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
@@ -337,14 +341,15 @@ k_wgrad_tn(const WgradArgs p) {
   if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
   __syncthreads();
 
-  const OperandDesc dA = operand_desc<BE>(AThi, ATlo), dB = operand_desc<BE>(BThi, BTlo);
+  const OperandDesc dA0 = operand_desc<BE>(AThi(0), ATlo(0)), dA1 = operand_desc<BE>(AThi(1), ATlo(1));
+  const OperandDesc dB0 = operand_desc<BE>(BThi(0), BTlo(0)), dB1 = operand_desc<BE>(BThi(1), BTlo(1));
   constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB);
-  Tile<BE, kFilt> ta;
-  Tile<BE, KB> tb;
+  Tile<BE, kFilt> ta0, ta1;                            // two register sets: loads run two tiles ahead
+  Tile<BE, KB> tb0, tb1;
   float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);     // this thread's 4 columns of A, summed over its rows
   const float c2 = p.coeff * kLog2e;
 
-  auto fetch = [&](int64_t tile) {
+  auto fetch = [&](Tile<BE, kFilt>& ta, Tile<BE, KB>& tb, int64_t tile) {
     const int32_t row0 = (int32_t)(tile * BE);
     const int32_t row_end = (int32_t)p.E;
     ta.load(p.a, kFilt, row0, row_end);
@@ -386,29 +391,50 @@ k_wgrad_tn(const WgradArgs p) {
       }
     }
   };
-
-  const int64_t num_tiles = (p.E + BE - 1) / BE;
-  uint32_t parity = 0;
-  bool first = true;
-  if ((int64_t)blockIdx.x < num_tiles) fetch(blockIdx.x);
-  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  // registers -> stage st (and the bias-gradient partial sums of A)
+  auto stage = [&](const Tile<BE, kFilt>& ta, const Tile<BE, KB>& tb, int st) {
 #pragma unroll
     for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
       colsum.x += ta.v[it].x; colsum.y += ta.v[it].y; colsum.z += ta.v[it].z; colsum.w += ta.v[it].w;
     }
-    ta.store_transposed(AThi, ATlo);
-    tb.store_transposed(BThi, BTlo);
-    publish_operands();
+    ta.store_transposed(AThi(st), ATlo(st));
+    tb.store_transposed(BThi(st), BTlo(st));
+  };
+
+  const int64_t num_tiles = (p.E + BE - 1) / BE;
+  const int64_t stride = gridDim.x;
+  uint32_t parity = 0;
+  bool first = true;
+  int st = 0;
+  // one iteration: MMAs on stage `st` (tile), meanwhile registers `ra/rb` (tile + stride) -> stage
+  // st^1 and the loads of tile + 3 stride are issued into the same registers
+  auto iterate = [&](Tile<BE, kFilt>& ra, Tile<BE, KB>& rb, int64_t tile) {
+    publish_operands();                                // stage `st` complete and visible
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<BE>(tmem, dA, dB, kIdesc, !first);
+      mma3_ss<BE>(tmem, st ? dA1 : dA0, st ? dB1 : dB0, kIdesc, !first);
       mma_commit(&bar);
     }
     first = false;
-    if (tile + gridDim.x < num_tiles) fetch(tile + gridDim.x);
+    if (tile + stride < num_tiles) {
+      stage(ra, rb, st ^ 1);
+      if (tile + 3 * stride < num_tiles) fetch(ra, rb, tile + 3 * stride);
+    }
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
+    st ^= 1;
+  };
+  const int64_t t0 = blockIdx.x;
+  if (t0 < num_tiles) {
+    fetch(ta0, tb0, t0);
+    stage(ta0, tb0, 0);
+    if (t0 + stride < num_tiles) fetch(ta1, tb1, t0 + stride);
+    if (t0 + 2 * stride < num_tiles) fetch(ta0, tb0, t0 + 2 * stride);
+  }
+  for (int64_t tile = t0; tile < num_tiles; tile += 2 * stride) {
+    iterate(ta1, tb1, tile);                           // registers 1 hold tile + stride
+    if (tile + stride < num_tiles) iterate(ta0, tb0, tile + stride);   // registers 0 hold tile + 2 stride
   }
 
   // ---- partial dW: lane n, this thread's KB/2 columns ----
@@ -493,7 +519,7 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   if (E <= 0) return 0;
-  return imin64(ceil_div(E, 64), kNumSM);
+  return imin64(ceil_div(E, 32), kNumSM);
 }
 
 extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, const float* scale_d,
@@ -518,7 +544,7 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
   const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
   cudaStream_t st = (cudaStream_t)stream;
   auto launch = [&](auto kernel, int kb) -> int {
-    const size_t smem = sizeof(float) * 2 * 64 * (tc::kFilt + kb);
+    const size_t smem = sizeof(float) * 2 * 2 * 32 * (tc::kFilt + kb);
     cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
     kernel<<<grid, tc::kThreads, smem, st>>>(args);

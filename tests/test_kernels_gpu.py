@@ -399,3 +399,54 @@ def test_schnet_filter_backward_kernels(ops, E, R):
             continue
         scale = float(c.grad.abs().max())
         torch.testing.assert_close(g.grad.cpu(), c.grad, rtol=1e-4, atol=1e-5 * max(scale, 1.0), msg=lambda m, k=k: f"param {k}: {m}")
+
+
+# ----------------------------------------------------------------------- edge cases ---
+def test_attn_empty_and_tiny_segments(ops):
+    """cu_seqlens with empty segments, single-node segments and a segment just over one tile."""
+    gen = torch.Generator().manual_seed(9)
+    sizes = [0, 1, 0, 129, 2, 0]
+    N, H, D = sum(sizes), 4, 32
+    cu = torch.tensor([0] + list(np.cumsum(sizes)), dtype=torch.int32)
+    q, k, v, do = (torch.randn(N, H * D, generator=gen) for _ in range(4))
+    scale = D ** -0.5
+    o, lse, *_ = ops["attention"]._attn_fwd_raw(q.to(DEV), k.to(DEV), v.to(DEV), cu.to(DEV), H, scale)
+    o_ref, lse_ref = ks.attn_varlen_fwd(q, k, v, cu, H, scale)
+    torch.testing.assert_close(o.cpu(), o_ref, rtol=1e-5, atol=2e-6)
+    torch.testing.assert_close(lse.cpu(), lse_ref, rtol=1e-5, atol=2e-6)
+    dq, dk, dv = ops["attention"]._attn_bwd_raw(do.to(DEV), o, lse, q.to(DEV), k.to(DEV), v.to(DEV), cu.to(DEV), H, scale)
+    rq, rk, rv = ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
+    for got, want in ((dq, rq), (dk, rk), (dv, rv)):
+        torch.testing.assert_close(got.cpu(), want, rtol=1e-4, atol=1e-5)
+
+
+def test_radius_graph_no_edges_and_single_atoms(ops):
+    """Graphs whose atoms are all farther apart than the cutoff, and one-atom graphs: E = 0."""
+    pos = torch.tensor([[0.0, 0, 0], [10.0, 0, 0], [0, 10.0, 0], [50.0, 50, 50]])
+    ptr = torch.tensor([0, 3, 4])
+    g = ops["ops"].radius_graph(pos.to(DEV), ptr, 2.0, 8, False)
+    assert g["edge_index"].shape == (2, 0) and int(g["rowptr"][-1]) == 0
+    cell = (torch.eye(3) * 30.0).repeat(2, 1, 1)
+    g = ops["ops"].radius_graph(pos.to(DEV), ptr, 2.0, 8, False, cell=cell, pbc=torch.ones(2, 3, dtype=torch.bool))
+    assert g["edge_index"].shape == (2, 0)
+    # one atom in a small periodic cell sees its own images (ASE semantics), never itself at S = 0
+    g = ops["ops"].radius_graph(torch.zeros(1, 3, device=DEV), torch.tensor([0, 1]), 1.5, 0, False,
+                                cell=torch.eye(3).reshape(1, 3, 3), pbc=torch.ones(1, 3, dtype=torch.bool))
+    src, dst, S, dist, _ = ks.radius_graph(torch.zeros(1, 3), torch.tensor([0, 1]), 1.5, 0, False,
+                                           torch.eye(3).reshape(1, 3, 3), torch.ones(1, 3, dtype=torch.bool), mode=0)
+    assert torch.equal(g["shift_int"].cpu(), S) and g["src"].numel() == 18      # 6 faces + 12 edges of the cube
+
+
+def test_segment_reductions_with_isolated_rows_and_long_segments(ops):
+    """Rows without edges give exact zeros; one hub row with thousands of edges keeps CPU order."""
+    gen = torch.Generator().manual_seed(4)
+    N, F = 300, 128
+    dst = torch.cat([torch.full((5000,), 7), torch.randint(100, 200, (3000,), generator=gen)])
+    src = torch.randint(0, N, (dst.numel(),), generator=gen)
+    ei = torch.stack([src, dst])
+    x, W = torch.randn(N, F, generator=gen), torch.randn(dst.numel(), F, generator=gen)
+    topo = make_topo(ops, ei, N)
+    got = ops["contract"]._node_raw(topo, 1, x.to(DEV), 0, W.to(DEV), None, 1, 1, F).cpu()
+    want = ks.contract_node(ei[1].int(), N, x, ei[0].int(), W, None, 1, 1, F)
+    assert torch.equal(got, want)
+    assert float(got[:7].abs().max()) == 0.0 and float(got[200:].abs().max()) == 0.0
