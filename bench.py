@@ -191,7 +191,8 @@ def kernel_table(summary, steps, peaks):
         sec = s["ms"] * 1e-3
         kind = ROOFLINE_KIND.get(name, "hbm")
         row = {"entry": name, "calls_per_step": s["calls"] / steps, "ms_per_step": s["ms"] / steps,
-               "bound": kind, "gbs": s["bytes"] / sec / 1e9, "tflops": s["flops"] / sec / 1e12}
+               "bound": kind, "gbs": s["bytes"] / sec / 1e9, "tflops": s["flops"] / sec / 1e12,
+               "gbs_compulsory": s["dram_bytes"] / sec / 1e9}
         if kind == "hbm":
             row.update(achieved=row["gbs"], peak=peaks["hbm_gbs"], unit="GB/s")
         else:
@@ -362,7 +363,8 @@ def run_b200(args):
             result["roofline"]["frac_of_effective_peak"] = top["achieved"] / (top["peak"] / 6.0)
             result["roofline"]["tensor_pipe_active_pct"] = measured.get("tensor_pipe_active_pct")
         result["kernels"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()
-                              if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs", "tflops", "frac")}
+                              if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs", "gbs_compulsory",
+                                       "tflops", "frac")}
                              for r in table]
         result["hgk_ms_per_step"] = sum(r["ms_per_step"] for r in table)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -162,6 +162,61 @@ k_contract_node(const NodeArgs p) {
   }
 }
 
+// ---------------------------------------------------- node, single channel (fast path) --
+// The shapes that carry the traffic (CFConv aggregate and its derivative w.r.t. x, segment sums,
+// pooling): C = CO = 1, no U.  Operand presence and the permutation are template parameters so the
+// inner loop is straight-line: 2 shuffles (1 when edges are already grouped), 2 row loads, 4 mul +
+// 4 add per lane and edge.  Same summation order as the generic kernel (sequential in CSR order).
+template <int VW, int TPR, bool HAS_A, bool HAS_W, bool HAS_PERM, int UNROLL>
+__global__ void __launch_bounds__(256)
+k_contract_node_c1(const NodeArgs p) {
+  using V = Vec<VW>;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % TPR;
+  const unsigned mask = group_mask<TPR>(lane);
+  const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / TPR;
+  if (n >= p.N) return;  // whole groups leave together
+  const int32_t beg = __ldg(p.rowptr + n), end = __ldg(p.rowptr + n + 1);
+  const int FV = p.F / VW;
+  for (int chunk = 0; chunk < FV; chunk += TPR) {
+    const int col = (chunk + sub) * VW;
+    const bool active = (chunk + sub) < FV;
+    const float* wcol = p.W + col;
+    const float* acol = p.A + col;
+    V acc = V::zero();
+    for (int32_t base = beg; base < end; base += TPR) {
+      int32_t my_e = base + sub, my_j = 0;
+      if (base + sub < end) {
+        if (HAS_PERM) my_e = __ldg(p.perm + base + sub);
+        if (HAS_A) my_j = __ldg(p.gidx + my_e);
+      }
+      const int cnt = min((int32_t)TPR, end - base);
+      for (int t = 0; t < cnt; t += UNROLL) {
+        V a[UNROLL], w[UNROLL];
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) {
+          const int tt = t + q;
+          const int32_t e = HAS_PERM ? __shfl_sync(mask, my_e, tt, TPR) : base + tt;
+          const int32_t j = HAS_A ? __shfl_sync(mask, my_j, tt, TPR) : 0;
+          a[q] = V::zero();
+          w[q] = V::zero();
+          if (active && tt < cnt) {
+            if (HAS_W) w[q] = V::load_stream(wcol + (int64_t)e * p.ldw);
+            if (HAS_A) a[q] = V::load(acol + (int64_t)j * p.lda);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) {
+          // a past-the-end slot contributes (+0) * (+0) = +0, which leaves the sum unchanged
+          const V term = (HAS_A && HAS_W) ? a[q].mul(w[q]) : (HAS_A ? a[q] : w[q]);
+          acc = acc.add(term);
+        }
+      }
+    }
+    if (active) acc.store(p.out + n * p.ldo + col);
+  }
+}
+
 // ---------------------------------------------------------------- edge_w --
 struct EdgeArgs {
   float* out; int64_t ldout;           // EW [E,F] (ldout) or EU [E,C]
@@ -328,8 +383,26 @@ inline int pick_tpr(int fv) {
     default: { constexpr int TPR = 32; __VA_ARGS__; } break; \
   }
 
+template <int VW, bool HAS_A, bool HAS_W>
+void launch_node_c1(const NodeArgs& a, cudaStream_t st) {
+  const int tpr = pick_tpr(a.F / VW);
+  const unsigned blocks = (unsigned)ceil_div(a.N * tpr, 256);
+  if (a.perm) {
+    HGK_DISPATCH_TPR(tpr, (k_contract_node_c1<VW, TPR, HAS_A, HAS_W, true, (TPR < 8 ? TPR : 8)>
+                           <<<blocks, 256, 0, st>>>(a)));
+  } else {
+    HGK_DISPATCH_TPR(tpr, (k_contract_node_c1<VW, TPR, HAS_A, HAS_W, false, (TPR < 8 ? TPR : 8)>
+                           <<<blocks, 256, 0, st>>>(a)));
+  }
+}
+
 template <int VW, int C>
 void launch_node(const NodeArgs& a, cudaStream_t st) {
+  if (C == 1 && a.CO == 1 && a.U == nullptr) {
+    if (a.A && a.W) return launch_node_c1<VW, true, true>(a, st);
+    if (a.W) return launch_node_c1<VW, false, true>(a, st);
+    if (a.A) return launch_node_c1<VW, true, false>(a, st);
+  }
   const int tpr = pick_tpr(a.F / VW);
   const int64_t threads = a.N * tpr;
   const unsigned blocks = (unsigned)ceil_div(threads, 256);

@@ -136,8 +136,10 @@ KERNELS_PER_CALL = {
 class Stats:
     """Call counters and (optionally) CUDA-event timing of every C-ABI call.
 
-    `cost` is the ALGORITHMIC work of the call -- (bytes, flops) from the formulas in DESIGN.md --
-    so that achieved GB/s or TFLOP/s = sum(cost) / sum(event time) per entry point."""
+    `cost` is the ALGORITHMIC work of the call -- (bytes, flops[, compulsory_bytes]) from the formulas
+    in DESIGN.md -- so that achieved GB/s or TFLOP/s = sum(cost) / sum(event time) per entry point.
+    `bytes` counts a gathered node row once per EDGE; `compulsory_bytes` counts the
+    gathered table once (what must cross HBM when the table stays in the 126 MB L2)."""
 
     def __init__(self):
         self.reset()
@@ -155,8 +157,8 @@ class Stats:
         """name -> dict(calls, ms, bytes, flops); call after torch.cuda.synchronize()."""
         out = {}
         for name, n in self.calls.items():
-            b, f = self.cost.get(name, (0, 0))
-            out[name] = dict(calls=n, ms=0.0, bytes=b, flops=f)
+            b, f, d = self.cost.get(name, (0, 0, 0))
+            out[name] = dict(calls=n, ms=0.0, bytes=b, flops=f, dram_bytes=d)
         for name, e0, e1 in self.events:
             out[name]["ms"] += e0.elapsed_time(e1)
         return out
@@ -170,8 +172,8 @@ def call(name, *args, cost=(0, 0)):
     fn = getattr(lib(), name)
     stats.calls[name] = stats.calls.get(name, 0) + 1
     if cost != (0, 0):
-        b, f = stats.cost.get(name, (0, 0))
-        stats.cost[name] = (b + cost[0], f + cost[1])
+        b, f, d = stats.cost.get(name, (0, 0, 0))
+        stats.cost[name] = (b + cost[0], f + cost[1], d + (cost[2] if len(cost) > 2 else cost[0]))
     if stats.timing:
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)

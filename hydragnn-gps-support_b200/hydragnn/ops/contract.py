@@ -40,9 +40,12 @@ def _node_raw(topo, side_out, A, side_a, W, U, C, CO, F):
     nbytes = E * (4 * F * (ca if A is not None else 0) + (4 * F if W is not None else 0)
                   + (4 * C if U is not None else 0) + (4 if A is not None else 0)
                   + (4 if perm is not None else 0)) + N * (4 * CO * F + 4)
+    # compulsory HBM bytes: the gathered table crosses HBM once (it is re-read from L2 afterwards)
+    table = 0 if A is None else A.size(0) * 4 * F * ca
+    dram = nbytes - E * 4 * F * (ca if A is not None else 0) + table
     _hgk.call("hgk_contract_node", _hgk.ptr(out), CO * F, CO, _hgk.ptr(a_t), lda, ca, _hgk.ptr(w_t), ldw,
               _hgk.ptr(u_t), _hgk.ptr(rowptr), _hgk.ptr(perm), _hgk.ptr(gidx), N, E, F, C,
-              cost=(nbytes, 0))
+              cost=(nbytes, 0, dram))
     return out
 
 
@@ -67,8 +70,11 @@ def _edge_w_raw(topo, G, side_g, X, side_x, U, C, F):
     E = topo.E
     nbytes = E * (4 * F * ((cg if G is not None else 0) + (cx if X is not None else 0)) + 4 * F
                   + (4 * C if U is not None else 0) + 4 * ((G is not None) + (X is not None)))
+    gathered = E * 4 * F * ((cg if G is not None else 0) + (cx if X is not None else 0))
+    tables = (0 if G is None else G.size(0) * 4 * F * cg) + (0 if X is None else X.size(0) * 4 * F * cx)
     _hgk.call("hgk_contract_edge_w", _hgk.ptr(out), F, _hgk.ptr(g_t), ldg, cg, _hgk.ptr(gi),
-              _hgk.ptr(x_t), ldx, cx, _hgk.ptr(xi), _hgk.ptr(u_t), E, F, C, cost=(nbytes, 0))
+              _hgk.ptr(x_t), ldx, cx, _hgk.ptr(xi), _hgk.ptr(u_t), E, F, C,
+              cost=(nbytes, 0, nbytes - gathered + tables))
     return out
 
 
