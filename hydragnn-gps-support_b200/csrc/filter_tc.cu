@@ -50,11 +50,13 @@ __device__ __forceinline__ float shifted_softplus(float z) {
   return fmaxf(z, 0.f) + (fast_log2(1.f + u) - 1.f) * kLn2;
 }
 
+constexpr int kFiltThreads = 512;   // 16 warps: 4 threads per row, 32 of the 128 columns each
+
 template <int G, int R>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFiltThreads, 1)
 k_schnet_filter_fwd(const FilterArgs p) {
   constexpr int GP = (G + 3) / 4 * 4;
-  static_assert(GP + R <= kK0 && R % 4 == 0, "input layout must fit 64 columns");
+  static_assert(GP + R <= kK0 && R % 4 == 0 && G > 48 && GP <= 52, "input layout: gaussians end in the last quarter");
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -65,17 +67,16 @@ k_schnet_filter_fwd(const FilterArgs p) {
 
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColXhi = 0, kColXlo = 64, kColZ = 128, kColHhi = 256, kColHlo = 384;
-  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);     // cs.half = column quarter 0..3
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
+  const int quarter = cs.half;
 
   // resident operands: weights (hi, lo) in shared memory, biases and gaussian centres
-  {
+  if (threadIdx.x < kThreads) {
     Tile<kFilt, kK0> t0;
     t0.load(p.w0, kK0, 0, kFilt);
     t0.store_rows(W0hi, W0lo);
-  }
-  {
     Tile<kFilt, kFilt> t1;
     t1.load(p.w1, kFilt, 0, kFilt);
     t1.store_rows(W1hi, W1lo);
@@ -88,43 +89,47 @@ k_schnet_filter_fwd(const FilterArgs p) {
   publish_operands();
 
   uint32_t parity = 0;
+  const float c2 = p.coeff * kLog2e;
   const int64_t num_tiles = (p.E + kFilt - 1) / kFilt;
   for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const int64_t e = tile * kFilt + cs.row_local;
     const bool ok = e < p.E;
     const float dist = ok ? __ldg(p.d + e) : 0.f;
-    const float c2 = p.coeff * kLog2e;
 
-    // ---- X = [gauss | raw]: this thread's 32 of the 64 columns -> TMEM (hi, lo) ----
+    // ---- X = [gauss | raw]: this thread's 16 of the 64 columns -> TMEM (hi, lo) ----
     {
-      uint32_t xh[32], xl[32];
-      float rawv[R > 0 ? R : 1];
-      if (R > 0 && cs.half == 1) {
+      uint32_t xh[16], xl[16];
+      float val[16];
+      if (quarter < 3) {                                // columns 0..47: gaussians only
 #pragma unroll
-        for (int c = 0; c < R; c += 4) {
-          float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ok) r4 = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + c));
-          rawv[c] = r4.x; rawv[c + 1] = r4.y; rawv[c + 2] = r4.z; rawv[c + 3] = r4.w;
+        for (int j = 0; j < 16; ++j) {
+          const float t = dist - off_s[quarter * 16 + j];
+          val[j] = fast_exp2(c2 * (t * t));
+        }
+      } else {                                          // columns 48..63: last gaussians | pad | raw | pad
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int k = 48 + j;                         // compile-time after unrolling
+          if (k < G) { const float t = dist - off_s[k]; val[j] = fast_exp2(c2 * (t * t)); }
+          else val[j] = 0.f;
+        }
+        if (R > 0 && ok) {
+#pragma unroll
+          for (int c = 0; c < R; c += 4) {
+            const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + c));
+            val[GP - 48 + c] = r4.x; val[GP - 48 + c + 1] = r4.y; val[GP - 48 + c + 2] = r4.z; val[GP - 48 + c + 3] = r4.w;
+          }
         }
       }
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float val = 0.f;
-        if (cs.half == 0) {
-          if (j < G) { const float t = dist - off_s[j]; val = fast_exp2(c2 * (t * t)); }
-        } else {
-          const int k = 32 + j;                         // compile-time after unrolling
-          if (k < G) { const float t = dist - off_s[k]; val = fast_exp2(c2 * (t * t)); }
-          else if (R > 0 && k >= GP && k < GP + R) val = rawv[(k - GP) < R ? (k - GP) : 0];
-        }
-        if (!ok) val = 0.f;
+      for (int j = 0; j < 16; ++j) {
         float hi_, lo_;
-        split_tf32(val, hi_, lo_);
+        split_tf32(ok ? val[j] : 0.f, hi_, lo_);
         xh[j] = __float_as_uint(hi_);
         xl[j] = __float_as_uint(lo_);
       }
-      tmem_st32(tmem + cs.lane_base + kColXhi + cs.half * 32, xh);
-      tmem_st32(tmem + cs.lane_base + kColXlo + cs.half * 32, xl);
+      tmem_st16(tmem + cs.lane_base + kColXhi + quarter * 16, xh);
+      tmem_st16(tmem + cs.lane_base + kColXlo + quarter * 16, xl);
       tmem_st_wait();
     }
     fence_before_sync();
@@ -138,12 +143,10 @@ k_schnet_filter_fwd(const FilterArgs p) {
     parity ^= 1;
     fence_after_sync();
 
-    // ---- H = ssp(Z0 + b0): my 64 columns, two passes of 32 ----
-    float* hrow = p.h + e * kFilt + cs.half * 64;
-#pragma unroll
-    for (int part = 0; part < 2; ++part) {
+    // ---- H = ssp(Z0 + b0): my 32 columns ----
+    const int c0 = quarter * 32;
+    {
       uint32_t z[32], lo[32];
-      const int c0 = cs.half * 64 + part * 32;
       tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
       tmem_ld_wait();
 #pragma unroll
@@ -155,17 +158,19 @@ k_schnet_filter_fwd(const FilterArgs p) {
         lo[j] = __float_as_uint(lo_);
       }
       if (ok) {
+        float* hrow = p.h + e * kFilt + c0;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          *reinterpret_cast<float4*>(hrow + part * 32 + j) =
-              make_float4(__uint_as_float(z[j]), __uint_as_float(z[j + 1]), __uint_as_float(z[j + 2]), __uint_as_float(z[j + 3]));
+        for (int j = 0; j < 32; j += 8)
+          st_global_v8(hrow + j,
+                       make_float4(__uint_as_float(z[j]), __uint_as_float(z[j + 1]), __uint_as_float(z[j + 2]), __uint_as_float(z[j + 3])),
+                       make_float4(__uint_as_float(z[j + 4]), __uint_as_float(z[j + 5]), __uint_as_float(z[j + 6]), __uint_as_float(z[j + 7])));
       }
 #pragma unroll
       for (int j = 0; j < 32; ++j) z[j] &= 0xffffe000u;            // hi part
       tmem_st32(tmem + cs.lane_base + kColHhi + c0, z);
       tmem_st32(tmem + cs.lane_base + kColHlo + c0, lo);
+      tmem_st_wait();
     }
-    tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (warp_u == 0 && elect_one_sync()) {
@@ -179,21 +184,19 @@ k_schnet_filter_fwd(const FilterArgs p) {
     fence_after_sync();
 
     // ---- W = (Z1 + b1) * C ----
-    float* wrow = p.w + e * kFilt + cs.half * 64;
-#pragma unroll
-    for (int part = 0; part < 2; ++part) {
+    {
       uint32_t z[32];
-      const int c0 = cs.half * 64 + part * 32;
       tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
       tmem_ld_wait();
       if (ok) {
+        float* wrow = p.w + e * kFilt + c0;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          *reinterpret_cast<float4*>(wrow + part * 32 + j) =
-              make_float4((__uint_as_float(z[j]) + b1_s[c0 + j]) * env,
-                          (__uint_as_float(z[j + 1]) + b1_s[c0 + j + 1]) * env,
-                          (__uint_as_float(z[j + 2]) + b1_s[c0 + j + 2]) * env,
-                          (__uint_as_float(z[j + 3]) + b1_s[c0 + j + 3]) * env);
+        for (int j = 0; j < 32; j += 8) {
+          float o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] = (__uint_as_float(z[j + i]) + b1_s[c0 + j + i]) * env;
+          st_global_v8(wrow + j, make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]));
+        }
       }
     }
     // the next tile's first barrier (after its X store) orders these Z reads before the next MMA
@@ -201,6 +204,10 @@ k_schnet_filter_fwd(const FilterArgs p) {
   cta_teardown(tmem, kCols);
 }
 
+}  // namespace tc
+}  // namespace hgk
+namespace hgk {
+namespace tc {
 
 // ================================================================================== backward ===
 // dZ1 = gW * C(d);  dH = dZ1 W1;  dZ0 = dH * ssp'(Z0),  ssp'(z) = sigmoid(z) = 1 - exp(-(H + ln 2)).
@@ -216,7 +223,7 @@ struct FilterBwdArgs {
   int64_t E;
 };
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFiltThreads, 1)
 k_schnet_filter_bwd(const FilterBwdArgs p) {
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
@@ -225,10 +232,11 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
   float* Wlo = Whi + kFilt * kFilt;
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColAhi = 0, kColAlo = 128, kColDH = 256;
-  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);     // cs.half = column quarter 0..3
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
-  {
+  const int c0 = cs.half * 32;
+  if (threadIdx.x < kThreads) {
     Tile<kFilt, kFilt> t;
     t.load(p.w1t, kFilt, 0, kFilt);
     t.store_rows(Whi, Wlo);
@@ -244,28 +252,26 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
     const bool ok = e < p.E;
     const float dist = ok ? __ldg(p.d + e) : 0.f;
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);
-    const float* grow = p.gw + e * kFilt + cs.half * 64;
-#pragma unroll
-    for (int part = 0; part < 2; ++part) {
+    {
+      const float* grow = p.gw + e * kFilt + c0;
       uint32_t hi[32], lo[32];
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ok) g = ld_stream4(grow + part * 32 + j);
-        const float x[4] = {g.x * env, g.y * env, g.z * env, g.w * env};
+      for (int j = 0; j < 32; j += 8) {
+        float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+        if (ok) ld_global_nc_v8(grow + j, g0, g1);
+        const float x[8] = {g0.x * env, g0.y * env, g0.z * env, g0.w * env, g1.x * env, g1.y * env, g1.z * env, g1.w * env};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 8; ++i) {
           float h_, l_;
           split_tf32(x[i], h_, l_);
           hi[j + i] = __float_as_uint(h_);
           lo[j + i] = __float_as_uint(l_);
         }
       }
-      const int c0 = cs.half * 64 + part * 32;
       tmem_st32(tmem + cs.lane_base + kColAhi + c0, hi);
       tmem_st32(tmem + cs.lane_base + kColAlo + c0, lo);
+      tmem_st_wait();
     }
-    tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (warp_u == 0 && elect_one_sync()) {
@@ -273,29 +279,32 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
       mma3_ts<kFilt>(tmem + kColDH, tmem + kColAhi, tmem + kColAlo, dW, kIdesc, false);   // dH = dZ1 W1
       mma_commit(&bar);
     }
+    // the saved activations of this thread's columns arrive while the MMAs run
+    float4 hv[8];
+    if (ok) {
+      const float* hrow = p.h + e * kFilt + c0;
+#pragma unroll
+      for (int j = 0; j < 8; j += 2) ld_global_nc_v8(hrow + 4 * j, hv[j], hv[j + 1]);
+    }
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
 
-    const float* hrow = p.h + e * kFilt + cs.half * 64;
-    float* orow = p.dz0 + e * kFilt + cs.half * 64;
+    uint32_t dh[32];
+    tmem_ld32(tmem + cs.lane_base + kColDH + c0, dh);
+    tmem_ld_wait();
+    if (ok) {
+      float* orow = p.dz0 + e * kFilt + c0;
+      float4 o[8];
 #pragma unroll
-    for (int part = 0; part < 2; ++part) {
-      uint32_t dh[32];
-      tmem_ld32(tmem + cs.lane_base + kColDH + cs.half * 64 + part * 32, dh);
-      tmem_ld_wait();
-      if (ok) {
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 hv = ld_stream4(hrow + part * 32 + j);
-          float4 o;
-          o.x = __uint_as_float(dh[j]) * (1.f - fast_exp2(-(hv.x + kLn2) * kLog2e));
-          o.y = __uint_as_float(dh[j + 1]) * (1.f - fast_exp2(-(hv.y + kLn2) * kLog2e));
-          o.z = __uint_as_float(dh[j + 2]) * (1.f - fast_exp2(-(hv.z + kLn2) * kLog2e));
-          o.w = __uint_as_float(dh[j + 3]) * (1.f - fast_exp2(-(hv.w + kLn2) * kLog2e));
-          *reinterpret_cast<float4*>(orow + part * 32 + j) = o;
-        }
+      for (int j = 0; j < 8; ++j) {
+        o[j].x = __uint_as_float(dh[4 * j]) * (1.f - fast_exp2(-(hv[j].x + kLn2) * kLog2e));
+        o[j].y = __uint_as_float(dh[4 * j + 1]) * (1.f - fast_exp2(-(hv[j].y + kLn2) * kLog2e));
+        o[j].z = __uint_as_float(dh[4 * j + 2]) * (1.f - fast_exp2(-(hv[j].z + kLn2) * kLog2e));
+        o[j].w = __uint_as_float(dh[4 * j + 3]) * (1.f - fast_exp2(-(hv[j].w + kLn2) * kLog2e));
       }
+#pragma unroll
+      for (int j = 0; j < 8; j += 2) st_global_v8(orow + 4 * j, o[j], o[j + 1]);
     }
     // the next tile's barrier after its TMEM stores orders these dH reads before the next MMA
   }
@@ -493,11 +502,11 @@ extern "C" int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const f
   if (R == 8) {
     err = cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in: %s", cudaGetErrorString(err));
-    tc::k_schnet_filter_fwd<50, 8><<<grid, tc::kThreads, smem, st>>>(a);
+    tc::k_schnet_filter_fwd<50, 8><<<grid, tc::kFiltThreads, smem, st>>>(a);
   } else {
     err = cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in: %s", cudaGetErrorString(err));
-    tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kThreads, smem, st>>>(a);
+    tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kFiltThreads, smem, st>>>(a);
   }
   return check_launch("schnet_filter_fwd");
 }
@@ -513,7 +522,7 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
   cudaError_t err = cudaFuncSetAttribute(tc::k_schnet_filter_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_bwd: smem opt-in: %s", cudaGetErrorString(err));
   const unsigned grid = (unsigned)imin64(ceil_div(E, tc::kFilt), kNumSM);
-  tc::k_schnet_filter_bwd<<<grid, tc::kThreads, smem, (cudaStream_t)stream>>>(a);
+  tc::k_schnet_filter_bwd<<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a);
   return check_launch("schnet_filter_bwd");
 }
 

@@ -51,6 +51,19 @@ __device__ __forceinline__ void st_stream4(float* p, float4 v) {
                : "memory");
 }
 
+// 256-bit accesses (sm_100: LDG.256 / STG.256): one full 32-byte sector per lane and instruction,
+// which matters when the lanes of a warp walk different rows.  `p` must be 32-byte aligned.
+__device__ __forceinline__ void st_global_v8(float* p, float4 a, float4 b) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z),
+               "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+               : "memory");
+}
+__device__ __forceinline__ void ld_global_nc_v8(const float* p, float4& a, float4& b) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p));
+}
+
 // IEEE multiply / add that the compiler may not contract into an FMA: the
 // segmented sums must round exactly like "materialise product, then add".
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
