@@ -310,10 +310,15 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
 }
 
 // ---- dK, dV: CTA owns 128 keys (TMEM lane = key), loops over 64-query tiles -------------------
+// 512 threads: one CTA per SM (it needs 448 TMEM columns), so the warps have to come from inside
+// the CTA -- four threads share a key row, 16 of the 64 query columns each.
+constexpr int kKvThreads = 512;
+
 template <int D>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kKvThreads, 1)
 k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv) {
   constexpr int BQ = BN;                               // queries per iteration
+  constexpr int QC = BQ / 4;                           // query columns per thread
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -340,20 +345,23 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   // this CTA's K and V rows (hi, lo) stay in TMEM as the A operands of S^T and dP^T
   constexpr uint32_t kColKhi = 256 + 2 * D, kColKlo = 256 + 3 * D, kColVhi = 256 + 4 * D, kColVlo = 256 + 5 * D;
   static_assert(256 + 6 * D <= 512, "TMEM budget");
-  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);     // cs.half = column quarter 0..3
   const uint32_t tmem = cs.tmem;
+  const int part = cs.half;
 
   {
     const int64_t krow_ld = key0 + cs.row_local;
     const bool kok = krow_ld < seg_end;
-    row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, cs.half, 1.f);
-    row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, cs.half, 1.f);
+    if (part < 2)
+      row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, part, 1.f);
+    else
+      row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, part - 2, 1.f);
   }
-  const OperandDesc dQ[2] = {operand_desc<D>(Qhi(0), Qlo(0)), operand_desc<D>(Qhi(1), Qlo(1))};
-  const OperandDesc dG[2] = {operand_desc<D>(Ghi(0), Glo(0)), operand_desc<D>(Ghi(1), Glo(1))};
-  const OperandDesc dQt[2] = {operand_desc<BQ>(QThi(0), QTlo(0)), operand_desc<BQ>(QThi(1), QTlo(1))};
-  const OperandDesc dGt[2] = {operand_desc<BQ>(GThi(0), GTlo(0)), operand_desc<BQ>(GThi(1), GTlo(1))};
-  Tile<BQ, D> tq, tg;                                  // next query / dO tile, prefetched in registers
+  const OperandDesc dQ0 = operand_desc<D>(Qhi(0), Qlo(0)), dQ1 = operand_desc<D>(Qhi(1), Qlo(1));
+  const OperandDesc dG0 = operand_desc<D>(Ghi(0), Glo(0)), dG1 = operand_desc<D>(Ghi(1), Glo(1));
+  const OperandDesc dQt0 = operand_desc<BQ>(QThi(0), QTlo(0)), dQt1 = operand_desc<BQ>(QThi(1), QTlo(1));
+  const OperandDesc dGt0 = operand_desc<BQ>(GThi(0), GTlo(0)), dGt1 = operand_desc<BQ>(GThi(1), GTlo(1));
+  Tile<BQ, D, kKvThreads> tq, tg;                      // next query / dO tile, prefetched in registers
   tq.load(p.q + h * D, p.ldq, seg_beg, seg_end);
   tg.load(b.dout + h * D, b.lddo, seg_beg, seg_end);
 
@@ -385,8 +393,8 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     publish_operands();                                // stage `st` is complete and visible
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ts<D>(tmem + kColST, tmem + kColKhi, tmem + kColKlo, dQ[st], kIdescS, false);    // S^T  = K Q^T
-      mma3_ts<D>(tmem + kColDPT, tmem + kColVhi, tmem + kColVlo, dG[st], kIdescS, false);   // dP^T = V dO^T
+      mma3_ts<D>(tmem + kColST, tmem + kColKhi, tmem + kColKlo, st ? dQ1 : dQ0, kIdescS, false);    // S^T  = K Q^T
+      mma3_ts<D>(tmem + kColDPT, tmem + kColVhi, tmem + kColVlo, st ? dG1 : dG0, kIdescS, false);   // dP^T = V dO^T
       mma_commit(&bar);
     }
     if (has_next) {                                    // global loads of the next tile fly under the MMAs
@@ -397,14 +405,14 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     parity ^= 1;
     fence_after_sync();
 
-    const int col0 = cs.half * HALF;
+    const int col0 = part * QC;
     const int32_t nvalid = seg_end - q0 - col0;        // my query columns [0, nvalid) exist
-    uint32_t sv[HALF], dp[HALF], plo[HALF], dslo[HALF];
-    tmem_ld32(tmem + cs.lane_base + kColST + col0, sv);
-    tmem_ld32(tmem + cs.lane_base + kColDPT + col0, dp);
+    uint32_t sv[QC], dp[QC], plo[QC], dslo[QC];
+    tmem_ld16(tmem + cs.lane_base + kColST + col0, sv);
+    tmem_ld16(tmem + cs.lane_base + kColDPT + col0, dp);
     tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < HALF; ++j) {
+    for (int j = 0; j < QC; ++j) {
       float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[st][col0 + j]);
       if (j >= nvalid) pj = 0.f;
       const float ds = pj * (__uint_as_float(dp[j]) - delta_s[st][col0 + j]);
@@ -414,17 +422,17 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
       split_tf32(ds, hi_, lo_);
       dp[j] = __float_as_uint(hi_); dslo[j] = __float_as_uint(lo_);
     }
-    tmem_st32(tmem + cs.lane_base + kColST + col0, sv);
-    tmem_st32(tmem + cs.lane_base + kColPlo + col0, plo);
-    tmem_st32(tmem + cs.lane_base + kColDPT + col0, dp);
-    tmem_st32(tmem + cs.lane_base + kColDSlo + col0, dslo);
+    tmem_st16(tmem + cs.lane_base + kColST + col0, sv);
+    tmem_st16(tmem + cs.lane_base + kColPlo + col0, plo);
+    tmem_st16(tmem + cs.lane_base + kColDPT + col0, dp);
+    tmem_st16(tmem + cs.lane_base + kColDSlo + col0, dslo);
     tmem_st_wait();
     fence_before_sync();
     __syncthreads();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, dGt[st], kIdescD, !first);       // dV += P^T dO
-      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, dQt[st], kIdescD, !first);     // dK += dS^T Q
+      mma3_ts<BQ>(tmem + kColDV, tmem + kColST, tmem + kColPlo, st ? dGt1 : dGt0, kIdescD, !first);       // dV += P^T dO
+      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT, tmem + kColDSlo, st ? dQt1 : dQt0, kIdescD, !first);     // dK += dS^T Q
       mma_commit(&bar);
     }
     first = false;
@@ -434,31 +442,25 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
     fence_after_sync();
   }
 
-  constexpr int DH = D / 2;
+  // parts 0, 1 write the two halves of dV's row, parts 2, 3 those of dK (D = 32: 16 columns each)
+  static_assert(D == 32, "epilogue column split");
+  constexpr int EC = D / 2;                            // columns per thread
   const int32_t krow = key0 + cs.row_local;
   const bool ok = krow < seg_end;
-  uint32_t tv_[16], tk_[16];
+  const bool is_k = part >= 2;
+  const int chalf = part & 1;
+  uint32_t t[16];
+  tmem_ld16(tmem + cs.lane_base + (is_k ? kColDK : kColDV) + chalf * EC, t);
+  tmem_ld_wait();
+  if (ok) {
+    // Q was staged as q * scale * log2(e):  dK = scale * dS^T Q = (dS^T Q_staged) * ln 2
+    const float mul = is_k ? kLn2 : 1.f;
+    float* orow = (is_k ? dk : dv) + ((int64_t)krow * p.H + h) * D + chalf * EC;
 #pragma unroll
-  for (int c0 = 0; c0 < DH; c0 += 16) {
-    tmem_ld16(tmem + cs.lane_base + kColDV + cs.half * DH + c0, tv_);
-    tmem_ld16(tmem + cs.lane_base + kColDK + cs.half * DH + c0, tk_);
-    tmem_ld_wait();
-    if (ok) {
-      float* vrow = dv + ((int64_t)krow * p.H + h) * D + cs.half * DH + c0;
-      float* krow_p = dk + ((int64_t)krow * p.H + h) * D + cs.half * DH + c0;
-#pragma unroll
-      for (int j = 0; j < 16; j += 4) {
-        if (c0 + j < DH) {
-          *reinterpret_cast<float4*>(vrow + j) =
-              make_float4(__uint_as_float(tv_[j]), __uint_as_float(tv_[j + 1]),
-                          __uint_as_float(tv_[j + 2]), __uint_as_float(tv_[j + 3]));
-          // Q was staged as q * scale * log2(e):  dK = scale * dS^T Q = (dS^T Q_staged) * ln 2
-          *reinterpret_cast<float4*>(krow_p + j) =
-              make_float4(__uint_as_float(tk_[j]) * kLn2, __uint_as_float(tk_[j + 1]) * kLn2,
-                          __uint_as_float(tk_[j + 2]) * kLn2, __uint_as_float(tk_[j + 3]) * kLn2);
-        }
-      }
-    }
+    for (int j = 0; j < EC; j += 4)
+      *reinterpret_cast<float4*>(orow + j) =
+          make_float4(__uint_as_float(t[j]) * mul, __uint_as_float(t[j + 1]) * mul,
+                      __uint_as_float(t[j + 2]) * mul, __uint_as_float(t[j + 3]) * mul);
   }
   cta_teardown(tmem, kCols);
 }
@@ -493,7 +495,7 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
   int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
   if (rc) return rc;
-  k_attn_bwd_kv_tc<D><<<grid, kThreads, smem_kv, st>>>(a, b, dk, dv);
+  k_attn_bwd_kv_tc<D><<<grid, kKvThreads, smem_kv, st>>>(a, b, dk, dv);
   size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
   if (smem_q < 80 * 1024) smem_q = 80 * 1024;
   rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
@@ -526,13 +528,12 @@ int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float
                 const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
                 const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
                 int32_t D, float scale, cudaStream_t st) {
-  if (!(D == 16 || D == 32)) return 1;
+  if (D != 32) return 1;    // the 512-thread dK/dV kernel is laid out for 32-wide heads
   if (!tc_aligned(q, ldq) || !tc_aligned(k, ldk) || !tc_aligned(v, ldv) || !tc_aligned(dout, lddo) ||
       !tc_aligned(dq, 4) || !tc_aligned(dk, 4) || !tc_aligned(dv, 4))
     return 1;
   AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
   tc::AttnTcBwdArgs b{dout, lddo, lse, delta};
-  if (D == 16) return tc::launch_bwd<16>(a, b, dq, dk, dv, N, st);
   return tc::launch_bwd<32>(a, b, dq, dk, dv, N, st);
 }
 

@@ -206,16 +206,16 @@ constexpr uint32_t kLbo = 128;   // bytes between the two 16-byte K chunks of on
 // so the 32 lanes of a warp cover 8 consecutive rows x 4 columns: global reads are 64-byte runs,
 // and in the core-matrix layout the 8 rows of one column are 128 contiguous bytes -- both the row
 // store and the transposed store below are free of shared-memory bank conflicts.
-template <int ROWS, int D>
+template <int ROWS, int D, int NT = kThreads>
 struct Tile {
   static constexpr int CH = D / 4;
-  static constexpr int PER = ROWS * CH / kThreads;
-  static_assert(ROWS * CH % kThreads == 0, "tile must divide evenly over the CTA");
+  static constexpr int PER = ROWS * CH / NT;
+  static_assert(ROWS * CH % NT == 0, "tile must divide evenly over the CTA");
   static_assert(CH % 4 == 0, "a warp spans 4 columns");
   float4 v[PER];
 
   __device__ __forceinline__ static void coord(int it, int& r, int& c) {
-    const int idx = threadIdx.x + it * kThreads;
+    const int idx = threadIdx.x + it * NT;
     r = (idx & 7) + 8 * (idx / (8 * CH));
     c = (idx >> 3) % CH;
   }
