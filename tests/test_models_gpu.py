@@ -28,7 +28,8 @@ def test_step_is_bit_reproducible(libhgk, name):
         assert torch.equal(a["grads"][n], b["grads"][n]), n
 
 
-@pytest.mark.parametrize("workload,kwargs", [("schnet_gps_fesi1024", dict(cells=3)), ("schnet_qm9", {})])
+@pytest.mark.parametrize("workload,kwargs", [("schnet_gps_fesi1024", dict(cells=3)), ("schnet_qm9", {}),
+                                             ("egnn_gps_zinc", {}), ("painn_oc20_forces", {})])
 def test_full_width_models_match_cpu_oracle(libhgk, workload, kwargs):
     """hidden 128 / 50 gaussians (the BASELINE widths, where the fused tcgen05 filter and attention
     kernels are selected) on a small batch: product on the GPU vs the CPU oracle with the same
@@ -46,9 +47,12 @@ def test_full_width_models_match_cpu_oracle(libhgk, workload, kwargs):
     rng = np.random.default_rng(11)
     graphs = [spec["sample"](rng, **kwargs) for _ in range(3)]
     batch = syn.collate(graphs)
-    g = radius_graph(batch["pos"].cuda(), batch["ptr"], spec["radius"], spec["max_neighbours"], loop=False,
-                     cell=batch.get("cell") if spec["pbc"] else None, pbc=batch.get("pbc") if spec["pbc"] else None)
-    batch["edge_index"] = g["edge_index"].cpu()
+    if spec["edges"] == "radius":
+        g = radius_graph(batch["pos"].cuda(), batch["ptr"], spec["radius"], spec["max_neighbours"], loop=False,
+                         cell=batch.get("cell") if spec["pbc"] else None, pbc=batch.get("pbc") if spec["pbc"] else None)
+        batch["edge_index"] = g["edge_index"].cpu()
+        if spec["pbc"]:
+            batch["edge_shifts"] = g["edge_shifts"].cpu()
     batch = syn.finish_edges(batch)
     arch = dict(spec["arch"], num_conv_layers=2)
 
@@ -56,7 +60,11 @@ def test_full_width_models_match_cpu_oracle(libhgk, workload, kwargs):
     ref.eval()
     state = {k: v.clone() for k, v in ref.state_dict().items()}
     data = mg.Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in batch.items()})
-    loss_ref = ref.loss(ref(data), data.y, [torch.arange(data.y.shape[0])])[0]
+    if spec["forces"]:
+        data.pos.requires_grad_(True)
+        loss_ref = ref.energy_force_loss(ref(data), data)[0]
+    else:
+        loss_ref = ref.loss(ref(data), data.y, [torch.arange(data.y.shape[0])])[0]
     loss_ref.backward()
 
     model = create_model(**arch)
@@ -64,8 +72,18 @@ def test_full_width_models_match_cpu_oracle(libhgk, workload, kwargs):
     model.eval()
     dev = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in batch.items() if k not in ("cell", "pbc")}
     d = Data(**dev)
-    loss = model.loss(model(d), d.y, [torch.arange(d.y.shape[0], device="cuda")])[0]
+    if spec["forces"]:
+        d.pos.requires_grad_(True)
+        loss = model.energy_force_loss(model(d), d)[0]
+    else:
+        loss = model.loss(model(d), d.y, [torch.arange(d.y.shape[0], device="cuda")])[0]
     loss.backward()
+    if spec["forces"]:   # forces = -dE/dpos of the summed node energies, against the oracle's
+        d2 = mg.Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in batch.items()})
+        d2.pos.requires_grad_(True)
+        energy = ref(d2)[0].sum()
+        forces_ref = -torch.autograd.grad(energy, d2.pos)[0]
+        torch.testing.assert_close(model.last_forces_pred.detach().cpu(), forces_ref, rtol=1e-4, atol=1e-6)
     torch.testing.assert_close(loss.detach().cpu(), loss_ref.detach(), rtol=1e-5, atol=1e-6)
     ref_grads = dict(ref.named_parameters())
     for n, p in model.named_parameters():
