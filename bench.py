@@ -164,6 +164,8 @@ def batch_bytes(batch):
 def to_data(batch, device, data_cls, non_blocking=False):
     fields = {k: batch[k].to(device, non_blocking=non_blocking) for k in TENSOR_FIELDS if k in batch}
     fields["num_graphs"] = batch["num_graphs"]
+    sizes = (batch["ptr"][1:] - batch["ptr"][:-1]).double()
+    fields["sum_sq_nodes"] = int((sizes * sizes).sum())     # host-side, for the attention flop accounting
     return data_cls(**fields)
 
 
@@ -237,10 +239,7 @@ def run_b200(args):
 
     model = create_model(**spec["arch"])
     model = get_distributed_model(model)
-    if args.gps_segments == "graph":
-        for m in model.modules():
-            if m.__class__.__name__ == "GPSConv":
-                m.segments = "graph"
+    model.module.gps_segments = args.gps_segments      # "batch" = the reference's semantics
     optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3)
     model.train()
 
