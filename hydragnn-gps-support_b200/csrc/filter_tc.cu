@@ -329,7 +329,7 @@ struct WgradArgs {
 };
 
 template <int KB, bool GAUSS, int G, int R>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 k_wgrad_tn(const WgradArgs p) {
   constexpr int BE = 32;                               // edges per iteration (the MMA K extent)
   constexpr int GP = (G + 3) / 4 * 4;
@@ -337,12 +337,10 @@ k_wgrad_tn(const WgradArgs p) {
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float off_s[64];
-  // two stages of transposed operands: stage (it+1) is written while the MMAs of `it` run
-  constexpr int kStage = 2 * BE * (kFilt + KB);
-  auto AThi = [&](int st) { return smem + st * kStage; };
-  auto ATlo = [&](int st) { return smem + st * kStage + kFilt * BE; };
-  auto BThi = [&](int st) { return smem + st * kStage + 2 * kFilt * BE; };
-  auto BTlo = [&](int st) { return smem + st * kStage + 2 * kFilt * BE + KB * BE; };
+  // Two CTAs share an SM (64 KB of shared memory and <= 128 TMEM columns each): while one waits
+  // for its global loads or its MMAs, the other transposes its tile.
+  float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
+  float* BThi = ATlo + kFilt * BE;   float* BTlo = BThi + KB * BE;
   constexpr uint32_t kCols = KB < 32 ? 32 : KB;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
@@ -350,26 +348,27 @@ k_wgrad_tn(const WgradArgs p) {
   if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
   __syncthreads();
 
-  const OperandDesc dA0 = operand_desc<BE>(AThi(0), ATlo(0)), dA1 = operand_desc<BE>(AThi(1), ATlo(1));
-  const OperandDesc dB0 = operand_desc<BE>(BThi(0), BTlo(0)), dB1 = operand_desc<BE>(BThi(1), BTlo(1));
+  const OperandDesc dA = operand_desc<BE>(AThi, ATlo), dB = operand_desc<BE>(BThi, BTlo);
   constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB);
-  Tile<BE, kFilt> ta0, ta1;                            // two register sets: loads run two tiles ahead
-  Tile<BE, KB> tb0, tb1;
+  Tile<BE, kFilt> ta;                                  // next tile, prefetched in registers
+  Tile<BE, KB> tb;
+  float dsc[Tile<BE, kFilt>::PER];                     // its row-scale arguments (d_e)
   float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);     // this thread's 4 columns of A, summed over its rows
   const float c2 = p.coeff * kLog2e;
 
-  auto fetch = [&](Tile<BE, kFilt>& ta, Tile<BE, KB>& tb, int64_t tile) {
+  auto fetch = [&](int64_t tile) {
     const int32_t row0 = (int32_t)(tile * BE);
     const int32_t row_end = (int32_t)p.E;
     ta.load(p.a, kFilt, row0, row_end);
+    // the row scale is only FETCHED here and applied in stage(): nothing in this function depends
+    // on the loads it has just issued
     if (p.scale_d != nullptr) {
 #pragma unroll
       for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
         int r, c;
         Tile<BE, kFilt>::coord(it, r, c);
-        const float dd = (row0 + r < row_end) ? __ldg(p.scale_d + row0 + r) : 0.f;
-        const float env = 0.5f * (__cosf(dd * p.pi_over_cutoff) + 1.0f);
-        ta.v[it].x *= env; ta.v[it].y *= env; ta.v[it].z *= env; ta.v[it].w *= env;
+        dsc[it] = 0.f;
+        if (row0 + r < row_end) asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(dsc[it]) : "l"(p.scale_d + row0 + r));
       }
     }
     if (!GAUSS) {
@@ -400,50 +399,41 @@ k_wgrad_tn(const WgradArgs p) {
       }
     }
   };
-  // registers -> stage st (and the bias-gradient partial sums of A)
-  auto stage = [&](const Tile<BE, kFilt>& ta, const Tile<BE, KB>& tb, int st) {
+  // registers -> shared memory (transposed, hi / lo) and the bias-gradient partial sums of A
+  auto stage = [&]() {
+    if (p.scale_d != nullptr) {
+#pragma unroll
+      for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
+        const float env = 0.5f * (__cosf(dsc[it] * p.pi_over_cutoff) + 1.0f);
+        ta.v[it].x *= env; ta.v[it].y *= env; ta.v[it].z *= env; ta.v[it].w *= env;
+      }
+    }
 #pragma unroll
     for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
       colsum.x += ta.v[it].x; colsum.y += ta.v[it].y; colsum.z += ta.v[it].z; colsum.w += ta.v[it].w;
     }
-    ta.store_transposed(AThi(st), ATlo(st));
-    tb.store_transposed(BThi(st), BTlo(st));
+    ta.store_transposed(AThi, ATlo);
+    tb.store_transposed(BThi, BTlo);
   };
 
   const int64_t num_tiles = (p.E + BE - 1) / BE;
   const int64_t stride = gridDim.x;
   uint32_t parity = 0;
   bool first = true;
-  int st = 0;
-  // one iteration: MMAs on stage `st` (tile), meanwhile registers `ra/rb` (tile + stride) -> stage
-  // st^1 and the loads of tile + 3 stride are issued into the same registers
-  auto iterate = [&](Tile<BE, kFilt>& ra, Tile<BE, KB>& rb, int64_t tile) {
-    publish_operands();                                // stage `st` complete and visible
+  if ((int64_t)blockIdx.x < num_tiles) fetch(blockIdx.x);
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += stride) {
+    stage();
+    publish_operands();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<BE>(tmem, st ? dA1 : dA0, st ? dB1 : dB0, kIdesc, !first);
+      mma3_ss<BE>(tmem, dA, dB, kIdesc, !first);
       mma_commit(&bar);
     }
     first = false;
-    if (tile + stride < num_tiles) {
-      stage(ra, rb, st ^ 1);
-      if (tile + 3 * stride < num_tiles) fetch(ra, rb, tile + 3 * stride);
-    }
+    if (tile + stride < num_tiles) fetch(tile + stride);       // in flight during the MMAs
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
-    st ^= 1;
-  };
-  const int64_t t0 = blockIdx.x;
-  if (t0 < num_tiles) {
-    fetch(ta0, tb0, t0);
-    stage(ta0, tb0, 0);
-    if (t0 + stride < num_tiles) fetch(ta1, tb1, t0 + stride);
-    if (t0 + 2 * stride < num_tiles) fetch(ta0, tb0, t0 + 2 * stride);
-  }
-  for (int64_t tile = t0; tile < num_tiles; tile += 2 * stride) {
-    iterate(ta1, tb1, tile);                           // registers 1 hold tile + stride
-    if (tile + stride < num_tiles) iterate(ta0, tb0, tile + stride);   // registers 0 hold tile + 2 stride
   }
 
   // ---- partial dW: lane n, this thread's KB/2 columns ----
@@ -528,7 +518,7 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   if (E <= 0) return 0;
-  return imin64(ceil_div(E, 32), kNumSM);
+  return imin64(ceil_div(E, 32), 2 * (int64_t)kNumSM);
 }
 
 extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, const float* scale_d,
@@ -553,7 +543,8 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
   const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
   cudaStream_t st = (cudaStream_t)stream;
   auto launch = [&](auto kernel, int kb) -> int {
-    const size_t smem = sizeof(float) * 2 * 2 * 32 * (tc::kFilt + kb);
+    size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + kb);
+    if (smem < 80 * 1024) smem = 80 * 1024;    // caps the occupancy at 2 CTAs per SM (register budget)
     cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
     kernel<<<grid, tc::kThreads, smem, st>>>(args);
