@@ -9,6 +9,6 @@ from .contract import (
     gather_mul_segment_sum,
     edge_gather_add,
 )
-from .radius import radius_graph, MODE_ASE, MODE_CLUSTER
+from .radius import radius_graph, radius_graph_pbc, MODE_ASE, MODE_CLUSTER
 from .attention import attn_varlen
 from .pna import pna_aggregate

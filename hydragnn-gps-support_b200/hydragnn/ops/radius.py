@@ -75,3 +75,115 @@ def radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=No
         g_of_edge = torch.bucketize(dst.long(), ptr32[1:].long(), right=True)
         out["edge_shifts"] = torch.einsum("ek,ekd->ed", shift.to(torch.float32), cell_t[g_of_edge])
     return out
+
+
+def _graphs_with_isolated_nodes(rowptr, graph_of_node, num_graphs):
+    isolated = rowptr[1:] == rowptr[:-1]
+    count = torch.zeros(num_graphs, dtype=torch.int64, device=rowptr.device)
+    count.index_add_(0, graph_of_node, isolated.to(torch.int64))     # integer adds: order independent
+    return count > 0, isolated
+
+
+def radius_graph_pbc(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=None,
+                     cutoff_multiplier=1.25, max_attempts=3):
+    """RadiusGraphPBC.__call__ for a whole batch of samples, including the part of it that is
+    per-sample control flow in the reference (graph_samples_checks_and_updates.py:163-221,284-307):
+    a sample in which some node receives no edge is searched again with the cutoff x1.25 (at most
+    `max_attempts` searches), and nodes still unconnected after the last search get one artificial
+    incoming edge from a random other node of the sample (zero shift, appended after the sample's
+    regular edges; the source is drawn with np.random.choice in ascending node order, like the
+    reference, so seeding numpy reproduces it).
+
+    Only the samples that need it are searched again -- as a sub-batch through the same kernels.
+    Returns the dict of `radius_graph` plus `edge_ptr` int64 [B+1] (edge offsets per sample, host)
+    and `cutoff` fp64 [B] (the cutoff each sample ended with); `rowptr` is None when artificial
+    edges were appended (they are not grouped by destination)."""
+    import numpy as np
+
+    if cell is None:
+        raise _hgk.HgkError("radius_graph_pbc needs a cell per sample")
+    dev = pos.device
+    ptr_d = ptr.to(device=dev, dtype=torch.int64)
+    B, N = ptr_d.numel() - 1, pos.size(0)
+    sizes = ptr_d[1:] - ptr_d[:-1]
+    graph_of_node = torch.repeat_interleave(torch.arange(B, device=dev), sizes)
+    cell_d = cell.detach().to(device=dev, dtype=torch.float32).reshape(B, 3, 3)
+    pbc_d = torch.as_tensor(pbc, device=dev).reshape(B, 3)
+    cutoffs = torch.full((B,), float(r), dtype=torch.float64)
+
+    g = radius_graph(pos, ptr_d, r, max_num_neighbors, loop, cell_d, pbc_d, mode=MODE_ASE)
+    bad, _ = _graphs_with_isolated_nodes(g["rowptr"], graph_of_node, B)
+    if max_attempts <= 1 or not bool(bad.any()):
+        g["edge_ptr"] = g["rowptr"].long()[ptr_d].cpu()
+        g["cutoff"] = cutoffs
+        return g
+
+    # edges of the samples that are complete, by search level; a sample is in exactly one level
+    edge_graph = graph_of_node[g["dst"].long()]
+    keep = ~bad[edge_graph]
+    parts = [dict(src=g["src"][keep].long(), dst=g["dst"][keep].long(), shift=g["shift_int"][keep],
+                  dist=g["dist"][keep], art=torch.zeros(int(keep.sum()), dtype=torch.int64, device=dev))]
+    todo = torch.nonzero(bad).flatten()                      # global sample ids still incomplete
+    cutoff = float(r)
+    for attempt in range(1, max_attempts):
+        cutoff *= cutoff_multiplier
+        cutoffs[todo.cpu()] = cutoff
+        sel = torch.zeros(B, dtype=torch.bool, device=dev)
+        sel[todo] = True
+        nodes = torch.nonzero(sel[graph_of_node]).flatten()  # global node ids of the sub-batch, ascending
+        sub_sizes = sizes[todo]
+        sub_ptr = torch.zeros(todo.numel() + 1, dtype=torch.int64, device=dev)
+        sub_ptr[1:] = torch.cumsum(sub_sizes, 0)
+        sub_gon = torch.repeat_interleave(torch.arange(todo.numel(), device=dev), sub_sizes)
+        sg = radius_graph(pos[nodes], sub_ptr, cutoff, max_num_neighbors, loop, cell_d[todo], pbc_d[todo],
+                          mode=MODE_ASE)
+        sub_bad, isolated = _graphs_with_isolated_nodes(sg["rowptr"], sub_gon, todo.numel())
+        last = attempt == max_attempts - 1
+        keep = torch.ones_like(sg["dst"], dtype=torch.bool) if last else ~sub_bad[sub_gon[sg["dst"].long()]]
+        parts.append(dict(src=nodes[sg["src"][keep].long()], dst=nodes[sg["dst"][keep].long()],
+                          shift=sg["shift_int"][keep], dist=sg["dist"][keep],
+                          art=torch.zeros(int(keep.sum()), dtype=torch.int64, device=dev)))
+        if last:
+            missing = nodes[isolated].cpu().numpy()          # ascending: sample order, node order inside
+            if missing.size:
+                ptr_h = ptr_d.cpu().numpy()
+                gon_h = graph_of_node.cpu().numpy()
+                a_src = []
+                for m in missing:
+                    lo, hi = int(ptr_h[gon_h[m]]), int(ptr_h[gon_h[m] + 1])
+                    local = np.arange(hi - lo)
+                    a_src.append(lo + (int(np.random.choice(local[local != m - lo])) if hi - lo > 1 else 0))
+                k = len(a_src)
+                parts.append(dict(src=torch.tensor(a_src, dtype=torch.int64, device=dev),
+                                  dst=torch.from_numpy(missing).to(dev),
+                                  shift=torch.zeros((k, 3), dtype=torch.int32, device=dev),
+                                  dist=torch.full((k,), cutoff - 1e-8, dtype=torch.float64, device=dev),
+                                  art=torch.ones(k, dtype=torch.int64, device=dev)))
+        else:
+            todo = todo[sub_bad]
+            if todo.numel() == 0:
+                break
+
+    cat = {k: torch.cat([p[k] for p in parts]) for k in parts[0]}
+    edge_graph = graph_of_node[cat["dst"]]
+    order = torch.sort(edge_graph * 2 + cat["art"], stable=True).indices
+    src, dst = cat["src"][order], cat["dst"][order]
+    shift, edge_graph = cat["shift"][order], edge_graph[order]
+    has_art = bool(cat["art"].any())
+    edge_ptr = torch.zeros(B + 1, dtype=torch.int64, device=dev)
+    edge_ptr[1:] = torch.cumsum(torch.bincount(edge_graph, minlength=B), 0)
+    rowptr = None
+    if not has_art:
+        rowptr = torch.zeros(N + 1, dtype=torch.int32, device=dev)
+        rowptr[1:] = torch.cumsum(torch.bincount(dst, minlength=N), 0)
+    return {
+        "edge_index": torch.stack([src, dst]),
+        "src": src.to(torch.int32),
+        "dst": dst.to(torch.int32),
+        "shift_int": shift,
+        "dist": cat["dist"][order],
+        "rowptr": rowptr,
+        "edge_shifts": torch.einsum("ek,ekd->ed", shift.to(torch.float32), cell_d[edge_graph]),
+        "edge_ptr": edge_ptr.cpu(),
+        "cutoff": cutoffs,
+    }

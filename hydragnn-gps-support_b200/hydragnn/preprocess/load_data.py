@@ -124,7 +124,7 @@ def _laplacian_pe(edge_index, num_nodes, k):
 def build_graphs(samples, arch, device):
     """Edges, edge lengths (normalised by the global maximum) and encodings for a list of samples,
     with ONE batched radius-graph call on `device` (reference: one call per sample on the CPU)."""
-    from ..ops import radius_graph
+    from ..ops import radius_graph, radius_graph_pbc
 
     if not samples:
         return samples
@@ -136,16 +136,19 @@ def build_graphs(samples, arch, device):
     if pbc:
         cell = torch.stack([d.cell.reshape(3, 3) for d in samples])
         pbc_flags = torch.ones(len(samples), 3, dtype=torch.bool)
-    g = radius_graph(pos, ptr, arch["radius"], arch["max_neighbours"], loop=False, cell=cell, pbc=pbc_flags)
+    if pbc:   # RadiusGraphPBC incl. cutoff expansion / artificial edges for unconnected nodes
+        g = radius_graph_pbc(pos, ptr, arch["radius"], arch["max_neighbours"], loop=False, cell=cell, pbc=pbc_flags)
+        edge_ptr = g["edge_ptr"]
+    else:     # edges are grouped by destination, i.e. by sample
+        g = radius_graph(pos, ptr, arch["radius"], arch["max_neighbours"], loop=False)
+        edge_ptr = g["rowptr"].long().cpu()[ptr]
     src, dst = g["src"].long(), g["dst"].long()
     vec = pos[dst] - pos[src]
     if pbc:
         vec = vec + g["edge_shifts"]
     length = vec.norm(dim=1, keepdim=True)
-    rowptr = g["rowptr"].long().cpu()
     src, dst, length = src.cpu(), dst.cpu(), length.cpu()
     shifts = g["edge_shifts"].cpu() if pbc else None
-    edge_ptr = rowptr[ptr]                      # edges are grouped by destination, i.e. by sample
     for k, d in enumerate(samples):
         a, b = int(edge_ptr[k]), int(edge_ptr[k + 1])
         d.edge_index = torch.stack([src[a:b], dst[a:b]]) - int(ptr[k])

@@ -698,3 +698,31 @@ def radius_graph_pbc(pos, cell, pbc, r, max_num_neighbors, loop=False):
         keep = (np.arange(j.size) - start) < max_num_neighbors
         i, j, d, S = i[keep], j[keep], d[keep], S[keep]
     return np.stack([i, j]).astype(np.int64), S.astype(np.int64), d
+
+
+def radius_graph_pbc_full(pos, cell, pbc, r, max_num_neighbors, loop=False,
+                          cutoff_multiplier=1.25, max_attempts=3):
+    """RadiusGraphPBC.__call__ with its retry loop (:163-206) and the artificial-edge fallback
+    `_ensure_connected` (:284-307).  The fallback draws from numpy's GLOBAL RNG exactly like the
+    reference (np.random.choice per missing node, ascending node order), so a caller that seeds
+    np.random the same way gets the same artificial sources.  Returns (edge_index, shift_int,
+    length, cutoff_used)."""
+    n = int(np.asarray(pos).shape[0])
+    cutoff = float(r)
+    for attempt in range(max_attempts):
+        ei, S, d = radius_graph_pbc(pos, cell, pbc, cutoff, max_num_neighbors, loop)
+        if np.unique(ei[1]).size == n:                                         # :196
+            break
+        if attempt < max_attempts - 1:                                         # :198-204
+            cutoff *= cutoff_multiplier
+            continue
+        nodes = np.arange(n)                                                   # :284-307
+        src, dst = list(ei[0]), list(ei[1])
+        for m in np.setdiff1d(nodes, np.unique(ei[1])):
+            s = np.random.choice(nodes[nodes != m]) if n > 1 else 0
+            src.append(int(s)); dst.append(int(m))
+        extra = len(src) - ei.shape[1]
+        ei = np.stack([np.asarray(src), np.asarray(dst)]).astype(np.int64)
+        S = np.concatenate([S, np.zeros((extra, 3), dtype=S.dtype)])
+        d = np.concatenate([d, np.full(extra, cutoff - 1e-8)])
+    return ei, S, d, cutoff

@@ -75,6 +75,7 @@ def cpu_kernels():
     import hydragnn.ops as ops_pkg
 
     scf_mod = importlib.import_module("hydragnn.models.SCFStack")
+    radius_mod = importlib.import_module("hydragnn.ops.radius")
 
     patches = [
         (contract, "_node_raw", _node_raw), (contract, "_edge_w_raw", _edge_w_raw),
@@ -82,7 +83,7 @@ def cpu_kernels():
         (pna, "_pna_fwd_raw", _pna_fwd_raw), (pna, "_pna_bwd_raw", _pna_bwd_raw),
         (attention, "_attn_fwd_raw", _attn_fwd_raw), (attention, "_attn_bwd_raw", _attn_bwd_raw),
         (topo, "build_csr", _build_csr), (ops_pkg, "radius_graph", _radius_graph),
-        (scf_mod, "radius_graph", _radius_graph),
+        (scf_mod, "radius_graph", _radius_graph), (radius_mod, "radius_graph", _radius_graph),
     ]
     saved = [(m, n, getattr(m, n)) for m, n, _ in patches]
     try:
