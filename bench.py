@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--gps-segments", default="batch", choices=["batch", "graph"],
                     help="batch = the reference's whole-mini-batch attention (SURVEY F3); graph = per-graph varlen")
     ap.add_argument("--graphs-per-gpu", type=int, default=0)
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling: fixed global batch split evenly over the ranks (SURVEY 8d: 64 for cfg 5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
@@ -232,6 +234,10 @@ def run_b200(args):
 
     spec = syn.WORKLOADS[args.workload]
     per_gpu = args.graphs_per_gpu or spec["graphs_per_gpu"]
+    if args.global_batch:
+        if args.global_batch % world:
+            raise SystemExit(f"--global-batch {args.global_batch} is not divisible by {world} ranks")
+        per_gpu = args.global_batch // world
     graphs = syn.sample_graphs(args.workload, per_gpu, rank=rank)
     host = build_batch_gpu(args.workload, graphs, device)
     pinned = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in host.items()}
@@ -328,7 +334,8 @@ def run_b200(args):
     result = {
         "metric": "train graphs/sec", "value": graphs_total * args.steps / (total_ms * 1e-3),
         "unit": "graphs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong" if args.global_batch else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "graphs_per_gpu": per_gpu, "global_batch": graphs_total,
                    "nodes_per_gpu": int(host["pos"].size(0)),

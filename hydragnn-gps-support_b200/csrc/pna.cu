@@ -62,31 +62,41 @@ k_pna_fwd(float* __restrict__ out, int32_t* __restrict__ cntmin, int32_t* __rest
   }
 }
 
+// Backward, destination-centric like the forward: the eleven per-node rows (gout x4, out x4, cntmin,
+// cntmax, P) are read once per destination and kept in registers while its edges stream by, instead
+// of once per edge (which made the kernel L2-bandwidth bound: 11 F floats per edge).
 template <int TPR>
 __global__ void __launch_bounds__(256)
 k_pna_bwd(float* __restrict__ gh, const float* __restrict__ gout, const float* __restrict__ out,
           const int32_t* __restrict__ cntmin, const int32_t* __restrict__ cntmax,
           const float* __restrict__ P, const float* __restrict__ Q, const float* __restrict__ R,
-          const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
-          const int32_t* __restrict__ dst, int64_t E, int F) {
+          const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
+          const int32_t* __restrict__ src, int64_t N, int F) {
   const int sub = (threadIdx.x & 31) % TPR;
-  const int64_t group = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / TPR;
-  const int64_t ngroups = ((int64_t)gridDim.x * blockDim.x) / TPR;
-  for (int64_t e = group; e < E; e += ngroups) {
-    const int64_t n = dst[e];
-    const int64_t s = src[e];
-    const float cnt = (float)(rowptr[n + 1] - rowptr[n]);
-    const float* o = out + n * 4 * F;
-    const float* g = gout + n * 4 * F;
-    for (int f = sub; f < F; f += TPR) {
-      float h = add_rn(P[n * F + f], Q[s * F + f]);
-      if (R) h = add_rn(h, R[e * F + f]);
-      float acc = g[f] / cnt;
-      if (h == o[F + f]) acc += g[F + f] / (float)cntmin[n * F + f];
-      if (h == o[2 * F + f]) acc += g[2 * F + f] / (float)cntmax[n * F + f];
-      const float sd = o[3 * F + f];
-      if (sd > 0.f) acc += g[3 * F + f] * (h - o[f]) / (cnt * sd);
-      gh[e * F + f] = acc;
+  const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / TPR;
+  if (n >= N) return;
+  const int32_t beg = rowptr[n], end = rowptr[n + 1];
+  if (end == beg) return;
+  const float cnt = (float)(end - beg);
+  const float* o = out + n * 4 * F;
+  const float* g = gout + n * 4 * F;
+  for (int f = sub; f < F; f += TPR) {
+    const float pn = P[n * F + f];
+    const float mean = o[f], omin = o[F + f], omax = o[2 * F + f], sd = o[3 * F + f];
+    const float g_mean = g[f] / cnt;
+    const float g_min = g[F + f] / (float)cntmin[n * F + f];
+    const float g_max = g[2 * F + f] / (float)cntmax[n * F + f];
+    const float g_sd = g[3 * F + f];
+    const float den = cnt * sd;
+    for (int32_t k = beg; k < end; ++k) {
+      const int32_t e = perm ? perm[k] : k;
+      float h = add_rn(pn, Q[(int64_t)src[e] * F + f]);
+      if (R) h = add_rn(h, R[(int64_t)e * F + f]);
+      float acc = g_mean;
+      if (h == omin) acc += g_min;
+      if (h == omax) acc += g_max;
+      if (sd > 0.f) acc += g_sd * (h - mean) / den;
+      gh[(int64_t)e * F + f] = acc;
     }
   }
 }
@@ -130,16 +140,16 @@ extern "C" int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntma
 extern "C" int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* out,
                                      const int32_t* cntmin, const int32_t* cntmax,
                                      const float* P, const float* Q, const float* R,
-                                     const int32_t* rowptr, const int32_t* src,
-                                     const int32_t* dst, int64_t N, int64_t E, int32_t F,
+                                     const int32_t* rowptr, const int32_t* perm,
+                                     const int32_t* src, int64_t N, int64_t E, int32_t F,
                                      void* stream) {
   HGK_REQUIRE(N >= 0 && E >= 0 && F >= 1, "pna_aggregate_bwd: bad sizes");
-  if (E == 0) return HGK_OK;
-  HGK_REQUIRE(gh && gout && out && cntmin && cntmax && P && Q && rowptr && src && dst,
+  if (E == 0 || N == 0) return HGK_OK;
+  HGK_REQUIRE(gh && gout && out && cntmin && cntmax && P && Q && rowptr && src,
               "pna_aggregate_bwd: NULL operand");
   const int tpr = pna_tpr(F);
-  const unsigned blocks = (unsigned)imin64(ceil_div(E * tpr, 256), (int64_t)kNumSM * 32);
+  const unsigned blocks = (unsigned)ceil_div(N * tpr, 256);
   cudaStream_t st = (cudaStream_t)stream;
-  HGK_PNA_DISPATCH(tpr, (k_pna_bwd<TPR><<<blocks, 256, 0, st>>>(gh, gout, out, cntmin, cntmax, P, Q, R, rowptr, src, dst, E, F)));
+  HGK_PNA_DISPATCH(tpr, (k_pna_bwd<TPR><<<blocks, 256, 0, st>>>(gh, gout, out, cntmin, cntmax, P, Q, R, rowptr, perm, src, N, F)));
   return check_launch("pna_aggregate_bwd");
 }

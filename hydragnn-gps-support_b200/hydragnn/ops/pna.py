@@ -27,13 +27,13 @@ def _pna_fwd_raw(P, Q, R, topo):
 
 def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo):
     N, F = P.shape
-    rowptr, _ = topo.csr(1)
+    rowptr, perm = topo.csr(1)
     gh = torch.empty((topo.E, F), dtype=torch.float32, device=P.device)
     E = topo.E
-    nbytes = E * (4 * F * (3 + (R is not None)) + 8) + N * (4 * F * 10)
+    nbytes = E * (4 * F * (2 + (R is not None)) + 8) + N * (4 * F * 11 + 4)
     _hgk.call("hgk_pna_aggregate_bwd", _hgk.ptr(gh), _hgk.ptr(gout.contiguous()), _hgk.ptr(out),
               _hgk.ptr(cmin), _hgk.ptr(cmax), _hgk.ptr(P), _hgk.ptr(Q), _hgk.ptr(R), _hgk.ptr(rowptr),
-              _hgk.ptr(topo.idx[0]), _hgk.ptr(topo.idx[1]), N, E, F, cost=(nbytes, 0))
+              _hgk.ptr(perm), _hgk.ptr(topo.idx[0]), N, E, F, cost=(nbytes, 0))
     return gh
 
 

@@ -194,12 +194,13 @@ int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntmax,
                           const int32_t* src, int64_t N, int64_t E, int32_t F,
                           void* stream);
 /* gh[e, f] = d loss / d h[e, f] given gout[N, 4F] and the forward's out /
- * cntmin / cntmax; dst[e] is the segment id of edge e. */
+ * cntmin / cntmax; rowptr / perm are the same destination CSR as in the
+ * forward (perm NULL when the edges are already grouped by destination). */
 int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* out,
                           const int32_t* cntmin, const int32_t* cntmax,
                           const float* P, const float* Q, const float* R,
-                          const int32_t* rowptr, const int32_t* src,
-                          const int32_t* dst, int64_t N, int64_t E, int32_t F,
+                          const int32_t* rowptr, const int32_t* perm,
+                          const int32_t* src, int64_t N, int64_t E, int32_t F,
                           void* stream);
 
 /* ------------------------------------------------------------------------- *
