@@ -1,6 +1,7 @@
 """CPU, gloo, world_size 2: the data-parallel plumbing (hydragnn.utils.distributed) -- same initial
 weights on every rank, gradients averaged across ranks through the flat-buffer GradientAverager,
 identical parameters after the optimizer step."""
+import copy
 import os
 import socket
 import sys
@@ -32,10 +33,14 @@ def _worker(rank, world, port, out_dir):
     opt = torch.optim.SGD(net.parameters(), lr=0.1)
     torch.manual_seed(7 + rank)
     x, y = torch.randn(5 + rank, 6), torch.randn(5 + rank, 1)    # each rank its own shard
+    # this rank's own gradient, from an unwrapped copy: the averager starts reducing chunks of the flat
+    # buffer while backward is still running, so p.grad of the wrapped net is not "local" any more
+    twin = copy.deepcopy(net)
+    torch.nn.functional.mse_loss(twin(x), y).backward()
+    local = [p.grad.clone() for p in twin.parameters()]
     model.zero_grad()
     loss = torch.nn.functional.mse_loss(model(x), y)
     loss.backward()
-    local = [p.grad.clone() for p in net.parameters()]
     model.finish_gradients()
     averaged = [p.grad.clone() for p in net.parameters()]
     opt.step()
