@@ -317,7 +317,7 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
 // Each CTA reduces its share of 64-edge tiles into a TMEM accumulator and writes ONE partial; the
 // partials are summed in a fixed order afterwards (deterministic, no atomics).
 struct WgradArgs {
-  const float* a;            // [E, 128]
+  const float* a; int64_t lda;   // [E, 128], row stride lda
   const float* scale_d;      // [E] or NULL: multiply row e of A by 0.5 (cos(d_e pi / r_c) + 1)
   float pi_over_cutoff;
   const float* b; int64_t ldb;                      // [E, KB] (GAUSS == false)
@@ -359,7 +359,7 @@ k_wgrad_tn(const WgradArgs p) {
   auto fetch = [&](int64_t tile) {
     const int32_t row0 = (int32_t)(tile * BE);
     const int32_t row_end = (int32_t)p.E;
-    ta.load(p.a, kFilt, row0, row_end);
+    ta.load(p.a, p.lda, row0, row_end);
     // the row scale is only FETCHED here and applied in stage(): nothing in this function depends
     // on the loads it has just issued
     if (p.scale_d != nullptr) {
@@ -518,17 +518,20 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   if (E <= 0) return 0;
-  return imin64(ceil_div(E, 32), 2 * (int64_t)kNumSM);
+  // two CTAs per SM; at least two 32-row tiles per CTA so that small inputs (node rows) do not
+  // write more partial sums than they read operands
+  return imin64(ceil_div(E, 64), 2 * (int64_t)kNumSM);
 }
 
-extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, const float* scale_d,
-                            float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
+extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, int64_t lda,
+                            const float* scale_d, float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
                             const float* raw, int64_t ldr, int32_t R, const float* offset, int32_t G,
                             float coeff, int64_t E, int32_t F, void* stream) {
   HGK_REQUIRE(E >= 0, "wgrad_tn: negative E");
   if (E == 0) return HGK_OK;
   HGK_REQUIRE(dw_partial && db_partial && a, "wgrad_tn: NULL operand");
   if (F != tc::kFilt) return fail(HGK_ERR_UNSUPPORTED, "wgrad_tn: built for 128-wide A (got %d)", F);
+  HGK_REQUIRE(lda >= F && lda % 4 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0, "wgrad_tn: A rows must be 16-byte aligned");
   const bool gauss = (b == nullptr);
   if (gauss) {
     HGK_REQUIRE(d && offset && (R == 0 || raw), "wgrad_tn: gaussian input needs d / offset / raw");
@@ -538,7 +541,7 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
     if (KB != 128) return fail(HGK_ERR_UNSUPPORTED, "wgrad_tn: built for KB=128 (got %d)", KB);
     HGK_REQUIRE(ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0, "wgrad_tn: B rows must be 16-byte aligned");
   }
-  tc::WgradArgs args{a, scale_d, 3.14159265358979323846f / cutoff, b, ldb, d, raw, ldr, offset, coeff,
+  tc::WgradArgs args{a, lda, scale_d, 3.14159265358979323846f / cutoff, b, ldb, d, raw, ldr, offset, coeff,
                      dw_partial, db_partial, E};
   const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
   cudaStream_t st = (cudaStream_t)stream;

@@ -53,7 +53,7 @@ _SIGNATURES = {
     "hgk_wgrad_tn_partials": (_c_i64, [_c_i64]),
     "hgk_wgrad_tn": (
         _c_i32,
-        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_i32,
          _c_ptr, _c_i32, _c_f32, _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_pna_aggregate_fwd": (

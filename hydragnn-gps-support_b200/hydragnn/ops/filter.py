@@ -51,6 +51,8 @@ def _wgrad_raw(a, scale_d, cutoff, b=None, gauss=None):
     """(dW [128, KB], db [128]) = (A^T B, colsum A); gauss = (dist, raw, offset, coeff) rebuilds B =
     [gauss(d) | raw] on the fly (KB = 64, the padded layout of the forward kernel)."""
     E, F = a.shape
+    if a.stride(1) != 1 or a.stride(0) % 4 or a.data_ptr() % 16:
+        a = a.contiguous()
     L = _hgk.lib()
     P = L.hgk_wgrad_tn_partials(E)
     KB = 64 if b is None else b.size(1)
@@ -65,7 +67,7 @@ def _wgrad_raw(a, scale_d, cutoff, b=None, gauss=None):
     else:
         args = (_hgk.ptr(b), b.stride(0), KB, _hgk.ptr(None), _hgk.ptr(None), 0, 0, _hgk.ptr(None), 0, 0.0)
         nbytes = E * 4 * (F + KB)
-    _hgk.call("hgk_wgrad_tn", _hgk.ptr(dw), _hgk.ptr(db), _hgk.ptr(a), _hgk.ptr(scale_d), float(cutoff), *args,
+    _hgk.call("hgk_wgrad_tn", _hgk.ptr(dw), _hgk.ptr(db), _hgk.ptr(a), a.stride(0), _hgk.ptr(scale_d), float(cutoff), *args,
               E, F, cost=(nbytes, 2 * E * F * KB))
     return dw.sum(0), db.sum(0)        # fixed-order reduction of the per-CTA partials
 

@@ -164,7 +164,8 @@ int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h,
                           int64_t E, int32_t F, void* stream);
 /* Weight / bias gradients of an edge-row Linear (reference: autograd of
  * nn.Linear on [E, .] inputs):  dW[n,k] = sum_e A[e,n] B[e,k],  db[n] =
- * sum_e A[e,n].  A is [E,128], optionally scaled per row by envelope(scale_d);
+ * sum_e A[e,n].  A is [E,128] (row stride lda, so a 128-column slice of a
+ * wider matrix works: node-level Linears of width 256 / 384), optionally scaled per row by envelope(scale_d);
  * B is [E,KB] (KB = 128), or, with b == NULL, the filter network's input
  * [gauss(d) | raw] in the 64-column layout of hgk_schnet_filter_fwd.
  * Each of the P = hgk_wgrad_tn_partials(E) CTAs writes one partial:
@@ -172,7 +173,7 @@ int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h,
  * order) gives the result -- deterministic, no atomics. */
 int64_t hgk_wgrad_tn_partials(int64_t E);
 int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a,
-                 const float* scale_d, float cutoff, const float* b, int64_t ldb,
+                 int64_t lda, const float* scale_d, float cutoff, const float* b, int64_t ldb,
                  int32_t KB, const float* d, const float* raw, int64_t ldr,
                  int32_t R, const float* offset, int32_t G, float coeff,
                  int64_t E, int32_t F, void* stream);
