@@ -465,6 +465,243 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   cta_teardown(tmem, kCols);
 }
 
+#ifdef HGK_KV_PROFILE
+// Phase timing of the pipelined dK/dV kernel (debug builds only: profiles/kv_phase_profile.py).
+__device__ unsigned long long g_kv_prof[8];
+__device__ __forceinline__ unsigned long long prof_clock() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
+  return t;
+}
+// accumulated in registers, flushed once: a global read-modify-write per sample would cost more
+// than the phases being measured
+#define KV_PROF_DECL unsigned long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long pt = prof_clock();
+#define KV_PROF(slot) { const unsigned long long now = prof_clock(); prof_acc[slot] += now - pt; pt = now; }
+#define KV_PROF_FLUSH if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) { for (int i = 0; i < 8; ++i) g_kv_prof[i] += prof_acc[i]; }
+#else
+#define KV_PROF_DECL
+#define KV_PROF(slot)
+#define KV_PROF_FLUSH
+#endif
+
+// ---- dK, dV: software pipelined, two compute groups, dedicated MMA-issuing warp ---------------
+// Same mapping as k_attn_bwd_kv_tc (CTA = 128 keys, TMEM lane = key).  What differs:
+//  * the query dimension is walked in steps of 32 with TWO sets of S^T / dP^T / P / dS columns;
+//  * compute group g (8 warps, two threads per key row, 16 query columns each) owns the steps
+//    s = g (mod 2) and column set g: while one group is waiting (TMEM load latency, the mbarrier,
+//    the proxy fence) the other one computes, and the tensor pipe runs the other group's
+//    dV / dK updates and S^T / dP^T products meanwhile;
+//  * a 17th warp does nothing but issue MMAs.  Issuing the 48 tcgen05.mma of one step costs the
+//    issuing thread ~1000 cycles (measured, profiles/kv_phase_profile.py); when that thread was
+//    also a compute thread every other warp waited for it at the next barrier.
+// Hand-offs: group g -> issuer through named barrier 2+g (bar.arrive, the group does not wait);
+// issuer -> group g through mbarrier g (tcgen05.commit).  For step s the issuer queues
+// [dV += P_s^T dO_s,  dK += dS_s^T Q_s,  S^T_{s+2} = K Q_{s+2}^T,  dP^T_{s+2} = V dO_{s+2}^T];
+// the MMAs of one thread execute in issue order, so S^T_{s+2} overwrites column set g only after
+// dV / dK of step s have read P_s / dS_s from it.  Four shared-memory stages: the stage written
+// during step s (for step s+2, same group) was last read by the MMAs of step s-2, which the
+// mbarrier wait at the top of step s has covered.
+constexpr int kKvPipeThreads = kKvThreads + 32;
+constexpr int kKvGroup = 256;                          // threads per compute group
+
+template <int D>
+__global__ void __launch_bounds__(kKvPipeThreads, 1)
+k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv) {
+  constexpr int BQ = 32;                               // queries per pipeline step
+  constexpr int QC = BQ / 2;                           // query columns per thread
+  constexpr int NST = 4;                               // shared-memory stages
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
+  __shared__ uint32_t tmem_slot;
+  __shared__ float lse2_s[NST][BQ], delta_s[NST][BQ];
+  int32_t seg_beg, seg_end, key0;
+  if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
+  const int h = blockIdx.y;
+  const int warp_u = warp_id_uniform();
+  const bool issuer = warp_u == kKvThreads / 32;       // warp 16
+
+  constexpr int kTile = BQ * D;                        // floats per operand tile
+  constexpr int kStage = 8 * kTile;                    // floats per stage
+  constexpr int oQhi = 0, oQlo = kTile;                // rows = queries (B of S^T)
+  constexpr int oGhi = 2 * kTile, oGlo = 3 * kTile;    // dO rows        (B of dP^T)
+  constexpr int oQThi = 4 * kTile, oQTlo = 5 * kTile;  // Q^T [D x BQ]   (B of dK)
+  constexpr int oGThi = 6 * kTile, oGTlo = 7 * kTile;  // dO^T [D x BQ]  (B of dV)
+
+  constexpr uint32_t kCols = 512;
+  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
+  constexpr uint32_t kColKhi = 256 + 2 * D, kColKlo = 256 + 3 * D, kColVhi = 256 + 4 * D, kColVlo = 256 + 5 * D;
+  static_assert(256 + 6 * D <= 512, "TMEM budget");
+  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }   // bar[0]: cta_setup, which also publishes all three
+  const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
+  const uint32_t tmem = cs.tmem;
+  const int nsub = (seg_end - seg_beg + BQ - 1) / BQ;
+  constexpr uint32_t kIdescS = idesc_tf32(BM, BQ);
+  constexpr uint32_t kIdescD = idesc_tf32(BM, D);
+
+  if (issuer) {
+    // ------------------------------------------------------------------ MMA-issuing warp ---
+    const OperandDesc dQ = operand_desc<D>(smem + oQhi, smem + oQlo), dG = operand_desc<D>(smem + oGhi, smem + oGlo);
+    const OperandDesc dQt = operand_desc<BQ>(smem + oQThi, smem + oQTlo), dGt = operand_desc<BQ>(smem + oGThi, smem + oGTlo);
+    auto at_stage = [](const OperandDesc& d, int st) {   // start-address field is in 16-byte units
+      const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
+      return OperandDesc{d.hi + adv, d.lo + adv};
+    };
+    auto issue_scores = [&](int s) {                   // S^T, dP^T of step s into column set s & 1
+      const uint32_t set = (uint32_t)(s & 1) * BQ;
+      mma3_ts<D>(tmem + kColST + set, tmem + kColKhi, tmem + kColKlo, at_stage(dQ, s & (NST - 1)), kIdescS, false);
+      mma3_ts<D>(tmem + kColDPT + set, tmem + kColVhi, tmem + kColVlo, at_stage(dG, s & (NST - 1)), kIdescS, false);
+    };
+    auto issue_updates = [&](int s) {                  // dV += P^T dO, dK += dS^T Q of step s
+      const uint32_t set = (uint32_t)(s & 1) * BQ;
+      mma3_ts<BQ>(tmem + kColDV, tmem + kColST + set, tmem + kColPlo + set, at_stage(dGt, s & (NST - 1)), kIdescD, s > 0);
+      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT + set, tmem + kColDSlo + set, at_stage(dQt, s & (NST - 1)), kIdescD, s > 0);
+    };
+    named_bar_sync(1, kKvPipeThreads);                 // K / V rows are in TMEM, stages 0 and 1 are written
+    fence_after_sync();
+    if (elect_one_sync()) {
+      issue_scores(0);
+      mma_commit(&bar[0]);
+      if (nsub > 1) { issue_scores(1); mma_commit(&bar[1]); }
+    }
+    __syncwarp();
+    for (int s = 0; s < nsub; ++s) {
+      const int g = s & 1;
+      named_bar_sync(2 + g, kKvGroup + 32);            // P_s, dS_s are in TMEM, stage of step s+2 is written
+      fence_after_sync();
+      if (elect_one_sync()) {
+        issue_updates(s);
+        if (s + 2 < nsub) issue_scores(s + 2);
+        mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[2]);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------- compute groups 0 and 1 ---
+    const int g = warp_u >> 3;                         // my group; it owns the steps s = g (mod 2)
+    const int part = cs.half;                          // warp / 4: 0..3 (K / V rows to TMEM, epilogue)
+    const int ch = part & 1;                           // my 16-column half of the step's 32 queries
+    {
+      const int64_t krow_ld = key0 + cs.row_local;
+      const bool kok = krow_ld < seg_end;
+      if (part < 2)
+        row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, part, 1.f);
+      else
+        row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, part - 2, 1.f);
+    }
+    // the group's next Q and dO tiles, prefetched in registers (one 16-byte chunk of each per thread)
+    Tile<BQ, D, kKvGroup, 0> tq0, tg0;
+    Tile<BQ, D, kKvGroup, kKvGroup> tq1, tg1;
+    float lse_r = 0.f, delta_r = 0.f;                  // next step's row statistics (first warp of the group)
+    const int tl = (int)threadIdx.x - g * kKvGroup;    // thread index inside the group
+    const float qmul = p.scale * kLog2e;
+    auto load = [&](int32_t q_at) {
+      if (g == 0) { tq0.load(p.q + h * D, p.ldq, q_at, seg_end); tg0.load(b.dout + h * D, b.lddo, q_at, seg_end); }
+      else        { tq1.load(p.q + h * D, p.ldq, q_at, seg_end); tg1.load(b.dout + h * D, b.lddo, q_at, seg_end); }
+      if (tl < BQ) {
+        const int32_t qrow = q_at + tl;
+        lse_r = 0.f; delta_r = 0.f;
+        if (qrow < seg_end) {
+          asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(lse_r) : "l"(b.lse + (int64_t)qrow * p.H + h));
+          asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(delta_r) : "l"(b.delta + (int64_t)qrow * p.H + h));
+        }
+      }
+    };
+    auto stage = [&](int st) {
+      float* base = smem + st * kStage;
+      if (g == 0) {
+        tq0.scale(qmul);
+        tq0.store_rows(base + oQhi, base + oQlo);  tq0.store_transposed(base + oQThi, base + oQTlo);
+        tg0.store_rows(base + oGhi, base + oGlo);  tg0.store_transposed(base + oGThi, base + oGTlo);
+      } else {
+        tq1.scale(qmul);
+        tq1.store_rows(base + oQhi, base + oQlo);  tq1.store_transposed(base + oQThi, base + oQTlo);
+        tg1.store_rows(base + oGhi, base + oGlo);  tg1.store_transposed(base + oGThi, base + oGTlo);
+      }
+      if (tl < BQ) {
+        lse2_s[st][tl] = lse_r * kLog2e;
+        delta_s[st][tl] = delta_r;
+      }
+    };
+
+    if (g < nsub) { load(seg_beg + g * BQ); stage(g); }
+    fence_smem_to_async();
+    fence_before_sync();
+    named_bar_arrive(1, kKvPipeThreads);
+    if (g + 2 < nsub) load(seg_beg + (g + 2) * BQ);    // after the fence: it would wait for these loads
+
+    uint32_t par = 0;
+    KV_PROF_DECL
+    for (int s = g; s < nsub; s += 2) {
+      KV_PROF(7)
+      mbar_wait(&bar[g], par);
+      par ^= 1;
+      fence_after_sync();
+      KV_PROF(0)
+
+      const int st = s & (NST - 1);
+      const int col0 = ch * QC;
+      const uint32_t set = (uint32_t)g * BQ;
+      const int32_t nvalid = seg_end - (seg_beg + s * BQ) - col0;   // my query columns [0, nvalid) exist
+      uint32_t sv[QC], dp[QC], plo[QC], dslo[QC];
+      tmem_ld16(tmem + cs.lane_base + kColST + set + col0, sv);
+      tmem_ld16(tmem + cs.lane_base + kColDPT + set + col0, dp);
+      tmem_ld_wait();
+      KV_PROF(1)
+#pragma unroll
+      for (int j = 0; j < QC; ++j) {
+        float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[st][col0 + j]);
+        if (j >= nvalid) pj = 0.f;
+        const float ds = pj * (__uint_as_float(dp[j]) - delta_s[st][col0 + j]);
+        float hi_, lo_;
+        split_tf32(pj, hi_, lo_);
+        sv[j] = __float_as_uint(hi_); plo[j] = __float_as_uint(lo_);
+        split_tf32(ds, hi_, lo_);
+        dp[j] = __float_as_uint(hi_); dslo[j] = __float_as_uint(lo_);
+      }
+      KV_PROF(2)
+      tmem_st16(tmem + cs.lane_base + kColST + set + col0, sv);
+      tmem_st16(tmem + cs.lane_base + kColPlo + set + col0, plo);
+      tmem_st16(tmem + cs.lane_base + kColDPT + set + col0, dp);
+      tmem_st16(tmem + cs.lane_base + kColDSlo + set + col0, dslo);
+      tmem_st_wait();
+      KV_PROF(3)
+
+      if (s + 2 < nsub) stage((s + 2) & (NST - 1));    // registers -> stage of my next step
+      KV_PROF(4)
+      fence_smem_to_async();
+      fence_before_sync();
+      named_bar_arrive(2 + g, kKvGroup + 32);
+      KV_PROF(5)
+      if (s + 4 < nsub) load(seg_beg + (s + 4) * BQ);  // global -> registers for the step after next
+      KV_PROF(6)
+    }
+    mbar_wait(&bar[2], 0);                             // committed after the last step's MMAs
+    fence_after_sync();
+    KV_PROF_FLUSH
+
+    static_assert(D == 32, "epilogue column split");
+    constexpr int EC = D / 2;                          // columns per thread
+    const int32_t krow = key0 + cs.row_local;
+    const bool ok = krow < seg_end;
+    const bool is_k = part >= 2;
+    const int chalf = part & 1;
+    uint32_t t[16];
+    tmem_ld16(tmem + cs.lane_base + (is_k ? kColDK : kColDV) + chalf * EC, t);
+    tmem_ld_wait();
+    if (ok) {
+      const float mul = is_k ? kLn2 : 1.f;             // Q was staged as q * scale * log2(e)
+      float* orow = (is_k ? dk : dv) + ((int64_t)krow * p.H + h) * D + chalf * EC;
+#pragma unroll
+      for (int j = 0; j < EC; j += 4)
+        *reinterpret_cast<float4*>(orow + j) =
+            make_float4(__uint_as_float(t[j]) * mul, __uint_as_float(t[j + 1]) * mul,
+                        __uint_as_float(t[j + 2]) * mul, __uint_as_float(t[j + 3]) * mul);
+    }
+  }
+  cta_teardown(tmem, kCols);
+}
+
 // ---------------------------------------------------------------------------------- launch ---
 template <typename K>
 int opt_in_smem(K kernel, size_t bytes, const char* what) {
@@ -493,9 +730,18 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
   // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
   size_t smem_kv = sizeof(float) * (2 * 8 * BN * D);
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
-  int rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
-  if (rc) return rc;
-  k_attn_bwd_kv_tc<D><<<grid, kKvThreads, smem_kv, st>>>(a, b, dk, dv);
+  // HGK_ATTN_KV_SERIAL=1 selects the unpipelined dK/dV kernel (A/B runs); read once
+  static const bool serial = [] { const char* e = getenv("HGK_ATTN_KV_SERIAL"); return e && e[0] == '1'; }();
+  int rc;
+  if (serial) {
+    rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
+    if (rc) return rc;
+    k_attn_bwd_kv_tc<D><<<grid, kKvThreads, smem_kv, st>>>(a, b, dk, dv);
+  } else {
+    rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
+    if (rc) return rc;
+    k_attn_bwd_kv_pipe<D><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv);
+  }
   size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
   if (smem_q < 80 * 1024) smem_q = 80 * 1024;
   rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
@@ -505,6 +751,16 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
 }
 
 }  // namespace tc
+
+#ifdef HGK_KV_PROFILE
+extern "C" int hgk_debug_kv_profile(unsigned long long* out8, int reset) {
+  unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaDeviceSynchronize();
+  if (out8) cudaMemcpyFromSymbol(out8, tc::g_kv_prof, sizeof(zero));
+  if (reset) cudaMemcpyToSymbol(tc::g_kv_prof, zero, sizeof(zero));
+  return 0;
+}
+#endif
 
 static bool tc_aligned(const void* ptr, int64_t ld) {
   return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && ld % 4 == 0;

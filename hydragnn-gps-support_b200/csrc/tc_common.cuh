@@ -96,6 +96,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---- named barriers: producers arrive and move on, the consumer warp waits ------------------------
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
+  asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(count) : "memory");
+}
+
 // ---- single-lane election inside a converged warp ------------------------------------------------
 // tcgen05.mma / commit take warp-uniform operands; issued under `if (elect_one_sync())` in a
 // warp-uniform branch the compiler emits them straight-line (under `if (threadIdx.x == 0)` it
@@ -157,6 +165,12 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
         "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+      : "r"(taddr) : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
@@ -201,12 +215,13 @@ constexpr float kLn2 = 0.6931471805599453f;
 constexpr uint32_t kLbo = 128;   // bytes between the two 16-byte K chunks of one MMA
 
 // ---- tile staging: global -> registers (prefetchable) -> shared memory --------------------------
-// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks.  Chunk idx (thread t owns t, t+256, ...) maps to
+// A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks, spread over the NT threads TOFF .. TOFF+NT-1
+// of the CTA (TOFF a multiple of 32).  Chunk idx (thread t owns t, t+NT, ...) maps to
 //   row r = idx % 8 + 8 * (idx / (8 * CH)),   16-byte column c = (idx / 8) % CH,      CH = D / 4
 // so the 32 lanes of a warp cover 8 consecutive rows x 4 columns: global reads are 64-byte runs,
 // and in the core-matrix layout the 8 rows of one column are 128 contiguous bytes -- both the row
 // store and the transposed store below are free of shared-memory bank conflicts.
-template <int ROWS, int D, int NT = kThreads>
+template <int ROWS, int D, int NT = kThreads, int TOFF = 0>
 struct Tile {
   static constexpr int CH = D / 4;
   static constexpr int PER = ROWS * CH / NT;
@@ -215,7 +230,7 @@ struct Tile {
   float4 v[PER];
 
   __device__ __forceinline__ static void coord(int it, int& r, int& c) {
-    const int idx = threadIdx.x + it * NT;
+    const int idx = (int)threadIdx.x - TOFF + it * NT;
     r = (idx & 7) + 8 * (idx / (8 * CH));
     c = (idx >> 3) % CH;
   }

@@ -109,7 +109,8 @@ def lib():
                 "`python hydragnn-gps-support_b200/csrc/build.py` "
                 "(or __graft_entry__.build()). There is no CPU fallback."
             )
-        handle = ctypes.CDLL(LIB_PATH)
+        # HGK_LIB: an instrumented build of the same sources (profiles/kv_phase_profile.py)
+        handle = ctypes.CDLL(os.environ.get("HGK_LIB") or LIB_PATH)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(handle, name)  # AttributeError if the symbol is absent
             fn.restype = res
