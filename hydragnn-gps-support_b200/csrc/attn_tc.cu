@@ -702,6 +702,164 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   cta_teardown(tmem, kCols);
 }
 
+// ---- dQ: the same pipeline, CTA = 128 queries (TMEM lane = query), 32-key steps ----------------
+// Q and dO rows (hi, lo) are resident in TMEM as the A operands of S = Q K^T and dP = dO V^T;
+// dS (hi, lo) overwrites the step's S / dP columns and is the A operand of dQ += dS K.
+template <int D>
+__global__ void __launch_bounds__(kKvPipeThreads, 1)
+k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dq) {
+  constexpr int BK = 32;                               // keys per pipeline step
+  constexpr int KC = BK / 2;                           // key columns per thread
+  constexpr int NST = 4;                               // shared-memory stages
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
+  __shared__ uint32_t tmem_slot;
+  int32_t seg_beg, seg_end, row0;
+  if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
+  const int h = blockIdx.y;
+  const int warp_u = warp_id_uniform();
+  const bool issuer = warp_u == kKvThreads / 32;       // warp 16
+
+  constexpr int kTile = BK * D;                        // floats per operand tile
+  constexpr int kStage = 6 * kTile;                    // floats per stage
+  constexpr int oKhi = 0, oKlo = kTile;                // rows = keys    (B of S)
+  constexpr int oVhi = 2 * kTile, oVlo = 3 * kTile;    // V rows         (B of dP)
+  constexpr int oKThi = 4 * kTile, oKTlo = 5 * kTile;  // K^T [D x BK]   (B of dQ)
+
+  constexpr uint32_t kCols = 512;
+  constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;
+  constexpr uint32_t kColQhi = 128 + D, kColQlo = 128 + 2 * D, kColGhi = 128 + 3 * D, kColGlo = 128 + 4 * D;
+  static_assert(128 + 5 * D <= 512, "TMEM budget");
+  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }
+  const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
+  const uint32_t tmem = cs.tmem;
+  const int nsub = (seg_end - seg_beg + BK - 1) / BK;
+  constexpr uint32_t kIdescS = idesc_tf32(BM, BK);
+  constexpr uint32_t kIdescQ = idesc_tf32(BM, D);
+
+  if (issuer) {
+    const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo), dV = operand_desc<D>(smem + oVhi, smem + oVlo);
+    const OperandDesc dKt = operand_desc<BK>(smem + oKThi, smem + oKTlo);
+    auto at_stage = [](const OperandDesc& d, int st) {
+      const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
+      return OperandDesc{d.hi + adv, d.lo + adv};
+    };
+    auto issue_scores = [&](int s) {                   // S, dP of step s into column set s & 1
+      const uint32_t set = (uint32_t)(s & 1) * BK;
+      mma3_ts<D>(tmem + kColS + set, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s & (NST - 1)), kIdescS, false);
+      mma3_ts<D>(tmem + kColDP + set, tmem + kColGhi, tmem + kColGlo, at_stage(dV, s & (NST - 1)), kIdescS, false);
+    };
+    named_bar_sync(1, kKvPipeThreads);                 // Q / dO rows are in TMEM, stages 0 and 1 are written
+    fence_after_sync();
+    if (elect_one_sync()) {
+      issue_scores(0);
+      mma_commit(&bar[0]);
+      if (nsub > 1) { issue_scores(1); mma_commit(&bar[1]); }
+    }
+    __syncwarp();
+    for (int s = 0; s < nsub; ++s) {
+      const int g = s & 1;
+      named_bar_sync(2 + g, kKvGroup + 32);            // dS_s is in TMEM, stage of step s+2 is written
+      fence_after_sync();
+      if (elect_one_sync()) {
+        const uint32_t set = (uint32_t)g * BK;
+        mma3_ts<BK>(tmem + kColDQ, tmem + kColS + set, tmem + kColDP + set, at_stage(dKt, s & (NST - 1)), kIdescQ, s > 0);
+        if (s + 2 < nsub) issue_scores(s + 2);
+        mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[2]);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int g = warp_u >> 3;                         // my group; it owns the steps s = g (mod 2)
+    const int part = cs.half;                          // warp / 4: 0..3
+    const int ch = part & 1;                           // my 16-column half of the step's 32 keys
+    const int32_t row = row0 + cs.row_local;
+    const bool row_ok = row < seg_end;
+    if (part < 2)
+      row_to_tmem<D>(tmem + cs.lane_base + kColQhi, tmem + cs.lane_base + kColQlo, p.q + h * D, p.ldq, row, row_ok, part,
+                     p.scale * kLog2e);
+    else
+      row_to_tmem<D>(tmem + cs.lane_base + kColGhi, tmem + cs.lane_base + kColGlo, b.dout + h * D, b.lddo, row, row_ok,
+                     part - 2, 1.f);
+    const float lse2 = row_ok ? b.lse[(int64_t)row * p.H + h] * kLog2e : 0.f;
+    const float delta = row_ok ? b.delta[(int64_t)row * p.H + h] : 0.f;
+
+    Tile<BK, D, kKvGroup, 0> tk0, tv0;                 // the group's next K and V tiles, in registers
+    Tile<BK, D, kKvGroup, kKvGroup> tk1, tv1;
+    auto load = [&](int32_t k_at) {
+      if (g == 0) { tk0.load(p.k + h * D, p.ldk, k_at, seg_end); tv0.load(p.v + h * D, p.ldv, k_at, seg_end); }
+      else        { tk1.load(p.k + h * D, p.ldk, k_at, seg_end); tv1.load(p.v + h * D, p.ldv, k_at, seg_end); }
+    };
+    auto stage = [&](int st) {
+      float* base = smem + st * kStage;
+      if (g == 0) {
+        tk0.store_rows(base + oKhi, base + oKlo);  tk0.store_transposed(base + oKThi, base + oKTlo);
+        tv0.store_rows(base + oVhi, base + oVlo);
+      } else {
+        tk1.store_rows(base + oKhi, base + oKlo);  tk1.store_transposed(base + oKThi, base + oKTlo);
+        tv1.store_rows(base + oVhi, base + oVlo);
+      }
+    };
+    if (g < nsub) { load(seg_beg + g * BK); stage(g); }
+    fence_smem_to_async();
+    fence_before_sync();
+    named_bar_arrive(1, kKvPipeThreads);
+    if (g + 2 < nsub) load(seg_beg + (g + 2) * BK);
+
+    uint32_t par = 0;
+    for (int s = g; s < nsub; s += 2) {
+      mbar_wait(&bar[g], par);
+      par ^= 1;
+      fence_after_sync();
+
+      const int col0 = ch * KC;
+      const uint32_t set = (uint32_t)g * BK;
+      const int32_t nvalid = seg_end - (seg_beg + s * BK) - col0;   // my key columns [0, nvalid) exist
+      uint32_t sv[KC], dv[KC];
+      tmem_ld16(tmem + cs.lane_base + kColS + set + col0, sv);
+      tmem_ld16(tmem + cs.lane_base + kColDP + set + col0, dv);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < KC; ++j) {
+        const float pj = fast_exp2(__uint_as_float(sv[j]) - lse2);
+        float ds = pj * (__uint_as_float(dv[j]) - delta);
+        if (j >= nvalid) ds = 0.f;                     // keys past the segment end contribute nothing
+        float hi_, lo_;
+        split_tf32(ds, hi_, lo_);
+        sv[j] = __float_as_uint(hi_);
+        dv[j] = __float_as_uint(lo_);
+      }
+      tmem_st16(tmem + cs.lane_base + kColS + set + col0, sv);
+      tmem_st16(tmem + cs.lane_base + kColDP + set + col0, dv);
+      tmem_st_wait();
+
+      if (s + 2 < nsub) stage((s + 2) & (NST - 1));
+      fence_smem_to_async();
+      fence_before_sync();
+      named_bar_arrive(2 + g, kKvGroup + 32);
+      if (s + 4 < nsub) load(seg_beg + (s + 4) * BK);
+    }
+    mbar_wait(&bar[2], 0);
+    fence_after_sync();
+
+    // four threads per row: D/4 columns each.  tcgen05.ld is warp-collective: everyone loads
+    constexpr int EC = D / 4;
+    static_assert(EC == 8, "epilogue column split");
+    uint32_t t[8];
+    tmem_ld8(tmem + cs.lane_base + kColDQ + part * EC, t);
+    tmem_ld_wait();
+    if (row_ok) {
+      float* drow = dq + ((int64_t)row * p.H + h) * D + part * EC;
+      *reinterpret_cast<float4*>(drow) = make_float4(__uint_as_float(t[0]) * p.scale, __uint_as_float(t[1]) * p.scale,
+                                                     __uint_as_float(t[2]) * p.scale, __uint_as_float(t[3]) * p.scale);
+      *reinterpret_cast<float4*>(drow + 4) = make_float4(__uint_as_float(t[4]) * p.scale, __uint_as_float(t[5]) * p.scale,
+                                                         __uint_as_float(t[6]) * p.scale, __uint_as_float(t[7]) * p.scale);
+    }
+  }
+  cta_teardown(tmem, kCols);
+}
+
 // ---------------------------------------------------------------------------------- launch ---
 template <typename K>
 int opt_in_smem(K kernel, size_t bytes, const char* what) {
@@ -730,8 +888,8 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
   // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
   size_t smem_kv = sizeof(float) * (2 * 8 * BN * D);
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
-  // HGK_ATTN_KV_SERIAL=1 selects the unpipelined dK/dV kernel (A/B runs); read once
-  static const bool serial = [] { const char* e = getenv("HGK_ATTN_KV_SERIAL"); return e && e[0] == '1'; }();
+  // HGK_ATTN_BWD_SERIAL=1 selects the unpipelined backward kernels (A/B runs); read once
+  static const bool serial = [] { const char* e = getenv("HGK_ATTN_BWD_SERIAL"); return e && e[0] == '1'; }();
   int rc;
   if (serial) {
     rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
@@ -742,11 +900,20 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     if (rc) return rc;
     k_attn_bwd_kv_pipe<D><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv);
   }
-  size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
-  if (smem_q < 80 * 1024) smem_q = 80 * 1024;
-  rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
-  if (rc) return rc;
-  k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
+  if (serial) {
+    size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
+    if (smem_q < 80 * 1024) smem_q = 80 * 1024;
+    rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
+    if (rc) return rc;
+    k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
+  } else {
+    // 512 TMEM columns: one CTA per SM, enforced through the shared-memory request as well
+    size_t smem_q = sizeof(float) * (4 * 6 * 32 * D);
+    if (smem_q < 120 * 1024) smem_q = 120 * 1024;
+    rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
+    if (rc) return rc;
+    k_attn_bwd_q_pipe<D><<<grid, kKvPipeThreads, smem_q, st>>>(a, b, dq);
+  }
   return check_launch("attn_varlen_bwd(tcgen05)");
 }
 
