@@ -183,6 +183,232 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
   cta_teardown(tmem, kCols);
 }
 
+// ---- forward, software pipelined --------------------------------------------------------------
+// CTA = 128 queries (TMEM lane = query), 544 threads: kFwdGroups compute groups of four warps (one
+// thread per query row, all 32 key columns of a step) and one MMA-issuing warp.  Group g owns the
+// 32-key steps s = g (mod kFwdGroups), its own TMEM column set (S -> P_hi in place, P_lo, its
+// output accumulator) and its own online-softmax state (reference max, row sum) over its steps;
+// the states are merged once at the end (the split-K form of the online softmax).
+// Hand-offs as in the backward kernels: group -> issuer through named barrier 2+g (bar.arrive),
+// issuer -> group through mbarrier g (tcgen05.commit).  For step s the issuer queues
+// [O_g += P_s V_s,  S_{s+G} = Q K_{s+G}^T]; while a group waits for its next scores the other
+// groups keep the ALUs and the TMEM ports busy.  Shared-memory ring of 2G stages: the stage
+// written during step s (for step s+G) was last read by step s-G, which the mbarrier wait at the
+// top of step s has covered.
+constexpr int kFwdGroups = 4;
+constexpr int kFwdGroup = 128;
+constexpr int kFwdThreads = kFwdGroups * kFwdGroup + 32;
+
+template <int D>
+__global__ void __launch_bounds__(kFwdThreads, 1)
+k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __restrict__ lse) {
+  constexpr int G = kFwdGroups;
+  constexpr int BK = 32;                               // keys per pipeline step
+  constexpr int NST = 2 * G;                           // shared-memory stages
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) uint64_t bar[G + 1];         // [g]: scores of group g are ready; [G]: everything done
+  __shared__ uint32_t tmem_slot;
+  int32_t seg_beg, seg_end, row0;
+  if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
+  const int h = blockIdx.y;
+  const int warp_u = warp_id_uniform();
+  const bool issuer = warp_u == G * kFwdGroup / 32;    // the last warp
+
+  constexpr int kTile = BK * D;
+  constexpr int kStage = 4 * kTile;                    // K rows hi/lo, V^T hi/lo
+  constexpr int oKhi = 0, oKlo = kTile, oVThi = 2 * kTile, oVTlo = 3 * kTile;
+  constexpr uint32_t kCols = 512;
+  constexpr uint32_t kColS = 0, kColPlo = G * BK, kColO = 2 * G * BK, kColQhi = 2 * G * BK + G * D,
+                     kColQlo = kColQhi + D;
+  static_assert(D == 32, "column sets are laid out for 32-wide heads");
+  static_assert(kColQlo + D <= kCols, "TMEM budget");
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 1; i <= G; ++i) mbar_init(&bar[i], 1);
+  }
+  const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4 = group (G: issuer)
+  const uint32_t tmem = cs.tmem;
+  const int nsub = (seg_end - seg_beg + BK - 1) / BK;
+  constexpr uint32_t kIdescS = idesc_tf32(BM, BK);
+  constexpr uint32_t kIdescO = idesc_tf32(BM, D);
+
+  if (issuer) {
+    const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo);
+    const OperandDesc dVt = operand_desc<BK>(smem + oVThi, smem + oVTlo);
+    auto at_stage = [](const OperandDesc& d, int st) {
+      const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
+      return OperandDesc{d.hi + adv, d.lo + adv};
+    };
+    auto issue_scores = [&](int s) {
+      mma3_ts<D>(tmem + kColS + (uint32_t)(s % G) * BK, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s % NST),
+                 kIdescS, false);
+    };
+    named_bar_sync(1, kFwdThreads);                    // Q rows are in TMEM, the first G stages are written
+    fence_after_sync();
+    if (elect_one_sync()) {
+      for (int s = 0; s < G && s < nsub; ++s) { issue_scores(s); mma_commit(&bar[s]); }
+    }
+    __syncwarp();
+    for (int s = 0; s < nsub; ++s) {
+      const int g = s % G;
+      named_bar_sync(2 + g, kFwdGroup + 32);           // P_s is in TMEM, stage of step s+G is written
+      fence_after_sync();
+      if (elect_one_sync()) {
+        mma3_ts<BK>(tmem + kColO + (uint32_t)g * D, tmem + kColS + (uint32_t)g * BK, tmem + kColPlo + (uint32_t)g * BK,
+                    at_stage(dVt, s % NST), kIdescO, s >= G);      // O_g += P_s V_s
+        if (s + G < nsub) issue_scores(s + G);
+        mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[G]);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int g = cs.half;                             // my group; it owns the steps s = g (mod G)
+    const int32_t row = row0 + cs.row_local;
+    const bool row_ok = row < seg_end;
+    // scores come out in the log2 domain: Q is pre-multiplied by scale * log2(e).  Groups 0 and 1
+    // write the two feature halves of every row.
+    if (g < 2)
+      row_to_tmem<D>(tmem + cs.lane_base + kColQhi, tmem + cs.lane_base + kColQlo, p.q + h * D, p.ldq, row, row_ok, g,
+                     p.scale * kLog2e);
+    Tile<BK, D, kFwdGroup, 0> tk, tv;                  // the group's next K and V tiles, in registers
+    const int tl = (int)threadIdx.x - g * kFwdGroup;   // thread index inside the group
+    auto load = [&](int32_t k_at) {
+      tk.load_as(tl, p.k + h * D, p.ldk, k_at, seg_end);
+      tv.load_as(tl, p.v + h * D, p.ldv, k_at, seg_end);
+    };
+    auto stage = [&](int st) {
+      float* base = smem + st * kStage;
+      tk.store_rows_as(tl, base + oKhi, base + oKlo);
+      tv.store_transposed_as(tl, base + oVThi, base + oVTlo);
+    };
+    if (g < nsub) { load(seg_beg + g * BK); stage(g); }
+    fence_smem_to_async();
+    fence_before_sync();
+    named_bar_arrive(1, kFwdThreads);
+    if (g + G < nsub) load(seg_beg + (g + G) * BK);
+
+    // The group's output accumulator stays in TMEM (the P V products accumulate into it); it is
+    // rescaled only when the running maximum has grown by more than 2^kLazy since the reference
+    // m_run was set (then, and only then, the 32 columns are read, scaled and written back).
+    // Until that happens P = 2^(s - m_run) may exceed 1 by up to 2^kLazy -- harmless in fp32.
+    constexpr float kLazy = 8.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const uint32_t t_s = tmem + cs.lane_base + kColS + (uint32_t)g * BK;
+    const uint32_t t_plo = tmem + cs.lane_base + kColPlo + (uint32_t)g * BK;
+    const uint32_t t_o = tmem + cs.lane_base + kColO + (uint32_t)g * D;
+    uint32_t par = 0;
+    for (int s = g; s < nsub; s += G) {
+      mbar_wait(&bar[g], par);                         // S_s is ready; P V of my previous step is complete
+      par ^= 1;
+      fence_after_sync();
+      uint32_t sv[BK];
+      tmem_ld32(t_s, sv);
+      tmem_ld_wait();
+      const int32_t nvalid = seg_end - (seg_beg + s * BK);   // key columns [0, nvalid) exist
+      if (nvalid < BK) {
+#pragma unroll
+        for (int j = 0; j < BK; ++j)
+          if (j >= nvalid) sv[j] = 0xff800000u;        // -inf
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int j = 0; j < BK; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(sv[j]));
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));   // finite: every step has a valid key
+      if (s == g) {
+        m_run = mx;                                    // first step: the issuer overwrites the accumulator
+      } else if (__any_sync(0xffffffffu, mx > m_run + kLazy)) {
+        const float m_new = mx > m_run + kLazy ? mx : m_run;
+        const float f = fast_exp2(m_run - m_new);      // 1 for the lanes that keep their reference
+        m_run = m_new;
+        l_run *= f;
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 16) {
+          uint32_t ot[16];
+          tmem_ld16(t_o + c0, ot);
+          tmem_ld_wait();
+#pragma unroll
+          for (int d = 0; d < 16; ++d) ot[d] = __float_as_uint(__uint_as_float(ot[d]) * f);
+          tmem_st16(t_o + c0, ot);
+        }
+      }
+      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c0 = 0; c0 < BK; c0 += 16) {
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float pj = fast_exp2(__uint_as_float(sv[c0 + j]) - m_run);
+          rs4[j & 3] += pj;
+          float hi_, lo_;
+          split_tf32(pj, hi_, lo_);
+          hi[j] = __float_as_uint(hi_);
+          lo[j] = __float_as_uint(lo_);
+        }
+        tmem_st16(t_s + c0, hi);
+        tmem_st16(t_plo + c0, lo);
+      }
+      l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+      tmem_st_wait();
+
+      if (s + G < nsub) stage((s + G) % NST);
+      fence_smem_to_async();
+      fence_before_sync();
+      named_bar_arrive(2 + g, kFwdGroup + 32);
+      if (s + 2 * G < nsub) load(seg_beg + (s + 2 * G) * BK);
+    }
+    mbar_wait(&bar[G], 0);                             // every MMA has completed
+    fence_after_sync();
+    float acc[D];
+    if (g < nsub) {
+      uint32_t ot[D];
+      tmem_ld32(t_o, ot);
+      tmem_ld_wait();
+#pragma unroll
+      for (int d = 0; d < D; ++d) acc[d] = __uint_as_float(ot[d]);
+    } else {
+#pragma unroll
+      for (int d = 0; d < D; ++d) acc[d] = 0.f;
+    }
+    // merge the groups' states: groups 1.. hand (m, l, acc) over through shared memory (the
+    // operand stages are free: all MMAs are complete)
+    constexpr int kX = (2 + D) * BM;                   // floats per group: m[128], l[128], acc[D][128]
+    if (g > 0) {
+      float* x = smem + (g - 1) * kX;
+      x[cs.row_local] = m_run;
+      x[BM + cs.row_local] = l_run;
+#pragma unroll
+      for (int d = 0; d < D; ++d) x[(2 + d) * BM + cs.row_local] = acc[d];
+    }
+    named_bar_sync(2 + G, G * kFwdGroup);
+    if (g == 0 && row_ok) {
+      float m = m_run;
+#pragma unroll
+      for (int i = 0; i < G - 1; ++i) m = fmaxf(m, smem[i * kX + cs.row_local]);
+      const float f0 = fast_exp2(m_run - m);
+      float l_tot = l_run * f0;
+#pragma unroll
+      for (int d = 0; d < D; ++d) acc[d] *= f0;
+#pragma unroll
+      for (int i = 0; i < G - 1; ++i) {
+        const float* x = smem + i * kX;
+        const float fi = fast_exp2(x[cs.row_local] - m);      // 0 for a group without steps (m = -inf)
+        l_tot = fmaf(x[BM + cs.row_local], fi, l_tot);
+#pragma unroll
+        for (int d = 0; d < D; ++d) acc[d] = fmaf(x[(2 + d) * BM + cs.row_local], fi, acc[d]);
+      }
+      const float inv = 1.f / l_tot;
+      float* orow = o + (int64_t)row * ldo + h * D;
+#pragma unroll
+      for (int d = 0; d < D; d += 4)
+        *reinterpret_cast<float4*>(orow + d) =
+            make_float4(acc[d] * inv, acc[d + 1] * inv, acc[d + 2] * inv, acc[d + 3] * inv);
+      lse[(int64_t)row * p.H + h] = (m + log2f(l_tot)) * kLn2;
+    }
+  }
+  cta_teardown(tmem, kCols);
+}
+
 // ================================================================================ backward ===
 struct AttnTcBwdArgs {
   const float* dout; int64_t lddo;
@@ -870,6 +1096,18 @@ int opt_in_smem(K kernel, size_t bytes, const char* what) {
 }
 
 template <int D>
+int launch_fwd_pipe(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
+  // one CTA per SM (512 TMEM columns): 8 operand stages of 16 KB
+  size_t smem = sizeof(float) * (2 * kFwdGroups * 4 * 32 * D);
+  if (smem < 120 * 1024) smem = 120 * 1024;
+  int rc = opt_in_smem(k_attn_fwd_pipe<D>, smem, "attn_fwd_pipe");
+  if (rc) return rc;
+  dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
+  k_attn_fwd_pipe<D><<<grid, kFwdThreads, smem, st>>>(a, o, ldo, lse);
+  return check_launch("attn_varlen_fwd(tcgen05, pipelined)");
+}
+
+template <int D>
 int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
   // 2 CTAs per SM: 256 TMEM columns each; the shared-memory request (> 1/3 of the SM) enforces it
   size_t smem = sizeof(float) * (4 * BN * D);
@@ -942,7 +1180,10 @@ int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, 
   if (!tc_aligned(q, ldq) || !tc_aligned(k, ldk) || !tc_aligned(v, ldv) || !tc_aligned(o, ldo)) return 1;
   AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
   if (D == 16) return tc::launch_fwd<16>(a, o, ldo, lse, N, st);
-  return tc::launch_fwd<32>(a, o, ldo, lse, N, st);
+  // HGK_ATTN_FWD_SERIAL=1 selects the unpipelined forward kernel (A/B runs); read once
+  static const bool serial = [] { const char* e = getenv("HGK_ATTN_FWD_SERIAL"); return e && e[0] == '1'; }();
+  if (serial) return tc::launch_fwd<32>(a, o, ldo, lse, N, st);
+  return tc::launch_fwd_pipe<32>(a, o, ldo, lse, N, st);
 }
 
 // Called by hgk_attn_varlen_bwd after delta = rowsum(dO * O) has been enqueued.  Same return

@@ -229,16 +229,26 @@ struct Tile {
   static_assert(CH % 4 == 0, "a warp spans 4 columns");
   float4 v[PER];
 
-  __device__ __forceinline__ static void coord(int it, int& r, int& c) {
-    const int idx = (int)threadIdx.x - TOFF + it * NT;
+  __device__ __forceinline__ static void coord_of(int tid, int it, int& r, int& c) {
+    const int idx = tid + it * NT;
     r = (idx & 7) + 8 * (idx / (8 * CH));
     c = (idx >> 3) % CH;
   }
+  __device__ __forceinline__ static void coord(int it, int& r, int& c) { coord_of((int)threadIdx.x - TOFF, it, r, c); }
+  // the *_as forms take the thread's index inside its group of NT threads explicitly (groups whose
+  // first thread is not a compile-time constant); the plain forms use threadIdx.x - TOFF
   __device__ __forceinline__ void load(const float* src, int64_t ld, int32_t row0, int32_t row_end) {
+    load_as((int)threadIdx.x - TOFF, src, ld, row0, row_end);
+  }
+  __device__ __forceinline__ void store_rows(float* hi, float* lo) const { store_rows_as((int)threadIdx.x - TOFF, hi, lo); }
+  __device__ __forceinline__ void store_transposed(float* hi, float* lo) const {
+    store_transposed_as((int)threadIdx.x - TOFF, hi, lo);
+  }
+  __device__ __forceinline__ void load_as(int tid, const float* src, int64_t ld, int32_t row0, int32_t row_end) {
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
       int r, c;
-      coord(it, r, c);
+      coord_of(tid, it, r, c);
       v[it] = make_float4(0.f, 0.f, 0.f, 0.f);          // rows past the segment end are zero
       // volatile asm: the load is issued HERE (a plain __ldg may be sunk to its first use, which
       // would put the whole L2 latency back on the critical path of the next iteration)
@@ -256,12 +266,12 @@ struct Tile {
     }
   }
   // hi / lo K-major tiles with MN index = row, K index = feature
-  __device__ __forceinline__ void store_rows(float* hi, float* lo) const {
+  __device__ __forceinline__ void store_rows_as(int tid, float* hi, float* lo) const {
     constexpr int SBO = CH * 32;
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
       int r, c;
-      coord(it, r, c);
+      coord_of(tid, it, r, c);
       float4 h, l;
       split_tf32(v[it].x, h.x, l.x); split_tf32(v[it].y, h.y, l.y);
       split_tf32(v[it].z, h.z, l.z); split_tf32(v[it].w, h.w, l.w);
@@ -273,14 +283,14 @@ struct Tile {
   // hi / lo K-major tiles of the TRANSPOSE: MN index = feature (D rows), K index = row (ROWS columns).
   // Lanes l, l^1, l^2, l^3 hold the same 16-byte column of 4 consecutive rows; a 4x4 register
   // transpose (4 shuffles) lets every lane write one 16-byte chunk: feature 4c + (l & 3), 4 rows.
-  __device__ __forceinline__ void store_transposed(float* hi, float* lo) const {
+  __device__ __forceinline__ void store_transposed_as(int tid, float* hi, float* lo) const {
     constexpr int SBO = (ROWS / 4) * 32;
     const int lane = threadIdx.x & 31;
     const int rr = lane & 3;                           // my row inside its group of 4
 #pragma unroll
     for (int it = 0; it < PER; ++it) {
       int r, c;
-      coord(it, r, c);
+      coord_of(tid, it, r, c);
       // 4x4 transpose across lanes l, l^1, l^2, l^3 in two butterfly stages; only selects (no
       // lane-dependent register indexing, which the compiler would turn into divergent branches)
       float w[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
