@@ -61,7 +61,8 @@ class GPSConv(torch.nn.Module):
         n = x.size(0)
         if cu_seqlens is None:
             if graph_batch is None:
-                cu_seqlens = torch.tensor([0, n], dtype=torch.int32, device=x.device)
+                cu_seqlens = torch.zeros(2, dtype=torch.int32, device=x.device)
+                cu_seqlens[1] = n                          # filled on the device: no blocking host copy
             else:
                 counts = torch.bincount(graph_batch)
                 cu_seqlens = torch.zeros(counts.numel() + 1, dtype=torch.int32, device=x.device)

@@ -25,6 +25,23 @@ from ..ops import segment_sum
 from ..utils.model import activation_function_selection, loss_function_selection
 
 
+_WHOLE_BATCH = {}
+
+
+def _whole_batch_segment(num_nodes, device):
+    """cu_seqlens = [0, N] on `device`, cached: torch.tensor(..., device=cuda) is a blocking copy
+    from pageable memory that drains the stream -- once per forward it kept the host from running
+    ahead of the GPU."""
+    key = (int(num_nodes), str(device))
+    cu = _WHOLE_BATCH.get(key)
+    if cu is None:
+        if len(_WHOLE_BATCH) > 64:
+            _WHOLE_BATCH.clear()
+        cu = torch.tensor([0, int(num_nodes)], dtype=torch.int32, device=device)
+        _WHOLE_BATCH[key] = cu
+    return cu.clone()      # device-side copy: callers attach attributes to it
+
+
 class Base(Module):
     def __init__(
         self,
@@ -291,7 +308,7 @@ class Base(Module):
             cu = data.ptr.to(device=device, dtype=torch.int32)
             sum_sq = getattr(data, "sum_sq_nodes", None)
         else:
-            cu = torch.tensor([0, num_nodes], dtype=torch.int32, device=device)
+            cu = _whole_batch_segment(num_nodes, device)
             sum_sq = num_nodes * num_nodes
         if sum_sq is not None:
             cu._hgk_sum_sq = int(sum_sq)

@@ -191,6 +191,12 @@ class SCFStack(Base):
                 conv_args["edge_attr"] = data.edge_attr
         else:
             conv_args = {"batch": data.batch}
+            if getattr(data, "ptr", None) is not None:
+                # graph offsets for the in-model radius graph without a device-side bincount (a sync)
+                try:
+                    data.batch._hgk_ptr = data.ptr.to(device=data.pos.device, dtype=torch.int32)
+                except Exception:
+                    pass
         if self.use_global_attn:
             return self._gps_embeddings(data, conv_args), data.pos, conv_args
         return data.x, data.pos, conv_args

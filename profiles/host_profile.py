@@ -54,6 +54,7 @@ def main():
     st = pstats.Stats(prof)
     st.sort_stats("tottime").print_stats(45)
     st.sort_stats("cumtime").print_stats(60)
+    st.print_callers("torch.tensor")
 
 
 if __name__ == "__main__":
