@@ -246,7 +246,7 @@ def run_b200(args):
     model = create_model(**spec["arch"])
     model = get_distributed_model(model)
     model.module.gps_segments = args.gps_segments      # "batch" = the reference's semantics
-    optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3)
+    optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3, fused=True)
     model.train()
 
     resident = to_data(host, device, Data)

@@ -95,7 +95,17 @@ def comm_reduce(x, op):
 
 
 class GradientAverager:
-    """Flat-buffer gradient mean across ranks, overlapped with backward."""
+    """Gradient mean across ranks through one flat fp32 buffer, overlapped with backward.
+
+    Gradients are NOT accumulated into the buffer by autograd (that costs one add kernel per
+    parameter per step): `zero_grad` sets them to None, so backward hands each parameter its
+    gradient tensor as is.  With more than one rank, a post-accumulate hook counts the parameters
+    of a chunk (reverse registration order = the order backward produces them); when a chunk is
+    complete its gradients are packed into the chunk's slice of the flat buffer with one `cat`,
+    the parameters' `.grad` are re-pointed at views of that slice, and the slice is all-reduced
+    asynchronously on a side stream while backward continues.  `finish()` waits, divides by the
+    world size, and leaves `.grad` = averaged views for the optimizer.  With one rank nothing is
+    packed at all."""
 
     def __init__(self, params, world_size=None, num_chunks=4, process_group=None):
         self.params = [p for p in params if p.requires_grad]
@@ -104,14 +114,13 @@ class GradientAverager:
         self.enabled = self.world_size > 1
         total = sum(p.numel() for p in self.params)
         dev = self.params[0].device if self.params else torch.device("cpu")
-        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat = torch.zeros(total if self.enabled else 0, dtype=torch.float32, device=dev)
         # reverse order: the last layers' gradients are produced first by backward
         order = list(reversed(self.params))
         per_chunk = max(1, -(-total // max(1, num_chunks)))
         self.chunks, self._chunk_of = [], {}
         off, start, members = 0, 0, []
         for p in order:
-            p.grad = self.flat[off:off + p.numel()].view_as(p)
             members.append(p)
             off += p.numel()
             if off - start >= per_chunk:
@@ -121,31 +130,44 @@ class GradientAverager:
             self._close_chunk(start, off, members)
         self._pending = [len(c["members"]) for c in self.chunks]
         self._works = []
-        self.stream = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        self.stream = torch.cuda.Stream(device=dev) if (dev.type == "cuda" and self.enabled) else None
+        for p in self.params:
+            p.grad = None
         if self.enabled:
             for p in self.params:
                 p.register_post_accumulate_grad_hook(self._on_grad_ready)
 
     def _close_chunk(self, start, stop, members):
         idx = len(self.chunks)
-        self.chunks.append({"view": self.flat[start:stop], "members": list(members)})
+        views, off = [], start
+        if self.enabled:
+            for p in members:
+                views.append(self.flat[off:off + p.numel()].view_as(p))
+                off += p.numel()
+        self.chunks.append({"view": self.flat[start:stop] if self.enabled else None, "members": list(members),
+                            "views": views})
         for p in members:
             self._chunk_of[p] = idx
 
     def zero_grad(self):
-        """Gradients stay views of the flat buffer (never set to None)."""
-        self.flat.zero_()
+        for p in self.params:
+            p.grad = None
         self._pending = [len(c["members"]) for c in self.chunks]
         self._works = []
 
     def _launch(self, idx):
-        view = self.chunks[idx]["view"]
+        chunk = self.chunks[idx]
+        # pack (parameters backward never reached contribute zeros), then hand .grad the views
+        parts = [(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in chunk["members"]]
+        torch.cat(parts, out=chunk["view"])
+        for p, v in zip(chunk["members"], chunk["views"]):
+            p.grad = v
         if self.stream is not None:
             self.stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.stream):
-                work = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                work = dist.all_reduce(chunk["view"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         else:
-            work = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            work = dist.all_reduce(chunk["view"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         self._works.append(work)
 
     def _on_grad_ready(self, p):

@@ -15,4 +15,8 @@ def select_optimizer(model, config):
         raise NotImplementedError("ZeroRedundancyOptimizer is not part of the B200 path (models are a few MB)")
     if kind not in _TABLE:
         raise NameError("The string used to identify the optimizer is NOT recognized by the code")
-    return _TABLE[kind](model.parameters(), lr=config["learning_rate"])
+    params = list(model.parameters())
+    kwargs = {}
+    if kind in ("Adam", "AdamW", "SGD") and params and all(p.is_cuda for p in params):
+        kwargs["fused"] = True      # one kernel for all parameters instead of a dozen foreach launches
+    return _TABLE[kind](params, lr=config["learning_rate"], **kwargs)

@@ -49,6 +49,13 @@ def main():
     print(f"# {name}: {total / 1e3:.2f} ms of kernel time per step, {sum(r[1] for r in rows):.0f} launches per step")
     for t, n, k in rows[:45]:
         print(f"{t / total * 100:6.2f}% {t:9.1f} us {n:6.1f}x  {k[:110]}")
+    # host side: ATen ops / autograd nodes by self CPU time
+    cpu = [(e.self_cpu_time_total / steps, e.count / steps, e.key) for e in prof.key_averages()
+           if e.device_type == torch.autograd.DeviceType.CPU]
+    cpu.sort(reverse=True)
+    print(f"# host: {sum(c[0] for c in cpu) / 1e3:.2f} ms of self CPU time per step in {sum(c[1] for c in cpu):.0f} ops")
+    for t, n, k in cpu[:60]:
+        print(f"{t:9.1f} us {n:6.1f}x  {k[:100]}")
 
 
 if __name__ == "__main__":
