@@ -2,7 +2,7 @@
 E ~ 474k edges grouped by destination, F = 128, 4 heads x 32) a few times, for `ncu` captures:
 
     python profiles/prof_kernels.py && ncu --set full --clock-control none --import-source on \
-        -k regex:'k_contract_node|k_attn' -c 12 -o gpurun_out/prof python profiles/prof_kernels.py
+        -k regex:'k_contract_node|k_attn|k_schnet|k_wgrad' -c 14 -o gpurun_out/prof python profiles/prof_kernels.py
 """
 import os
 import sys
@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "hydragnn-gps-support_b200"))
 
 from hydragnn import ops  # noqa: E402
-from hydragnn.ops import attention, contract  # noqa: E402
+from hydragnn.ops import attention, contract, filter as filt  # noqa: E402
 from hydragnn.ops.topo import Topo  # noqa: E402
 
 
@@ -32,7 +32,21 @@ def main(reps=3):
     cu = torch.tensor([0, N], dtype=torch.int32, device=dev)
     topo.csr(0), topo.csr(1)
     c = H * D
+    G = 50
+    d = (torch.rand(E, generator=gen) * 4.9 + 0.05).to(dev)
+    raw = torch.rand(E, 8, generator=gen).to(dev)
+    offset = torch.linspace(0, 5.0, G).to(dev)
+    coeff = -0.5 / float(offset[1] - offset[0]) ** 2
+    w0p = torch.zeros(F, 64, device=dev)
+    w0p[:, :G] = torch.randn(F, G, generator=gen).to(dev) * 0.1
+    w0p[:, 52:60] = torch.randn(F, 8, generator=gen).to(dev) * 0.1
+    b0 = torch.zeros(F, device=dev)
+    w1 = (torch.randn(F, F, generator=gen) * 0.1).to(dev)
     for _ in range(reps):
+        fw, fh = filt._filter_fwd_raw(d, raw, offset, coeff, 5.0, w0p, b0, w1, b0)      # filter network forward
+        dz0 = filt._filter_bwd_raw(W, fh, d, 5.0, w1.t().contiguous())                  # its backward (dZ0)
+        filt._wgrad_raw(W, d, 5.0, b=fh)                                                # dW1 (envelope-scaled A)
+        filt._wgrad_raw(dz0, None, 5.0, gauss=(d, raw, offset, coeff))                  # dW0 (gaussians rebuilt)
         contract._node_raw(topo, 1, x, 0, W, None, 1, 1, F)          # CFConv aggregate (streams W)
         contract._node_raw(topo, 0, x, 1, W, None, 1, 1, F)          # its backward w.r.t. x (perm gather)
         contract._edge_w_raw(topo, x, 1, x, 0, None, 1, F)           # its backward w.r.t. W
