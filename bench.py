@@ -53,7 +53,9 @@ def parse_args():
 
 # --------------------------------------------------------------------------- clocks ---
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed region runs.  ONE
+    sampler per job (rank 0 queries all the job's GPUs): eight nvidia-smi pollers next to eight
+    host-bound ranks on a 16-thread box cost more than a millisecond per step."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -63,6 +65,8 @@ class ClockSampler:
         self.index, self.rows, self.proc = index, [], None
 
     def __enter__(self):
+        if self.index is None:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
@@ -224,6 +228,7 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))   # ranks share the host cores
     torch.backends.cuda.matmul.allow_tf32 = False      # fp32 parity with the reference (rel 1e-5)
     torch.backends.cudnn.allow_tf32 = False
     if rank == 0:
@@ -285,7 +290,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     stops = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    with ClockSampler(local) as clocks:
+    with ClockSampler(",".join(str(i) for i in range(world)) if rank == 0 else None) as clocks:
         for i in range(args.steps):
             if flush is not None:
                 flush.fill_(float(i))        # evict L2 between timed steps (not timed)
