@@ -337,6 +337,7 @@ k_wgrad_tn(const WgradArgs p) {
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float off_s[64];
+  __shared__ __align__(16) float cs_s[2][kFilt];
   // Two CTAs share an SM (64 KB of shared memory and <= 128 TMEM columns each): while one waits
   // for its global loads or its MMAs, the other transposes its tile.
   float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
@@ -450,18 +451,21 @@ k_wgrad_tn(const WgradArgs p) {
           any ? make_float4(__uint_as_float(t[j]), __uint_as_float(t[j + 1]), __uint_as_float(t[j + 2]), __uint_as_float(t[j + 3]))
               : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  // ---- partial db: the 8 lanes that share a 16-byte column add up their rows ----
+  // ---- partial db: the 4 lanes that share a 16-byte column add up their rows; threads t and
+  // t + 128 hold the same column ----
 #pragma unroll
-  for (int off = 1; off < 8; off <<= 1) {
+  for (int off = 1; off < 4; off <<= 1) {
     colsum.x += __shfl_xor_sync(0xffffffffu, colsum.x, off);
     colsum.y += __shfl_xor_sync(0xffffffffu, colsum.y, off);
     colsum.z += __shfl_xor_sync(0xffffffffu, colsum.z, off);
     colsum.w += __shfl_xor_sync(0xffffffffu, colsum.w, off);
   }
-  if ((threadIdx.x & 7) == 0) {
-    const int c = (threadIdx.x >> 3) % (kFilt / 4);
-    *reinterpret_cast<float4*>(p.db_partial + (int64_t)blockIdx.x * kFilt + 4 * c) = colsum;
+  if ((threadIdx.x & 3) == 0) {
+    const int c = (threadIdx.x >> 2) % (kFilt / 4);
+    *reinterpret_cast<float4*>(&cs_s[threadIdx.x >> 7][4 * c]) = colsum;
   }
+  __syncthreads();
+  if (threadIdx.x < kFilt) p.db_partial[(int64_t)blockIdx.x * kFilt + threadIdx.x] = cs_s[0][threadIdx.x] + cs_s[1][threadIdx.x];
   cta_teardown(tmem, kCols);
 }
 
@@ -518,8 +522,8 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   if (E <= 0) return 0;
-  // two CTAs per SM; at least two 32-row tiles per CTA so that small inputs (node rows) do not
-  // write more partial sums than they read operands
+  // two CTAs per SM; at least two 32-row tiles per CTA so that small inputs do not write more
+  // partial sums than they read operands
   return imin64(ceil_div(E, 64), 2 * (int64_t)kNumSM);
 }
 

@@ -217,22 +217,24 @@ constexpr uint32_t kLbo = 128;   // bytes between the two 16-byte K chunks of on
 // ---- tile staging: global -> registers (prefetchable) -> shared memory --------------------------
 // A [ROWS x D] fp32 tile is ROWS * D/4 float4 chunks, spread over the NT threads TOFF .. TOFF+NT-1
 // of the CTA (TOFF a multiple of 32).  Chunk idx (thread t owns t, t+NT, ...) maps to
-//   row r = idx % 8 + 8 * (idx / (8 * CH)),   16-byte column c = (idx / 8) % CH,      CH = D / 4
-// so the 32 lanes of a warp cover 8 consecutive rows x 4 columns: global reads are 64-byte runs,
-// and in the core-matrix layout the 8 rows of one column are 128 contiguous bytes -- both the row
-// store and the transposed store below are free of shared-memory bank conflicts.
+//   row r = idx % 4 + 4 * (idx / (4 * CH)),   16-byte column c = (idx / 4) % CH,      CH = D / 4
+// so the 32 lanes of a warp cover 4 consecutive rows x 8 columns: a global read is four full
+// 128-byte lines (the LSU data pipe, not HBM, was the limiter with 64-byte runs: ncu showed it 90 %
+// busy in the weight-gradient kernel), and in the transposed store the 8 lanes of a store phase
+// write 8 different features of one k chunk = 128 contiguous bytes (no bank conflicts); the row
+// store pays a 2-way conflict instead (two columns of the same four rows share their banks).
 template <int ROWS, int D, int NT = kThreads, int TOFF = 0>
 struct Tile {
   static constexpr int CH = D / 4;
   static constexpr int PER = ROWS * CH / NT;
   static_assert(ROWS * CH % NT == 0, "tile must divide evenly over the CTA");
-  static_assert(CH % 4 == 0, "a warp spans 4 columns");
+  static_assert(CH % 4 == 0, "rows are whole 64-byte runs");
   float4 v[PER];
 
   __device__ __forceinline__ static void coord_of(int tid, int it, int& r, int& c) {
     const int idx = tid + it * NT;
-    r = (idx & 7) + 8 * (idx / (8 * CH));
-    c = (idx >> 3) % CH;
+    r = (idx & 3) + 4 * (idx / (4 * CH));
+    c = (idx >> 2) % CH;
   }
   __device__ __forceinline__ static void coord(int it, int& r, int& c) { coord_of((int)threadIdx.x - TOFF, it, r, c); }
   // the *_as forms take the thread's index inside its group of NT threads explicitly (groups whose
