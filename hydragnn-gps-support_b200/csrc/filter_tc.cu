@@ -52,6 +52,23 @@ __device__ __forceinline__ float shifted_softplus(float z) {
 
 constexpr int kFiltThreads = 512;   // 16 warps: 4 threads per row, 32 of the 128 columns each
 
+#ifdef HGK_KV_PROFILE
+// Phase timing of the forward filter kernel (debug builds only: profiles/filter_phase_profile.py)
+__device__ unsigned long long g_filt_prof[8];
+__device__ __forceinline__ unsigned long long fprof_clock() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
+  return t;
+}
+#define F_PROF_DECL unsigned long long fprof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long fpt = fprof_clock();
+#define F_PROF(slot) { const unsigned long long now = fprof_clock(); fprof_acc[slot] += now - fpt; fpt = now; }
+#define F_PROF_FLUSH if (threadIdx.x == 0 && blockIdx.x == 0) { for (int i = 0; i < 8; ++i) g_filt_prof[i] += fprof_acc[i]; }
+#else
+#define F_PROF_DECL
+#define F_PROF(slot)
+#define F_PROF_FLUSH
+#endif
+
 template <int G, int R>
 __global__ void __launch_bounds__(kFiltThreads, 1)
 k_schnet_filter_fwd(const FilterArgs p) {
@@ -91,7 +108,9 @@ k_schnet_filter_fwd(const FilterArgs p) {
   uint32_t parity = 0;
   const float c2 = p.coeff * kLog2e;
   const int64_t num_tiles = (p.E + kFilt - 1) / kFilt;
+  F_PROF_DECL
   for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    F_PROF(7)
     const int64_t e = tile * kFilt + cs.row_local;
     const bool ok = e < p.E;
     const float dist = ok ? __ldg(p.d + e) : 0.f;
@@ -132,16 +151,20 @@ k_schnet_filter_fwd(const FilterArgs p) {
       tmem_st16(tmem + cs.lane_base + kColXlo + quarter * 16, xl);
       tmem_st_wait();
     }
+    F_PROF(0)
     fence_before_sync();
     __syncthreads();
+    F_PROF(1)
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
       mma3_ts<kK0>(tmem + kColZ, tmem + kColXhi, tmem + kColXlo, dW0, kIdesc, false);   // Z0 = X W0'^T
       mma_commit(&bar);
     }
+    F_PROF(2)
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
+    F_PROF(3)
 
     // ---- H = ssp(Z0 + b0): my 32 columns ----
     const int c0 = quarter * 32;
@@ -171,6 +194,7 @@ k_schnet_filter_fwd(const FilterArgs p) {
       tmem_st32(tmem + cs.lane_base + kColHlo + c0, lo);
       tmem_st_wait();
     }
+    F_PROF(4)
     fence_before_sync();
     __syncthreads();
     if (warp_u == 0 && elect_one_sync()) {
@@ -179,9 +203,11 @@ k_schnet_filter_fwd(const FilterArgs p) {
       mma_commit(&bar);
     }
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);   // argument in [0, pi]
+    F_PROF(5)
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
+    F_PROF(6)
 
     // ---- W = (Z1 + b1) * C ----
     {
@@ -201,6 +227,8 @@ k_schnet_filter_fwd(const FilterArgs p) {
     }
     // the next tile's first barrier (after its X store) orders these Z reads before the next MMA
   }
+  F_PROF(7)
+  F_PROF_FLUSH
   cta_teardown(tmem, kCols);
 }
 
@@ -473,6 +501,16 @@ k_wgrad_tn(const WgradArgs p) {
 }  // namespace hgk
 
 using namespace hgk;
+
+#ifdef HGK_KV_PROFILE
+extern "C" int hgk_debug_filter_profile(unsigned long long* out8, int reset) {
+  unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaDeviceSynchronize();
+  if (out8) cudaMemcpyFromSymbol(out8, tc::g_filt_prof, sizeof(zero));
+  if (reset) cudaMemcpyToSymbol(tc::g_filt_prof, zero, sizeof(zero));
+  return 0;
+}
+#endif
 
 extern "C" int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const float* raw, int64_t ldr,
                                      int32_t R, const float* offset, int32_t G, float coeff, float cutoff,
