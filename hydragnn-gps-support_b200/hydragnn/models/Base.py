@@ -315,6 +315,15 @@ class Base(Module):
         return cu
 
     def forward(self, data):
+        pos = getattr(data, "pos", None)
+        if self.use_global_attn and pos is not None and pos.requires_grad:
+            # force loss: backward itself is differentiated, which a captured backward cannot provide
+            from ..globalAtt import graphed_tail
+            with graphed_tail.eager():
+                return self._forward(data)
+        return self._forward(data)
+
+    def _forward(self, data):
         inv_node_feat, equiv_node_feat, conv_args = self._embedding(data)
         if self.use_global_attn:
             conv_args["cu_seqlens"] = self._attention_segments(
