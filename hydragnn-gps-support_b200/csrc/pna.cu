@@ -1,5 +1,7 @@
 // PNA multi-aggregation: mean / min / max / std of the per-edge message
-// h[e,:] = P[dst(e),:] + Q[src[e],:] (+ R[e,:]) over each destination's edges.
+// h[e,:] = (P[dst(e),:] + Q[src[e],:] (+ R[e,:])) (* M[e,:]) over each destination's edges.
+// The optional per-edge multiplier M is PNAPlus's Hadamard product with the projected radial basis
+// (hydragnn/models/PNAPlusStack.py:275-283).
 //
 // Replaces PyG PNAConv.propagate + DegreeScalerAggregation as configured by
 // the reference (hydragnn/models/PNAStack.py:30-53: aggregators mean,min,max,
@@ -22,6 +24,7 @@ template <int TPR>
 __global__ void __launch_bounds__(256)
 k_pna_fwd(float* __restrict__ out, int32_t* __restrict__ cntmin, int32_t* __restrict__ cntmax,
           const float* __restrict__ P, const float* __restrict__ Q, const float* __restrict__ R,
+          const float* __restrict__ M,
           const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
           const int32_t* __restrict__ src, int64_t N, int F) {
   const int sub = (threadIdx.x & 31) % TPR;
@@ -38,6 +41,7 @@ k_pna_fwd(float* __restrict__ out, int32_t* __restrict__ cntmin, int32_t* __rest
       const int32_t e = perm ? perm[k] : k;
       float h = add_rn(pn, Q[(int64_t)src[e] * F + f]);
       if (R) h = add_rn(h, R[(int64_t)e * F + f]);
+      if (M) h = mul_rn(h, M[(int64_t)e * F + f]);
       sum = add_rn(sum, h);
       sumsq = add_rn(sumsq, mul_rn(h, h));
       if (h < mn) { mn = h; cmn = 1; } else if (h == mn) { ++cmn; }
@@ -67,10 +71,10 @@ k_pna_fwd(float* __restrict__ out, int32_t* __restrict__ cntmin, int32_t* __rest
 // of once per edge (which made the kernel L2-bandwidth bound: 11 F floats per edge).
 template <int TPR>
 __global__ void __launch_bounds__(256)
-k_pna_bwd(float* __restrict__ gh, const float* __restrict__ gout, const float* __restrict__ out,
-          const int32_t* __restrict__ cntmin, const int32_t* __restrict__ cntmax,
+k_pna_bwd(float* __restrict__ gh, float* __restrict__ gm, const float* __restrict__ gout,
+          const float* __restrict__ out, const int32_t* __restrict__ cntmin, const int32_t* __restrict__ cntmax,
           const float* __restrict__ P, const float* __restrict__ Q, const float* __restrict__ R,
-          const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
+          const float* __restrict__ M, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
           const int32_t* __restrict__ src, int64_t N, int F) {
   const int sub = (threadIdx.x & 31) % TPR;
   const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / TPR;
@@ -92,10 +96,17 @@ k_pna_bwd(float* __restrict__ gh, const float* __restrict__ gout, const float* _
       const int32_t e = perm ? perm[k] : k;
       float h = add_rn(pn, Q[(int64_t)src[e] * F + f]);
       if (R) h = add_rn(h, R[(int64_t)e * F + f]);
+      const float pre = h;
+      float m = 1.f;
+      if (M) { m = M[(int64_t)e * F + f]; h = mul_rn(h, m); }
       float acc = g_mean;
       if (h == omin) acc += g_min;
       if (h == omax) acc += g_max;
       if (sd > 0.f) acc += g_sd * (h - mean) / den;
+      if (M) {                                   // h = pre * m: hand back both factors' gradients
+        gm[(int64_t)e * F + f] = acc * pre;
+        acc *= m;
+      }
       gh[(int64_t)e * F + f] = acc;
     }
   }
@@ -122,7 +133,7 @@ using namespace hgk;
   }
 
 extern "C" int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntmax,
-                                     const float* P, const float* Q, const float* R,
+                                     const float* P, const float* Q, const float* R, const float* M,
                                      const int32_t* rowptr, const int32_t* perm,
                                      const int32_t* src, int64_t N, int64_t E, int32_t F,
                                      void* stream) {
@@ -133,13 +144,13 @@ extern "C" int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntma
   const int tpr = pna_tpr(F);
   const unsigned blocks = (unsigned)ceil_div(N * tpr, 256);
   cudaStream_t st = (cudaStream_t)stream;
-  HGK_PNA_DISPATCH(tpr, (k_pna_fwd<TPR><<<blocks, 256, 0, st>>>(out, cntmin, cntmax, P, Q, R, rowptr, perm, src, N, F)));
+  HGK_PNA_DISPATCH(tpr, (k_pna_fwd<TPR><<<blocks, 256, 0, st>>>(out, cntmin, cntmax, P, Q, R, M, rowptr, perm, src, N, F)));
   return check_launch("pna_aggregate_fwd");
 }
 
-extern "C" int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* out,
+extern "C" int hgk_pna_aggregate_bwd(float* gh, float* gm, const float* gout, const float* out,
                                      const int32_t* cntmin, const int32_t* cntmax,
-                                     const float* P, const float* Q, const float* R,
+                                     const float* P, const float* Q, const float* R, const float* M,
                                      const int32_t* rowptr, const int32_t* perm,
                                      const int32_t* src, int64_t N, int64_t E, int32_t F,
                                      void* stream) {
@@ -147,9 +158,10 @@ extern "C" int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* 
   if (E == 0 || N == 0) return HGK_OK;
   HGK_REQUIRE(gh && gout && out && cntmin && cntmax && P && Q && rowptr && src,
               "pna_aggregate_bwd: NULL operand");
+  HGK_REQUIRE(!M || gm, "pna_aggregate_bwd: M given without gm");
   const int tpr = pna_tpr(F);
   const unsigned blocks = (unsigned)ceil_div(N * tpr, 256);
   cudaStream_t st = (cudaStream_t)stream;
-  HGK_PNA_DISPATCH(tpr, (k_pna_bwd<TPR><<<blocks, 256, 0, st>>>(gh, gout, out, cntmin, cntmax, P, Q, R, rowptr, perm, src, N, F)));
+  HGK_PNA_DISPATCH(tpr, (k_pna_bwd<TPR><<<blocks, 256, 0, st>>>(gh, gm, gout, out, cntmin, cntmax, P, Q, R, M, rowptr, perm, src, N, F)));
   return check_launch("pna_aggregate_bwd");
 }

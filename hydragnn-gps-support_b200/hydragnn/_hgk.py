@@ -58,12 +58,12 @@ _SIGNATURES = {
     ),
     "hgk_pna_aggregate_fwd": (
         _c_i32,
-        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
          _c_i64, _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_pna_aggregate_bwd": (
         _c_i32,
-        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
          _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_radius_graph_workspace_bytes": (_c_i64, [_c_i64, _c_i64]),

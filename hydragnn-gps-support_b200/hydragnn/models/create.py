@@ -12,6 +12,7 @@ import torch
 from .EGCLStack import EGCLStack
 from .PAINNStack import PAINNStack
 from .PNAStack import PNAStack
+from .PNAPlusStack import PNAPlusStack
 from .SCFStack import SCFStack
 
 # Architecture keys, in the positional order of create_model (create.py:40-81 of the reference)
@@ -26,7 +27,7 @@ _ARCH_KEYS_TAIL = (
     "envelope_exponent", "num_spherical", "num_gaussians", "num_filters", "radius", "equivariance",
     "correlation", "max_ell", "node_max_ell", "avg_num_neighbors",
 )
-_NOT_ON_THIS_PATH = ("GIN", "GAT", "MFC", "SAGE", "CGCNN", "PNAPlus", "PNAEq", "DimeNet", "MACE")
+_NOT_ON_THIS_PATH = ("GIN", "GAT", "MFC", "SAGE", "CGCNN", "PNAEq", "DimeNet", "MACE")
 
 
 def create_model_config(config: dict, verbosity: int = 0, use_gpu: bool = True):
@@ -98,6 +99,13 @@ def create_model(
         assert pna_deg is not None, "PNA requires degree input."
         model = PNAStack("inv_node_feat, equiv_node_feat, edge_index", "inv_node_feat, edge_index",
                          pna_deg, edge_dim, *shared, **options)
+    elif mpnn_type == "PNAPlus":
+        assert pna_deg is not None, "PNAPlus requires degree input."
+        assert envelope_exponent is not None, "PNAPlus requires envelope_exponent input."
+        assert num_radial is not None, "PNAPlus requires num_radial input."
+        assert radius is not None, "PNAPlus requires radius input."
+        model = PNAPlusStack("inv_node_feat, equiv_node_feat, edge_index, rbf", "inv_node_feat, edge_index, rbf",
+                             pna_deg, edge_dim, envelope_exponent, num_radial, radius, *shared, **options)
     elif mpnn_type == "SchNet":
         assert num_gaussians is not None, "SchNet requires num_guassians input."
         assert num_filters is not None, "SchNet requires num_filters input."
@@ -115,7 +123,7 @@ def create_model(
         model = PAINNStack(signature, signature, edge_dim, num_radial, radius, *shared, **options)
     elif mpnn_type in _NOT_ON_THIS_PATH:
         raise NotImplementedError(
-            f"mpnn_type {mpnn_type} is not on the B200 hot path (SchNet, EGNN, PNA, PAINN are)")
+            f"mpnn_type {mpnn_type} is not on the B200 hot path (SchNet, EGNN, PNA, PNAPlus, PAINN are)")
     else:
         raise ValueError("Unknown mpnn_type: {0}".format(mpnn_type))
 

@@ -191,16 +191,18 @@ int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a,
  * ------------------------------------------------------------------------- */
 int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntmax,
                           const float* P, const float* Q, const float* R,
-                          const int32_t* rowptr, const int32_t* perm,
+                          const float* M, const int32_t* rowptr, const int32_t* perm,
                           const int32_t* src, int64_t N, int64_t E, int32_t F,
                           void* stream);
-/* gh[e, f] = d loss / d h[e, f] given gout[N, 4F] and the forward's out /
- * cntmin / cntmax; rowptr / perm are the same destination CSR as in the
- * forward (perm NULL when the edges are already grouped by destination). */
-int hgk_pna_aggregate_bwd(float* gh, const float* gout, const float* out,
+/* gh[e, f] = d loss / d (P[dst]+Q[src]+R[e])[f] given gout[N, 4F] and the
+ * forward's out / cntmin / cntmax; rowptr / perm are the same destination CSR
+ * as in the forward (perm NULL when the edges are already grouped by
+ * destination).  With the per-edge multiplier M (PNAPlus: h = (P+Q+R) * M,
+ * reference hydragnn/models/PNAPlusStack.py:275-283) gm[e, f] = d loss / d M. */
+int hgk_pna_aggregate_bwd(float* gh, float* gm, const float* gout, const float* out,
                           const int32_t* cntmin, const int32_t* cntmax,
                           const float* P, const float* Q, const float* R,
-                          const int32_t* rowptr, const int32_t* perm,
+                          const float* M, const int32_t* rowptr, const int32_t* perm,
                           const int32_t* src, int64_t N, int64_t E, int32_t F,
                           void* stream);
 

@@ -557,6 +557,69 @@ class PNAStack(Base):                                                          #
              "inv_node_feat, equiv_node_feat -> inv_node_feat, equiv_node_feat")])
 
 
+# -- models/PNAPlusStack.py -----------------------------------------------------
+class PNAPlusConv(pyg.MessagePassing):                                         # :144-283
+    """PNAConv with a radial basis: messages pre([x_i, x_j, e]) * rbf_lin(rbf), e = edge_encoder(
+    [edge_attr, rbf_emb(rbf)]) or rbf_emb(rbf); towers = 1, one pre / post Linear."""
+
+    def __init__(self, in_channels, out_channels, aggregators, scalers, deg, edge_dim=None, num_radial=5):
+        super().__init__(aggr=pyg.DegreeScalerAggregation(aggregators, scalers, deg), node_dim=0)
+        self.in_channels, self.out_channels, self.edge_dim = in_channels, out_channels, edge_dim
+        F_in = in_channels
+        self.pre_nns = nn.ModuleList([nn.Sequential(nn.Linear(3 * F_in, F_in))])
+        self.post_nns = nn.ModuleList([nn.Sequential(
+            nn.Linear((len(aggregators) * len(scalers) + 1) * F_in, out_channels))])
+        self.lin = nn.Linear(out_channels, out_channels)
+        self.rbf_lin = nn.Linear(num_radial, F_in, bias=False)
+        self.rbf_emb = nn.Sequential(nn.Linear(num_radial, F_in), nn.ReLU())
+        if edge_dim is not None:
+            self.edge_encoder = nn.Linear(F_in + edge_dim, F_in)
+
+    def forward(self, x, edge_index, rbf=None, edge_attr=None):                # :239-256
+        x = x.view(-1, 1, self.in_channels)
+        out = self.propagate(edge_index, x=x, edge_attr=edge_attr, rbf=rbf)
+        out = torch.cat([x, out], dim=-1)
+        return self.lin(self.post_nns[0](out[:, 0]))
+
+    def message(self, x_i, x_j, rbf=None, edge_attr=None):                     # :258-283
+        e = self.rbf_emb(rbf)
+        if edge_attr is not None:
+            e = self.edge_encoder(torch.cat([edge_attr, e], dim=-1))
+        h = torch.cat([x_i, x_j, e.view(-1, 1, self.in_channels)], dim=-1)
+        return self.pre_nns[0](h[:, 0]).unsqueeze(1) * self.rbf_lin(rbf).view(-1, 1, self.in_channels)
+
+
+class PNAPlusStack(Base):                                                      # :40-141
+    def __init__(self, input_args, conv_args, deg, edge_dim, envelope_exponent, num_radial, radius,
+                 *args, **kwargs):
+        self.aggregators = ["mean", "min", "max", "std"]
+        self.scalers = ["identity", "amplification", "attenuation", "linear"]
+        self.deg = torch.Tensor(deg)
+        self.edge_dim, self.envelope_exponent = edge_dim, envelope_exponent
+        self.num_radial, self.radius = num_radial, radius
+        self.is_edge_model = True
+        super().__init__(input_args, conv_args, *args, **kwargs)
+        self.rbf = pyg.BesselBasisLayer(num_radial, radius, envelope_exponent)
+
+    def get_conv(self, input_dim, output_dim, edge_dim=None):
+        pna = PNAPlusConv(input_dim, output_dim, self.aggregators, self.scalers, self.deg, edge_dim,
+                          self.num_radial)
+        return pyg.Sequential(self.input_args, [
+            (pna, self.conv_args + " -> inv_node_feat"),
+            (lambda inv_node_feat, equiv_node_feat: [inv_node_feat, equiv_node_feat],
+             "inv_node_feat, equiv_node_feat -> inv_node_feat, equiv_node_feat")])
+
+    def _embedding(self, data):                                                # :104-138
+        Base._embedding(self, data)
+        _, dist = get_edge_vectors_and_lengths(data.pos, data.edge_index, data.edge_shifts)
+        conv_args = {"edge_index": data.edge_index.to(torch.long), "rbf": self.rbf(dist.squeeze())}
+        if self.use_edge_attr:
+            conv_args["edge_attr"] = data.edge_attr
+        if self.use_global_attn:
+            return self._gps_embed(data, conv_args), data.pos, conv_args
+        return data.x, data.pos, conv_args
+
+
 # -- models/PAINNStack.py -------------------------------------------------------
 def sinc_expansion(edge_dist, num_radial, cutoff):                             # :322-329
     n = torch.arange(num_radial, device=edge_dist.device) + 1
@@ -658,7 +721,8 @@ def create_model(mpnn_type, input_dim, hidden_dim, output_dim, pe_dim, global_at
                  global_attn_type, global_attn_heads, output_type, output_heads, activation_function,
                  loss_function_type, task_weights, num_conv_layers, freeze_conv=False, initial_bias=None,
                  num_nodes=None, max_neighbours=None, edge_dim=None, pna_deg=None, num_radial=None,
-                 num_gaussians=None, num_filters=None, radius=None, equivariance=False, **unused):
+                 num_gaussians=None, num_filters=None, radius=None, equivariance=False,
+                 envelope_exponent=None, **unused):
     torch.manual_seed(0)                                                       # :131
     common = (input_dim, hidden_dim, output_dim, pe_dim, global_attn_engine, global_attn_type,
               global_attn_heads, output_type, output_heads, activation_function, loss_function_type,
@@ -668,6 +732,9 @@ def create_model(mpnn_type, input_dim, hidden_dim, output_dim, pe_dim, global_at
     if mpnn_type == "PNA":
         return PNAStack("inv_node_feat, equiv_node_feat, edge_index", "inv_node_feat, edge_index",
                         pna_deg, edge_dim, *common, **kw)
+    if mpnn_type == "PNAPlus":                                                  # create.py:185-214
+        return PNAPlusStack("inv_node_feat, equiv_node_feat, edge_index, rbf", "inv_node_feat, edge_index, rbf",
+                            pna_deg, edge_dim, envelope_exponent, num_radial, radius, *common, **kw)
     if mpnn_type == "SchNet":
         return SCFStack("", "inv_node_feat, equiv_node_feat, edge_index, edge_weight, edge_rbf",
                         num_filters, edge_dim, num_gaussians, radius, *common,

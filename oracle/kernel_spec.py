@@ -97,11 +97,13 @@ def edge_gather_add(P, pi, Q, qi):
 
 
 # hgk_pna_aggregate_fwd -- PyG PNAConv.propagate + aggregators mean,min,max,std (PNAStack.py:30-53)
-def pna_aggregate_fwd(P, Q, R, src, dst, N):
+def pna_aggregate_fwd(P, Q, R, src, dst, N, M=None):
     F = P.size(1)
     h = P.index_select(0, dst.long()) + Q.index_select(0, src.long())
     if R is not None:
         h = h + R
+    if M is not None:            # PNAPlus: Hadamard product with the projected radial basis
+        h = h * M
     idx = dst.long()
     mean = pyg.scatter(h, idx, 0, N, "mean")
     mn = pyg.scatter(h, idx, 0, N, "min")
@@ -117,12 +119,16 @@ def pna_aggregate_fwd(P, Q, R, src, dst, N):
 
 
 # hgk_pna_aggregate_bwd -- d/dh of the four aggregators (ties split evenly like scatter_reduce)
-def pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, src, dst, N):
+def pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, src, dst, N, M=None):
+    """-> gh, or (gh, gm) when the multiplier M is given."""
     F = P.size(1)
     idx = dst.long()
     h = P.index_select(0, idx) + Q.index_select(0, src.long())
     if R is not None:
         h = h + R
+    pre = h
+    if M is not None:
+        h = h * M
     cnt = torch.bincount(idx, minlength=N).to(torch.float32).unsqueeze(1)[idx]
     o, g = out[idx], gout[idx]
     gh = g[:, :F] / cnt
@@ -131,6 +137,8 @@ def pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, src, dst, N):
     sd = o[:, 3 * F:]
     safe = torch.where(sd > 0, sd, torch.ones_like(sd))
     gh = gh + torch.where(sd > 0, g[:, 3 * F:] * (h - o[:, :F]) / (cnt * safe), torch.zeros_like(h))
+    if M is not None:
+        return gh * M, gh * pre
     return gh
 
 

@@ -9,6 +9,7 @@ restated here, each piece citing the reference call site that depends on it:
       nn.Sequential             hydragnn/models/*Stack.py get_conv
       nn.MessagePassing(add)    hydragnn/models/SCFStack.py:214,285
       nn.PNAConv + DegreeScalerAggregation   hydragnn/models/PNAStack.py:43-53
+      nn.models.dimenet.BesselBasisLayer     hydragnn/models/PNAPlusStack.py:32,73
       nn.BatchNorm, global_mean_pool         hydragnn/models/Base.py:15,206,478
       nn.models.schnet.{GaussianSmearing, ShiftedSoftplus, RadiusInteractionGraph}
                                 hydragnn/models/SCFStack.py:21-25,58-61
@@ -169,13 +170,20 @@ class Sequential(torch.nn.Module):
 
 
 class MessagePassing(torch.nn.Module):
-    """Sum-aggregating message passing, flow source_to_target: x_j = x[edge_index[0]],
-    x_i = x[edge_index[1]], aggregation at edge_index[1]."""
+    """Message passing, flow source_to_target: x_j = x[edge_index[0]], x_i = x[edge_index[1]],
+    aggregation at edge_index[1] -- a sum, or an aggregation module called as
+    aggr(messages, index, dim_size) (PyG's `aggr_module`, e.g. DegreeScalerAggregation)."""
 
     def __init__(self, aggr="add", flow="source_to_target", node_dim=0, **kwargs):
         super().__init__()
-        assert aggr in ("add", "sum") and flow == "source_to_target" and node_dim == 0
-        self.aggr = aggr
+        assert flow == "source_to_target" and node_dim == 0
+        if isinstance(aggr, torch.nn.Module):
+            self.aggr_module = aggr
+            self.aggr = None
+        else:
+            assert aggr in ("add", "sum")
+            self.aggr_module = None
+            self.aggr = aggr
 
     def reset_parameters(self):
         pass
@@ -200,6 +208,8 @@ class MessagePassing(torch.nn.Module):
             else:
                 args.append(kwargs.get(p))
         msg = self.message(*args)
+        if self.aggr_module is not None:
+            return self.aggr_module(msg, edge_index[1], num_nodes)
         return scatter_add(msg, edge_index[1], 0, num_nodes)
 
 
@@ -410,6 +420,46 @@ class PNAConv(torch.nn.Module):
         out = torch.cat([x, out], dim=-1)
         outs = [nn(out[:, i]) for i, nn in enumerate(self.post_nns)]
         return self.lin(torch.cat(outs, dim=1))
+
+
+# ------------------------------------------------------- DimeNet radial basis ---
+class Envelope(torch.nn.Module):
+    """torch_geometric.nn.models.dimenet.Envelope: smooth polynomial cutoff on x = d / cutoff."""
+
+    def __init__(self, exponent: int):
+        super().__init__()
+        self.p = exponent + 1
+        self.a = -(self.p + 1) * (self.p + 2) / 2
+        self.b = self.p * (self.p + 2)
+        self.c = -self.p * (self.p + 1) / 2
+
+    def forward(self, x: Tensor) -> Tensor:
+        p, a, b, c = self.p, self.a, self.b, self.c
+        x_pow_p0 = x.pow(p - 1)
+        x_pow_p1 = x_pow_p0 * x
+        x_pow_p2 = x_pow_p1 * x
+        return (1.0 / x + a * x_pow_p0 + b * x_pow_p1 + c * x_pow_p2) * (x < 1.0).to(x.dtype)
+
+
+class BesselBasisLayer(torch.nn.Module):
+    """torch_geometric.nn.models.dimenet.BesselBasisLayer (used by PNAPlusStack.py:73-75,114):
+    envelope(d / cutoff) * sin(freq * d / cutoff), freq a parameter initialised to pi * (1..num_radial)."""
+
+    def __init__(self, num_radial: int, cutoff: float = 5.0, envelope_exponent: int = 5):
+        super().__init__()
+        self.cutoff = cutoff
+        self.envelope = Envelope(envelope_exponent)
+        self.freq = torch.nn.Parameter(torch.empty(num_radial))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        with torch.no_grad():
+            torch.arange(1, self.freq.numel() + 1, out=self.freq).mul_(math.pi)
+        self.freq.requires_grad_()
+
+    def forward(self, dist: Tensor) -> Tensor:
+        dist = dist.unsqueeze(-1) / self.cutoff
+        return self.envelope(dist) * (self.freq * dist).sin()
 
 
 # ----------------------------------------------------------- resolvers etc ---

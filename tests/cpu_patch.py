@@ -32,12 +32,13 @@ def _edge_gather_add_raw(topo, P, side_p, Q, side_q):
     return ks.edge_gather_add(P, topo.idx[side_p], Q, topo.idx[side_q])
 
 
-def _pna_fwd_raw(P, Q, R, topo):
-    return ks.pna_aggregate_fwd(P, Q, R, topo.idx[0], topo.idx[1], P.size(0))
+def _pna_fwd_raw(P, Q, R, topo, M=None):
+    return ks.pna_aggregate_fwd(P, Q, R, topo.idx[0], topo.idx[1], P.size(0), M)
 
 
-def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo):
-    return ks.pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, topo.idx[0], topo.idx[1], P.size(0))
+def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo, M=None):
+    res = ks.pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, topo.idx[0], topo.idx[1], P.size(0), M)
+    return res if M is not None else (res, None)
 
 
 def _attn_fwd_raw(q, k, v, cu, H, scale):

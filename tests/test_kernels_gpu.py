@@ -177,26 +177,34 @@ def test_autograd_closure_double_backward(ops):
 
 
 # ------------------------------------------------------------------------------ PNA ---
-@pytest.mark.parametrize("N,E,F,hasR", [(40, 300, 8, False), (40, 300, 8, True), (200, 3000, 128, True), (10, 0, 4, False)])
-def test_pna_aggregate(ops, N, E, F, hasR):
+@pytest.mark.parametrize("N,E,F,hasR,hasM", [(40, 300, 8, False, False), (40, 300, 8, True, False),
+                                              (200, 3000, 128, True, False), (10, 0, 4, False, False),
+                                              (40, 300, 8, False, True), (200, 3000, 64, True, True)])
+def test_pna_aggregate(ops, N, E, F, hasR, hasM):
     gen = torch.Generator().manual_seed(N + F)
     ei = random_graph(gen, N, E)
     # quantised values create exact ties for min / max
     P = torch.randint(-3, 4, (N, F), generator=gen).float() * 0.25
     Q = torch.randint(-3, 4, (N, F), generator=gen).float() * 0.25
     R = torch.randn(E, F, generator=gen) if hasR else None
+    M = torch.randint(-2, 3, (E, F), generator=gen).float() * 0.5 if hasM else None   # PNAPlus multiplier (zeros too)
     topo = make_topo(ops, ei, N)
     dev = lambda t: None if t is None else t.to(DEV)
-    out, cmin, cmax = ops["pna"]._pna_fwd_raw(dev(P), dev(Q), dev(R), topo)
-    want, wmin, wmax = ks.pna_aggregate_fwd(P, Q, R, ei[0], ei[1], N)
+    out, cmin, cmax = ops["pna"]._pna_fwd_raw(dev(P), dev(Q), dev(R), topo, dev(M))
+    want, wmin, wmax = ks.pna_aggregate_fwd(P, Q, R, ei[0], ei[1], N, M)
     F4 = out.size(1) // 4
     assert torch.equal(out.cpu()[:, F4:3 * F4], want[:, F4:3 * F4])          # min, max: exact
     assert torch.equal(cmin.cpu(), wmin) and torch.equal(cmax.cpu(), wmax)
     torch.testing.assert_close(out.cpu(), want, rtol=1e-5, atol=1e-6)        # mean, std
     gout = torch.randn(N, 4 * F, generator=gen)
-    gh = ops["pna"]._pna_bwd_raw(gout.to(DEV), out, cmin, cmax, dev(P), dev(Q), dev(R), topo)
-    want_gh = ks.pna_aggregate_bwd(gout, out.cpu(), cmin.cpu(), cmax.cpu(), P, Q, R, ei[0], ei[1], N)
-    torch.testing.assert_close(gh.cpu(), want_gh, rtol=1e-5, atol=1e-6)
+    gh, gm = ops["pna"]._pna_bwd_raw(gout.to(DEV), out, cmin, cmax, dev(P), dev(Q), dev(R), topo, dev(M))
+    res = ks.pna_aggregate_bwd(gout, out.cpu(), cmin.cpu(), cmax.cpu(), P, Q, R, ei[0], ei[1], N, M)
+    if hasM:
+        torch.testing.assert_close(gh.cpu(), res[0], rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(gm.cpu(), res[1], rtol=1e-5, atol=1e-6)
+    else:
+        assert gm is None
+        torch.testing.assert_close(gh.cpu(), res, rtol=1e-5, atol=1e-6)
 
 
 # ------------------------------------------------------------------------ attention ---
@@ -450,3 +458,36 @@ def test_segment_reductions_with_isolated_rows_and_long_segments(ops):
     want = ks.contract_node(ei[1].int(), N, x, ei[0].int(), W, None, 1, 1, F)
     assert torch.equal(got, want)
     assert float(got[:7].abs().max()) == 0.0 and float(got[200:].abs().max()) == 0.0
+
+
+def test_attn_varlen_double_backward(ops):
+    """create_graph=True through the attention op (a force loss on a GPS model whose node features
+    depend on the positions): the backward switches to differentiable torch ops; first and second
+    derivatives agree with a dense torch attention."""
+    from hydragnn.ops import attn_varlen
+
+    gen = torch.Generator().manual_seed(21)
+    sizes, H, D = [37, 5, 64], 4, 32
+    N = sum(sizes)
+    cu = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int32, device=DEV)
+    base = [torch.randn(N, H * D, generator=gen).to(DEV) for _ in range(3)]
+
+    def dense(q, k, v):
+        outs, b = [], 0
+        for L in sizes:
+            qs, ks, vs = (t[b:b + L].reshape(L, H, D).transpose(0, 1) for t in (q, k, v))
+            p = torch.softmax((qs @ ks.transpose(1, 2)) * D ** -0.5, dim=-1)
+            outs.append((p @ vs).transpose(0, 1).reshape(L, H * D))
+            b += L
+        return torch.cat(outs)
+
+    res = []
+    for fn in (lambda q, k, v: attn_varlen(q, k, v, cu, H), dense):
+        q, k, v = (t.clone().requires_grad_(True) for t in base)
+        e = (fn(q, k, v) ** 2).sum()
+        gq, gk = torch.autograd.grad(e, (q, k), create_graph=True)
+        loss = (gq * gq).sum() + (gk * v).sum()
+        loss.backward()
+        res.append((e.detach(), gq.detach(), loss.detach(), q.grad, k.grad, v.grad))
+    for a, b in zip(*res):
+        torch.testing.assert_close(a, b, rtol=2e-4, atol=2e-4)
