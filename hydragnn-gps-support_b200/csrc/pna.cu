@@ -34,12 +34,12 @@ k_pna_fwd(float* __restrict__ out, int32_t* __restrict__ cntmin, int32_t* __rest
   const int32_t deg = end - beg;
   const float sqrt_eps = sqrtf(kVarEps);
   for (int f = sub; f < F; f += TPR) {
-    const float pn = P[n * F + f];
+    const float pn = P ? P[n * F + f] : 0.f;
     float sum = 0.f, sumsq = 0.f, mn = INFINITY, mx = -INFINITY;
     int32_t cmn = 0, cmx = 0;
     for (int32_t k = beg; k < end; ++k) {
       const int32_t e = perm ? perm[k] : k;
-      float h = add_rn(pn, Q[(int64_t)src[e] * F + f]);
+      float h = Q ? add_rn(pn, Q[(int64_t)src[e] * F + f]) : pn;
       if (R) h = add_rn(h, R[(int64_t)e * F + f]);
       if (M) h = mul_rn(h, M[(int64_t)e * F + f]);
       sum = add_rn(sum, h);
@@ -85,7 +85,7 @@ k_pna_bwd(float* __restrict__ gh, float* __restrict__ gm, const float* __restric
   const float* o = out + n * 4 * F;
   const float* g = gout + n * 4 * F;
   for (int f = sub; f < F; f += TPR) {
-    const float pn = P[n * F + f];
+    const float pn = P ? P[n * F + f] : 0.f;
     const float mean = o[f], omin = o[F + f], omax = o[2 * F + f], sd = o[3 * F + f];
     const float g_mean = g[f] / cnt;
     const float g_min = g[F + f] / (float)cntmin[n * F + f];
@@ -94,7 +94,7 @@ k_pna_bwd(float* __restrict__ gh, float* __restrict__ gm, const float* __restric
     const float den = cnt * sd;
     for (int32_t k = beg; k < end; ++k) {
       const int32_t e = perm ? perm[k] : k;
-      float h = add_rn(pn, Q[(int64_t)src[e] * F + f]);
+      float h = Q ? add_rn(pn, Q[(int64_t)src[e] * F + f]) : pn;
       if (R) h = add_rn(h, R[(int64_t)e * F + f]);
       const float pre = h;
       float m = 1.f;
@@ -139,8 +139,9 @@ extern "C" int hgk_pna_aggregate_fwd(float* out, int32_t* cntmin, int32_t* cntma
                                      void* stream) {
   HGK_REQUIRE(N >= 0 && E >= 0 && F >= 1, "pna_aggregate_fwd: bad sizes");
   if (N == 0) return HGK_OK;
-  HGK_REQUIRE(out && cntmin && cntmax && P && Q && rowptr, "pna_aggregate_fwd: NULL operand");
-  HGK_REQUIRE(E == 0 || src, "pna_aggregate_fwd: src NULL");
+  HGK_REQUIRE(out && cntmin && cntmax && rowptr, "pna_aggregate_fwd: NULL operand");
+  HGK_REQUIRE(P || Q || R, "pna_aggregate_fwd: P, Q and R all NULL");
+  HGK_REQUIRE(E == 0 || !Q || src, "pna_aggregate_fwd: src NULL");
   const int tpr = pna_tpr(F);
   const unsigned blocks = (unsigned)ceil_div(N * tpr, 256);
   cudaStream_t st = (cudaStream_t)stream;
@@ -156,7 +157,7 @@ extern "C" int hgk_pna_aggregate_bwd(float* gh, float* gm, const float* gout, co
                                      void* stream) {
   HGK_REQUIRE(N >= 0 && E >= 0 && F >= 1, "pna_aggregate_bwd: bad sizes");
   if (E == 0 || N == 0) return HGK_OK;
-  HGK_REQUIRE(gh && gout && out && cntmin && cntmax && P && Q && rowptr && src,
+  HGK_REQUIRE(gh && gout && out && cntmin && cntmax && rowptr && (src || !Q) && (P || Q || R),
               "pna_aggregate_bwd: NULL operand");
   HGK_REQUIRE(!M || gm, "pna_aggregate_bwd: M given without gm");
   const int tpr = pna_tpr(F);

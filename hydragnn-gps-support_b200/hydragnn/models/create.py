@@ -13,6 +13,7 @@ from .EGCLStack import EGCLStack
 from .PAINNStack import PAINNStack
 from .PNAStack import PNAStack
 from .PNAPlusStack import PNAPlusStack
+from .PNAEqStack import PNAEqStack
 from .SCFStack import SCFStack
 
 # Architecture keys, in the positional order of create_model (create.py:40-81 of the reference)
@@ -27,7 +28,7 @@ _ARCH_KEYS_TAIL = (
     "envelope_exponent", "num_spherical", "num_gaussians", "num_filters", "radius", "equivariance",
     "correlation", "max_ell", "node_max_ell", "avg_num_neighbors",
 )
-_NOT_ON_THIS_PATH = ("GIN", "GAT", "MFC", "SAGE", "CGCNN", "PNAEq", "DimeNet", "MACE")
+_NOT_ON_THIS_PATH = ("GIN", "GAT", "MFC", "SAGE", "CGCNN", "DimeNet", "MACE")
 
 
 def create_model_config(config: dict, verbosity: int = 0, use_gpu: bool = True):
@@ -121,9 +122,13 @@ def create_model(
         assert radius is not None, "PAINN requires radius input."
         signature = "inv_node_feat, equiv_node_feat, edge_index, diff, dist"
         model = PAINNStack(signature, signature, edge_dim, num_radial, radius, *shared, **options)
+    elif mpnn_type == "PNAEq":
+        assert pna_deg is not None, "PNAEq requires degree input."
+        signature = "inv_node_feat, equiv_node_feat, edge_index, edge_rbf, edge_vec"
+        model = PNAEqStack(signature, signature, pna_deg, edge_dim, num_radial, radius, *shared, **options)
     elif mpnn_type in _NOT_ON_THIS_PATH:
         raise NotImplementedError(
-            f"mpnn_type {mpnn_type} is not on the B200 hot path (SchNet, EGNN, PNA, PNAPlus, PAINN are)")
+            f"mpnn_type {mpnn_type} is not on the B200 hot path (SchNet, EGNN, PNA, PNAPlus, PNAEq, PAINN are)")
     else:
         raise ValueError("Unknown mpnn_type: {0}".format(mpnn_type))
 

@@ -181,8 +181,11 @@ int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a,
 /* ------------------------------------------------------------------------- *
  * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
  * DegreeScalerAggregation with aggregators mean,min,max,std).
- * h[e,:] = P[dst(e),:] + Q[src[e],:] (+ R[e,:]) is formed in registers,
- * never stored.  Segments are destination rows n (dst(e) = n).
+ * h[e,:] = (P[dst(e),:] + Q[src[e],:] + R[e,:]) * M[e,:] is formed in
+ * registers, never stored; any of P, Q, R (not all) and M may be NULL (an
+ * edge-level message alone, R, is what PNAEqStack.py:371-377 aggregates).
+ * Segments are the rows n of the CSR handed in (rowptr / perm), `src` the
+ * endpoint on the other side.
  *   out[n, 0:F]=mean, [F:2F]=min, [2F:3F]=max, [3F:4F]=std
  *   std = sqrt(max(E[h^2]-E[h]^2, 1e-5)), zeroed where <= sqrt(1e-5);
  *   empty segment -> all zeros.  cntmin/cntmax[n,f] = number of edges of the

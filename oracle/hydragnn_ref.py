@@ -716,6 +716,111 @@ class PAINNStack(Base):                                                        #
         return x, v, conv_args
 
 
+# -- models/PNAEqStack.py --------------------------------------------------------
+def pnaeq_rbf(edge_dist, num_radial, cutoff):                                  # rbf_BasisLayer :453-493
+    """sinc expansion times the cosine cutoff; edge_dist is [E]."""
+    n = torch.arange(num_radial, device=edge_dist.device) + 1
+    sinc = torch.sin(edge_dist.unsqueeze(-1) * n * torch.pi / cutoff) / edge_dist.unsqueeze(-1)
+    cut = torch.where(edge_dist < cutoff, 0.5 * (torch.cos(torch.pi * edge_dist / cutoff) + 1),
+                      torch.tensor(0.0, dtype=edge_dist.dtype))
+    return sinc * cut.unsqueeze(-1)
+
+
+class PNAEqMessage(nn.Module):                                                 # PainnMessage :224-395
+    def __init__(self, node_size, x_aggregators, x_scalers, deg, edge_dim, num_radial):
+        super().__init__()
+        self.node_size, self.edge_dim = node_size, edge_dim
+        F_in = node_size
+        self.aggr_module = pyg.DegreeScalerAggregation(x_aggregators, x_scalers, deg)
+        self.pre_nns = nn.ModuleList([nn.Sequential(nn.Linear((4 if edge_dim else 3) * F_in, F_in))])
+        self.post_nns = nn.ModuleList([nn.Sequential(
+            nn.Linear((len(x_aggregators) * len(x_scalers) + 1) * F_in, F_in))])
+        self.rbf_emb = nn.Sequential(nn.Linear(num_radial, F_in), nn.Tanh())
+        if edge_dim is not None:
+            self.edge_encoder = nn.Linear(edge_dim, F_in)
+        self.rbf_lin = nn.Linear(num_radial, F_in * 3, bias=False)
+        self.scalar_message_mlp = nn.Sequential(nn.Linear(F_in, F_in), nn.Tanh(), nn.Linear(F_in, F_in),
+                                                nn.SiLU(), nn.Linear(F_in, F_in * 3))
+
+    def forward(self, x, v, edge_index, edge_rbf, edge_vec, edge_attr=None):   # :318-389
+        src, dst = edge_index.t()
+        parts = [x[src], x[dst], self.rbf_emb(edge_rbf)]
+        if edge_attr is not None:
+            parts.append(self.edge_encoder(edge_attr))
+        scalar_out = self.scalar_message_mlp(self.pre_nns[0](torch.cat(parts, dim=-1)))
+        filter_out = scalar_out * self.rbf_lin(edge_rbf)
+        g_sv, g_ev, m_s = torch.split(filter_out, self.node_size, dim=-1)
+        m_v = v[dst] * g_sv.unsqueeze(1) + g_ev.unsqueeze(1) * edge_vec.unsqueeze(-1)
+        agg = self.aggr_module(m_s, src, x.shape[0])
+        delta_x = self.post_nns[0](torch.cat([x, agg], dim=-1))
+        delta_v = torch.zeros_like(v).index_add_(0, src, m_v)
+        return x + delta_x, v + delta_v
+
+
+class PNAEqUpdate(nn.Module):                                                  # PainnUpdate :398-450
+    def __init__(self, node_size, last_layer=False):
+        super().__init__()
+        self.update_X = nn.Linear(node_size, node_size)
+        self.update_V = nn.Linear(node_size, node_size)
+        self.last_layer = last_layer
+        self.update_mlp = nn.Sequential(nn.Linear(node_size * 2, node_size), nn.SiLU(),
+                                        nn.Linear(node_size, node_size * (2 if last_layer else 3)))
+
+    def forward(self, x, v):
+        Xv, Vv = self.update_X(v), self.update_V(v)
+        a = self.update_mlp(torch.cat((torch.linalg.norm(Vv, dim=1), x), dim=-1))
+        inner = torch.sum(Xv * Vv, dim=1)
+        if self.last_layer:
+            a_xv, a_xx = torch.split(a, v.shape[-1], dim=-1)
+            return x + a_xv * inner + a_xx
+        a_vv, a_xv, a_xx = torch.split(a, x.shape[-1], dim=-1)
+        return x + a_xv * inner + a_xx, v + a_vv.unsqueeze(1) * Xv
+
+
+class PNAEqStack(Base):                                                        # :40-221
+    def __init__(self, input_args, conv_args, deg, edge_dim, num_radial, radius, *args, **kwargs):
+        self.x_aggregators = ["mean", "min", "max", "std"]
+        self.x_scalers = ["identity", "amplification", "attenuation", "linear", "inverse_linear"]
+        self.deg = torch.Tensor(deg)
+        self.edge_dim, self.num_radial, self.radius = edge_dim, num_radial, radius
+        self.is_edge_model = True
+        super().__init__(input_args, conv_args, *args, **kwargs)
+
+    def _init_conv(self):                                                      # :75-100
+        dims = [self.embed_dim] + [self.hidden_dim] * self.num_conv_layers
+        for k, (a, b) in enumerate(zip(dims[:-1], dims[1:])):
+            last = k == self.num_conv_layers - 1
+            self.graph_convs.append(self._apply_global_attn(self.get_conv(a, b, last, edge_dim=self.edge_embed_dim)))
+            self.feature_layers.append(nn.Identity())
+
+    def get_conv(self, input_dim, output_dim, last_layer=False, edge_dim=None):  # :102-176
+        assert (output_dim if input_dim == 1 else input_dim) > 1
+        msg = PNAEqMessage(input_dim, self.x_aggregators, self.x_scalers, self.deg, edge_dim, self.num_radial)
+        upd = PNAEqUpdate(input_dim, last_layer)
+        s_out = nn.Sequential(nn.Linear(input_dim, output_dim), nn.Tanh(), nn.Linear(output_dim, output_dim))
+        both = "inv_node_feat, equiv_node_feat -> inv_node_feat, equiv_node_feat"
+        steps = [(msg, self.conv_args + " -> inv_node_feat, equiv_node_feat")]
+        if not last_layer:
+            steps += [(upd, both), (s_out, "inv_node_feat -> inv_node_feat"),
+                      (nn.Linear(input_dim, output_dim), "equiv_node_feat -> equiv_node_feat")]
+        else:
+            steps += [(upd, "inv_node_feat, equiv_node_feat -> inv_node_feat"),
+                      (s_out, "inv_node_feat -> inv_node_feat")]
+        steps.append((lambda inv_node_feat, equiv_node_feat: [inv_node_feat, equiv_node_feat], both))
+        return pyg.Sequential(self.input_args, steps)
+
+    def _embedding(self, data):                                                # :178-221
+        Base._embedding(self, data)
+        unit, dist = get_edge_vectors_and_lengths(data.pos, data.edge_index, data.edge_shifts, normalize=True)
+        conv_args = {"edge_index": data.edge_index.t().to(torch.long),
+                     "edge_rbf": pnaeq_rbf(dist.squeeze(), self.num_radial, self.radius), "edge_vec": unit}
+        if self.use_edge_attr:
+            conv_args["edge_attr"] = data.edge_attr
+        x = self._gps_embed(data, conv_args) if self.use_global_attn else data.x
+        v = torch.zeros(x.size(0), 3, x.size(1))
+        return x, v, conv_args
+
+
 # -- models/create.py:86-519 (the four stacks on the hot path) -------------------
 def create_model(mpnn_type, input_dim, hidden_dim, output_dim, pe_dim, global_attn_engine,
                  global_attn_type, global_attn_heads, output_type, output_heads, activation_function,
@@ -732,6 +837,9 @@ def create_model(mpnn_type, input_dim, hidden_dim, output_dim, pe_dim, global_at
     if mpnn_type == "PNA":
         return PNAStack("inv_node_feat, equiv_node_feat, edge_index", "inv_node_feat, edge_index",
                         pna_deg, edge_dim, *common, **kw)
+    if mpnn_type == "PNAEq":                                                    # create.py:446-470
+        sig = "inv_node_feat, equiv_node_feat, edge_index, edge_rbf, edge_vec"
+        return PNAEqStack(sig, sig, pna_deg, edge_dim, num_radial, radius, *common, **kw)
     if mpnn_type == "PNAPlus":                                                  # create.py:185-214
         return PNAPlusStack("inv_node_feat, equiv_node_feat, edge_index, rbf", "inv_node_feat, edge_index, rbf",
                             pna_deg, edge_dim, envelope_exponent, num_radial, radius, *common, **kw)

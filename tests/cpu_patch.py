@@ -32,12 +32,23 @@ def _edge_gather_add_raw(topo, P, side_p, Q, side_q):
     return ks.edge_gather_add(P, topo.idx[side_p], Q, topo.idx[side_q])
 
 
-def _pna_fwd_raw(P, Q, R, topo, M=None):
-    return ks.pna_aggregate_fwd(P, Q, R, topo.idx[0], topo.idx[1], P.size(0), M)
+def _pna_operands(P, Q, R, topo, side):
+    """kernel_spec's functions take dense P / Q and aggregate at `dst`: zeros for absent operands,
+    endpoints swapped for side 0."""
+    first = next(t for t in (P, Q, R) if t is not None)
+    N, F = topo.num_rows[side], first.size(1)
+    zero = first.new_zeros((N, F))
+    return (zero if P is None else P, zero if Q is None else Q, topo.idx[1 - side], topo.idx[side], N)
 
 
-def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo, M=None):
-    res = ks.pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, topo.idx[0], topo.idx[1], P.size(0), M)
+def _pna_fwd_raw(P, Q, R, topo, M=None, side=1):
+    p, q, src, dst, N = _pna_operands(P, Q, R, topo, side)
+    return ks.pna_aggregate_fwd(p, q, R, src, dst, N, M)
+
+
+def _pna_bwd_raw(gout, out, cmin, cmax, P, Q, R, topo, M=None, side=1):
+    p, q, src, dst, N = _pna_operands(P, Q, R, topo, side)
+    res = ks.pna_aggregate_bwd(gout, out, cmin, cmax, p, q, R, src, dst, N, M)
     return res if M is not None else (res, None)
 
 
