@@ -122,6 +122,14 @@ WORKLOADS = {
                    output_heads=NODE_HEAD, num_nodes=120),
         sample=_oc20_slab, graphs_per_gpu=32, radius=6.0, max_neighbours=50, pbc=True,
         edges="radius", forces=True, seed=1238),
+    # the model of the reference's physics-informed multibranch configuration
+    # (PNAEq + force loss) on the OC20-shaped batch of configs[3]; degree histogram of a 50-neighbour cap
+    "pnaeq_oc20_forces": dict(
+        arch=_arch("PNAEq", num_conv_layers=3, num_radial=6, radius=6.0, output_type=["node"],
+                   output_heads=NODE_HEAD, num_nodes=120,
+                   pna_deg=[0] * 20 + [1, 2, 4, 8, 16, 32, 64, 128, 256, 512] + [1024] * 21),
+        sample=_oc20_slab, graphs_per_gpu=32, radius=6.0, max_neighbours=50, pbc=True,
+        edges="radius", forces=True, seed=1238),
     # configs[4] -- the multi-GPU headline
     "schnet_gps_fesi1024": dict(
         arch=_arch("SchNet", num_gaussians=50, num_filters=128, radius=5.0, max_neighbours=64,
