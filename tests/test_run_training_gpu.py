@@ -1,7 +1,7 @@
 """`-m gpu`: the public API end to end on the reference's CI toy problem (BASELINE config 1:
-tests/inputs/ci.json -- PNA, hidden 8, 2 conv layers, graph head): hydragnn.run_training then
-hydragnn.run_prediction, with the reference's own acceptance gate (test error below 0.20,
-reference tests/test_graphs.py:143-198)."""
+tests/inputs/ci.json -- hidden 8, 2 conv layers, graph head) for every stack on the B200 path:
+hydragnn.run_training then hydragnn.run_prediction, with the reference's own acceptance gates
+(reference tests/test_graphs.py:143-198)."""
 import copy
 import os
 
@@ -26,6 +26,7 @@ CI_CONFIG = {
         "Architecture": {
             "global_attn_engine": "", "global_attn_type": "", "mpnn_type": "PNA", "radius": 2.0,
             "max_neighbours": 100, "num_gaussians": 50, "num_filters": 126, "num_radial": 6,
+            "envelope_exponent": 5,
             "periodic_boundary_conditions": False, "pe_dim": 1, "global_attn_heads": 8, "hidden_dim": 8,
             "num_conv_layers": 2,
             "output_heads": {"graph": {"num_sharedlayers": 2, "dim_sharedlayers": 4, "num_headlayers": 2,
@@ -43,7 +44,12 @@ CI_CONFIG = {
 }
 
 
-@pytest.mark.parametrize("mpnn_type", ["PNA", "SchNet", "EGNN"])
+# RMSE / MAE gates of the reference (tests/test_graphs.py:143-158)
+GATES = {"PNA": (0.20, 0.20), "SchNet": (0.20, 0.20), "EGNN": (0.20, 0.20), "PNAPlus": (0.20, 0.20),
+         "PNAEq": (0.60, 0.60), "PAINN": (0.60, 0.60)}
+
+
+@pytest.mark.parametrize("mpnn_type", sorted(GATES))
 def test_run_training_then_prediction_on_ci_toy(libhgk, tmp_path, monkeypatch, mpnn_type):
     import hydragnn
 
@@ -60,4 +66,4 @@ def test_run_training_then_prediction_on_ci_toy(libhgk, tmp_path, monkeypatch, m
     assert true_values[0].shape == predicted[0].shape and true_values[0].shape[0] == 75
     rmse = torch.sqrt(torch.mean((true_values[0] - predicted[0]) ** 2)).item()
     mae = torch.mean(torch.abs(true_values[0] - predicted[0])).item()
-    assert rmse < 0.20 and mae < 0.20, (mpnn_type, rmse, mae)
+    assert rmse < GATES[mpnn_type][0] and mae < GATES[mpnn_type][1], (mpnn_type, rmse, mae)
