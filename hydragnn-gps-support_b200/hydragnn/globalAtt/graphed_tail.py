@@ -18,8 +18,14 @@ Opt out with HYDRAGNN_GRAPH_TAIL=0.
 """
 import contextlib
 import os
+import warnings
 
 import torch
+
+# make_graphed_callables captures its backward graphs on a side stream; autograd then notes, once per
+# process, that the parameters' AccumulateGrad nodes live on another stream.  Harmless here (the
+# replay is ordered after the producing stream), and noise in every training log.
+warnings.filterwarnings("ignore", message=".*AccumulateGrad node's stream does not match.*")
 
 ENABLED = os.environ.get("HYDRAGNN_GRAPH_TAIL", "1") != "0"
 CAPTURE_AFTER = 3          # occurrences of one (layer, piece, N) signature before it is captured
