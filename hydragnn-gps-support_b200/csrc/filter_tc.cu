@@ -497,6 +497,29 @@ k_wgrad_tn(const WgradArgs p) {
   cta_teardown(tmem, kCols);
 }
 
+// Sum of the per-CTA partials of k_wgrad_tn in CTA order (fixed, so the result is reproducible):
+// element i of [dw | db] = sum_p partial[p][i].  Consecutive threads read consecutive addresses.
+__global__ void __launch_bounds__(256)
+k_wgrad_reduce(float* __restrict__ dw, float* __restrict__ db, const float* __restrict__ dw_partial,
+               const float* __restrict__ db_partial, int P, int n_w, int n_b) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_w + n_b) return;
+  const bool is_w = i < n_w;
+  const float* src = is_w ? dw_partial + i : db_partial + (i - n_w);
+  const int64_t stride = is_w ? n_w : n_b;
+  float acc = 0.f;
+  int p = 0;
+  for (; p + 8 <= P; p += 8) {
+    float v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = __ldg(src + (int64_t)(p + q) * stride);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc += v[q];
+  }
+  for (; p < P; ++p) acc += __ldg(src + (int64_t)p * stride);
+  if (is_w) dw[i] = acc; else db[i - n_w] = acc;
+}
+
 }  // namespace tc
 }  // namespace hgk
 
@@ -598,4 +621,14 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
   if (!gauss) return launch(tc::k_wgrad_tn<128, false, 50, 0>, 128);
   if (R == 8) return launch(tc::k_wgrad_tn<64, true, 50, 8>, 64);
   return launch(tc::k_wgrad_tn<64, true, 50, 0>, 64);
+}
+
+extern "C" int hgk_wgrad_reduce(float* dw, float* db, const float* dw_partial, const float* db_partial,
+                                int64_t P, int32_t KB, int32_t F, void* stream) {
+  HGK_REQUIRE(P >= 0 && KB >= 1 && F >= 1, "wgrad_reduce: bad sizes");
+  HGK_REQUIRE(dw && db && (P == 0 || (dw_partial && db_partial)), "wgrad_reduce: NULL operand");
+  const int n_w = F * KB, n_b = F;
+  const unsigned blocks = (unsigned)ceil_div((int64_t)n_w + n_b, 256);
+  tc::k_wgrad_reduce<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw, db, dw_partial, db_partial, (int)P, n_w, n_b);
+  return check_launch("wgrad_reduce");
 }

@@ -69,7 +69,11 @@ def _wgrad_raw(a, scale_d, cutoff, b=None, gauss=None):
         nbytes = E * 4 * (F + KB)
     _hgk.call("hgk_wgrad_tn", _hgk.ptr(dw), _hgk.ptr(db), _hgk.ptr(a), a.stride(0), _hgk.ptr(scale_d), float(cutoff), *args,
               E, F, cost=(nbytes, 2 * E * F * KB))
-    return dw.sum(0), db.sum(0)        # fixed-order reduction of the per-CTA partials
+    gw = torch.empty((F, KB), dtype=torch.float32, device=a.device)
+    gb = torch.empty(F, dtype=torch.float32, device=a.device)
+    _hgk.call("hgk_wgrad_reduce", _hgk.ptr(gw), _hgk.ptr(gb), _hgk.ptr(dw), _hgk.ptr(db), P, KB, F,
+              cost=(4 * P * F * (KB + 1), 0))        # fixed-order sum of the per-CTA partials, one launch
+    return gw, gb
 
 
 class SchnetFilter(torch.autograd.Function):

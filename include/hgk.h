@@ -177,6 +177,11 @@ int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a,
                  int32_t KB, const float* d, const float* raw, int64_t ldr,
                  int32_t R, const float* offset, int32_t G, float coeff,
                  int64_t E, int32_t F, void* stream);
+/* dw[128, KB] and db[128] = the P partials of hgk_wgrad_tn summed in CTA order
+ * (one launch for both; fixed order, so reproducible). */
+int hgk_wgrad_reduce(float* dw, float* db, const float* dw_partial,
+                     const float* db_partial, int64_t P, int32_t KB, int32_t F,
+                     void* stream);
 
 /* ------------------------------------------------------------------------- *
  * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
