@@ -527,3 +527,58 @@ extern "C" int hgk_edge_gather_add(float* out, int64_t ldo, const float* P, int6
   }
   return check_launch("edge_gather_add");
 }
+
+// --------------------------------------------------------------------------- column sums ---
+// out[c] = sum_n x[n, c] (the bias gradient of a node-row Linear).  torch's column reduction runs
+// 128-block grids for 20 us on a [8192, 128] matrix; here S row slabs x C/32 column groups of CTAs
+// write partials (warp = rows, lane = column: 128-byte coalesced reads; the eight warps of a CTA are
+// combined in warp order), and a second tiny kernel adds the S partials in slab order: fixed
+// summation order, reproducible.
+namespace hgk {
+__global__ void __launch_bounds__(256)
+k_colsum_partial(float* __restrict__ partial, const float* __restrict__ x, int64_t ldx, int64_t N, int C,
+                 int64_t rows_per_slab) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int64_t beg = (int64_t)blockIdx.y * rows_per_slab;
+  const int64_t end = beg + rows_per_slab < N ? beg + rows_per_slab : N;
+  float acc = 0.f;
+  if (c < C)
+    for (int64_t n = beg + warp; n < end; n += 8) acc += __ldg(x + n * ldx + c);
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < C) {
+    float t = red[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) t += red[w][lane];
+    partial[(int64_t)blockIdx.y * C + c] = t;
+  }
+}
+__global__ void __launch_bounds__(256)
+k_colsum_final(float* __restrict__ out, const float* __restrict__ partial, int S, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float t = 0.f;
+  for (int s = 0; s < S; ++s) t += partial[(int64_t)s * C + c];
+  out[c] = t;
+}
+}  // namespace hgk
+
+extern "C" int64_t hgk_colsum_slabs(int64_t N) {
+  if (N <= 0) return 1;
+  return imin64(ceil_div(N, 128), 64);
+}
+
+extern "C" int hgk_colsum(float* out, float* partial, const float* x, int64_t ldx, int64_t N, int32_t C,
+                          void* stream) {
+  HGK_REQUIRE(N >= 0 && C >= 1 && ldx >= C, "colsum: bad sizes N=%lld C=%d", (long long)N, C);
+  HGK_REQUIRE(out && partial && (N == 0 || x), "colsum: NULL operand");
+  const int S = (int)hgk_colsum_slabs(N);
+  const int64_t rows = N > 0 ? ceil_div(N, S) : 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((unsigned)ceil_div(C, 32), (unsigned)S);
+  k_colsum_partial<<<grid, 256, 0, st>>>(partial, x, ldx, N, C, rows);
+  k_colsum_final<<<(unsigned)ceil_div(C, 256), 256, 0, st>>>(out, partial, S, C);
+  return check_launch("colsum");
+}

@@ -56,6 +56,8 @@ _SIGNATURES = {
         [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_i32,
          _c_ptr, _c_i32, _c_f32, _c_i64, _c_i32, _c_ptr],
     ),
+    "hgk_colsum_slabs": (_c_i64, [_c_i64]),
+    "hgk_colsum": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
     "hgk_wgrad_reduce": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_i32, _c_ptr]),
     "hgk_pna_aggregate_fwd": (
         _c_i32,
@@ -129,7 +131,7 @@ def check(status, what):
 # CUDA kernels enqueued by one call of each entry point (for bench.py's gpu_launches count)
 KERNELS_PER_CALL = {
     "hgk_csr_build": 4, "hgk_csr_build_static": 4, "hgk_contract_node": 1, "hgk_contract_edge_w": 1, "hgk_contract_edge_u": 1,
-    "hgk_edge_gather_add": 1, "hgk_schnet_filter_fwd": 1, "hgk_schnet_filter_bwd": 1, "hgk_wgrad_tn": 1, "hgk_wgrad_reduce": 1, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
+    "hgk_edge_gather_add": 1, "hgk_schnet_filter_fwd": 1, "hgk_schnet_filter_bwd": 1, "hgk_wgrad_tn": 1, "hgk_wgrad_reduce": 1, "hgk_colsum": 2, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
     "hgk_radius_graph_count": 8, "hgk_radius_graph_fill": 1, "hgk_attn_varlen_fwd": 1,
     "hgk_attn_varlen_bwd": 3,
 }

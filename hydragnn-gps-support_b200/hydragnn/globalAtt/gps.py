@@ -18,10 +18,10 @@ from typing import Any, Dict, Optional
 import torch
 import torch.nn.functional as F
 from torch import Tensor
-from torch.nn import Dropout, Linear, Sequential
+from torch.nn import Dropout, Sequential
 
-from ..nn import activation_resolver, normalization_resolver
-from ..ops import attn_varlen
+from ..nn import Linear, activation_resolver, normalization_resolver
+from ..ops import attn_varlen, linear_rows
 from . import graphed_tail
 
 
@@ -83,11 +83,11 @@ class GPSConv(torch.nn.Module):
             h1 = h1 + x
             if self.norm1 is not None:
                 h1 = self.norm1(h1)
-        qkv = F.linear(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
+        qkv = linear_rows(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
         return h1, qkv
 
     def _tail_post(self, x: Tensor, h1: Optional[Tensor], o: Tensor) -> Tensor:
-        h = F.linear(o, self.attn.out_proj.weight, self.attn.out_proj.bias)
+        h = linear_rows(o, self.attn.out_proj.weight, self.attn.out_proj.bias)
         h = F.dropout(h, p=self.dropout, training=self.training)
         h = h + x
         if self.norm2 is not None:

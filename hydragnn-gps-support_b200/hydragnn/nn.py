@@ -48,6 +48,16 @@ class Sequential(nn.Module):
         return out
 
 
+class Linear(nn.Linear):
+    """torch.nn.Linear (same parameters and state-dict keys); inside a CUDA-graph capture the bias
+    gradient comes from hgk_colsum (ops/linear.py)."""
+
+    def forward(self, x):
+        from .ops import linear_rows
+
+        return linear_rows(x, self.weight, self.bias)
+
+
 class BatchNorm(nn.Module):
     """PyG BatchNorm: nn.BatchNorm1d under the child name `module`."""
 

@@ -12,3 +12,4 @@ from .contract import (
 from .radius import radius_graph, radius_graph_pbc, MODE_ASE, MODE_CLUSTER
 from .attention import attn_varlen
 from .pna import pna_aggregate
+from .linear import linear_rows, colsum

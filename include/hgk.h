@@ -136,6 +136,14 @@ int hgk_edge_gather_add(float* out, int64_t ldo, const float* P, int64_t ldp,
                         const int32_t* pi, const float* Q, int64_t ldq,
                         const int32_t* qi, int64_t E, int32_t F, void* stream);
 
+/* Column sums out[c] = sum_n x[n, c] of a row-major [N, C] matrix (row stride
+ * ldx): the bias gradient of a node-row Linear (reference: autograd of
+ * nn.Linear in GPSConv, hydragnn/globalAtt/gps.py:58-83).  `partial` is caller
+ * scratch of hgk_colsum_slabs(N) * C floats; fixed summation order. */
+int64_t hgk_colsum_slabs(int64_t N);
+int hgk_colsum(float* out, float* partial, const float* x, int64_t ldx,
+               int64_t N, int32_t C, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * SchNet filter-generating network, fused (reference: hydragnn/models/
  * SCFStack.py:259-272 = PyG GaussianSmearing -> cat with the edge attribute ->

@@ -491,3 +491,19 @@ def test_attn_varlen_double_backward(ops):
         res.append((e.detach(), gq.detach(), loss.detach(), q.grad, k.grad, v.grad))
     for a, b in zip(*res):
         torch.testing.assert_close(a, b, rtol=2e-4, atol=2e-4)
+
+
+@pytest.mark.parametrize("n,c,strided", [(8192, 128, False), (5000, 384, False), (1, 7, False), (333, 256, True),
+                                         (0, 16, False)])
+def test_colsum(ops, n, c, strided):
+    """hgk_colsum (bias gradient of a node-row Linear): fp64 reference, run-to-run identical bits."""
+    from hydragnn.ops import colsum
+
+    gen = torch.Generator().manual_seed(n + c)
+    full = torch.randn(n, c * (2 if strided else 1), generator=gen).to(DEV)
+    x = full[:, :c]
+    got = colsum(x)
+    want = x.double().sum(0)
+    assert got.shape == (c,)
+    torch.testing.assert_close(got.double(), want, rtol=1e-5, atol=1e-4 * max(1.0, n ** 0.5))
+    assert torch.equal(got, colsum(x))
