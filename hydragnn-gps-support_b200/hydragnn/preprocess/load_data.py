@@ -121,6 +121,41 @@ def _laplacian_pe(edge_index, num_nodes, k):
     return pe
 
 
+def _laplacian_pe_batched(samples, k, device):
+    """`_laplacian_pe` for every sample, on `device`, one batched eigendecomposition per graph size
+    (datasets of fixed-size structures: one call for the whole split instead of one dense fp64 eigh
+    per sample on the host; chunked to bound memory)."""
+    by_size = {}
+    for i, d in enumerate(samples):
+        by_size.setdefault(d.num_nodes, []).append(i)
+    for n, idxs in by_size.items():
+        if k == 0 or n < 2:
+            for i in idxs:
+                samples[i].pe = torch.zeros(n, k)
+            continue
+        chunk = max(1, min(len(idxs), (1 << 27) // (n * n)))          # <= 1 GiB of fp64 matrices
+        for c0 in range(0, len(idxs), chunk):
+            part = idxs[c0:c0 + chunk]
+            A = torch.zeros((len(part), n, n), dtype=torch.float64, device=device)
+            for b, i in enumerate(part):
+                ei = samples[i].edge_index.to(device)
+                A[b, ei[0], ei[1]] = 1.0
+            A = torch.maximum(A, A.transpose(1, 2))
+            deg = A.sum(2).clamp(min=1e-12)
+            L = torch.eye(n, dtype=torch.float64, device=device) - A / torch.sqrt(deg[:, :, None] * deg[:, None, :])
+            vecs = torch.linalg.eigh(L).eigenvectors[:, :, 1:k + 1]                  # [b, n, <=k]
+            # sign: first entry with |v| > 1e-9 positive
+            big = vecs.abs() > 1e-9
+            first = torch.argmax(big.to(torch.int8), dim=1, keepdim=True)           # [b, 1, k']
+            lead = torch.gather(vecs, 1, first)
+            sign = torch.where((lead < 0) & big.any(dim=1, keepdim=True), -1.0, 1.0)
+            vecs = (vecs * sign).to(torch.float32).cpu()
+            for b, i in enumerate(part):
+                pe = torch.zeros(n, k)
+                pe[:, :vecs.size(2)] = vecs[b]
+                samples[i].pe = pe
+
+
 def build_graphs(samples, arch, device):
     """Edges, edge lengths (normalised by the global maximum) and encodings for a list of samples,
     with ONE batched radius-graph call on `device` (reference: one call per sample on the CPU)."""
@@ -165,10 +200,12 @@ def finish_samples(samples, config, max_edge_length):
     pe_dim = int(arch.get("pe_dim") or 0)
     node_dims = config["Dataset"]["node_features"]["dim"]
     graph_dims = config["Dataset"]["graph_features"]["dim"]
+    if pe_dim > 0 and samples:
+        device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        _laplacian_pe_batched(samples, pe_dim, device)
     for d in samples:
         d.edge_attr = d.edge_attr / max_edge_length
         if pe_dim > 0:
-            d.pe = _laplacian_pe(d.edge_index, d.num_nodes, pe_dim)
             d.rel_pe = (d.pe[d.edge_index[0]] - d.pe[d.edge_index[1]]).abs()
         update_predicted_values(var["type"], var["output_index"], graph_dims, node_dims, d)
         d.x = d.x[:, list(var["input_node_features"])]

@@ -17,3 +17,19 @@ def test_product_stack_matches_reference_on_cpu(name):
     with cpu_kernels():
         res = pu.run_golden_case(name, device="cpu")
     pu.assert_case_close(res)
+
+
+def test_batched_laplacian_pe_matches_per_sample():
+    """preprocess.load_data: one batched eigendecomposition per graph size == the per-sample routine."""
+    import types
+
+    from hydragnn.preprocess import load_data as ld
+
+    gen = torch.Generator().manual_seed(0)
+    samples = []
+    for n in (5, 5, 7, 1, 5, 7, 12):
+        ei = torch.randint(0, n, (2, 3 * n), generator=gen) if n > 1 else torch.zeros(2, 0, dtype=torch.long)
+        samples.append(types.SimpleNamespace(num_nodes=n, edge_index=ei))
+    ld._laplacian_pe_batched(samples, 3, torch.device("cpu"))
+    for d in samples:
+        torch.testing.assert_close(d.pe, ld._laplacian_pe(d.edge_index, d.num_nodes, 3), rtol=1e-5, atol=1e-6)
