@@ -121,5 +121,8 @@ def run(layer, which, x, *rest):
         ready = sum(1 for e in cache.values() if e["graphed"] is not None)
         if entry["seen"] < CAPTURE_AFTER or ready >= MAX_GRAPHS_PER_LAYER or not all(a.requires_grad for a in args):
             return _eager(layer, which, x, *rest)
+        if not all(p.requires_grad for p in _Piece(layer, which, has_local).parameters()):
+            entry["seen"] = -(1 << 30)                 # frozen parameters (freeze_conv): never capture this one
+            return _eager(layer, which, x, *rest)
         entry["graphed"] = _capture(layer, which, has_local, args)
     return entry["graphed"](*args)
