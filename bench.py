@@ -37,7 +37,11 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="schnet_gps_fesi1024")
+    ap.add_argument("--workload", default="schnet_gps_fesi1024",
+                    help="one of hydragnn/utils/synthetic.py:WORKLOADS, or 'all': the headline config 5 "
+                         "plus a `workloads` array with BASELINE configs 2-4 (N = 1 only; the default when "
+                         "no --workload is given on one GPU)")
+    ap.add_argument("--single", action="store_true", help="default workload only (no `workloads` array)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gps-segments", default="batch", choices=["batch", "graph"],
                     help="batch = the reference's whole-mini-batch attention (SURVEY F3); graph = per-graph varlen")
@@ -202,11 +206,14 @@ def kernel_table(summary, steps, peaks):
                "bound": kind, "gbs": s["bytes"] / sec / 1e9, "tflops": s["flops"] / sec / 1e12,
                "gbs_compulsory": s["dram_bytes"] / sec / 1e9}
         if kind == "hbm":
-            row.update(achieved=row["gbs"], peak=peaks["hbm_gbs"], unit="GB/s")
+            # `achieved` for an HBM-bound entry point = COMPULSORY bytes / time (a gathered node table
+            # counted once: it crosses HBM once and is re-read from L2).  The per-edge figure of SURVEY
+            # 8(d), which counts a gathered row once per edge, is L2 traffic and is kept as `gbs_l2`.
+            row.update(achieved=row["gbs_compulsory"], peak=peaks["hbm_gbs"], unit="GB/s", gbs_l2=row["gbs"])
         else:
             row.update(achieved=row["tflops"], peak=peaks["tflops"], unit="TFLOP/s")
         row["frac"] = row["achieved"] / row["peak"]
-        row["bytes_per_launch"] = s["bytes"] / s["calls"]
+        row["bytes_per_launch"] = (s["dram_bytes"] if kind == "hbm" else s["bytes"]) / s["calls"]
         rows.append(row)
     rows.sort(key=lambda r: -r["ms_per_step"])
     return rows
@@ -215,11 +222,7 @@ def kernel_table(summary, steps, peaks):
 def run_b200(args):
     import __graft_entry__
     from hydragnn import _hgk
-    from hydragnn.graph import Data
-    from hydragnn.models import create_model
-    from hydragnn.train import train_step
-    from hydragnn.utils import synthetic as syn
-    from hydragnn.utils.distributed import get_distributed_model, setup_ddp
+    from hydragnn.utils.distributed import setup_ddp
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
@@ -236,15 +239,50 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
     _hgk.lib()
+    ctx = dict(world=world, rank=rank, device=device)
 
-    spec = syn.WORKLOADS[args.workload]
-    per_gpu = args.graphs_per_gpu or spec["graphs_per_gpu"]
-    if args.global_batch:
+    HEADLINE = "schnet_gps_fesi1024"
+    everything = args.workload == "all" or (args.workload == HEADLINE and world == 1 and not args.single
+                                            and not args.global_batch and not args.graphs_per_gpu)
+    first = HEADLINE if args.workload == "all" else args.workload
+    result = measure(args, first, ctx, headline=True)
+    if everything and world == 1:
+        # BASELINE configs[1..3] on the same GPU, same protocol (device-resident `value`, `e2e` with
+        # the H2D copy and the loss read-back), without the CPU leg: one JSON line carries all four
+        result["workloads"] = [measure(args, w, ctx, headline=False)
+                               for w in ("schnet_qm9", "egnn_gps_zinc", "painn_oc20_forces")]
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def set_dropout(model, p):
+    for m in model.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = p
+        elif hasattr(m, "attn") and isinstance(getattr(m, "dropout", None), float):
+            m.dropout = p
+
+
+def measure(args, workload, ctx, headline):
+    from hydragnn import _hgk
+    from hydragnn.graph import Data
+    from hydragnn.models import create_model
+    from hydragnn.train import train_step
+    from hydragnn.utils import synthetic as syn
+    from hydragnn.utils.distributed import get_distributed_model
+
+    world, rank, device = ctx["world"], ctx["rank"], ctx["device"]
+    spec = syn.WORKLOADS[workload]
+    per_gpu = (args.graphs_per_gpu if headline else 0) or spec["graphs_per_gpu"]
+    if args.global_batch and headline:
         if args.global_batch % world:
             raise SystemExit(f"--global-batch {args.global_batch} is not divisible by {world} ranks")
         per_gpu = args.global_batch // world
-    graphs = syn.sample_graphs(args.workload, per_gpu, rank=rank)
-    host = build_batch_gpu(args.workload, graphs, device)
+    graphs = syn.sample_graphs(workload, per_gpu, rank=rank)
+    host = build_batch_gpu(workload, graphs, device)
     pinned = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in host.items()}
     forces = spec["forces"]
 
@@ -252,7 +290,8 @@ def run_b200(args):
     # mini-batch: real for datasets of fixed-size structures (config 5), but this bench repeats ONE
     # batch, which would make every workload look fixed-size -- so it is switched off for the others
     from hydragnn.globalAtt import graphed_tail
-    graphed_tail.ENABLED = graphed_tail.ENABLED and args.workload == "schnet_gps_fesi1024"
+    graphed_default = ctx.setdefault("graphed_default", graphed_tail.ENABLED)
+    graphed_tail.ENABLED = graphed_default and workload == "schnet_gps_fesi1024"
     model = create_model(**spec["arch"])
     model = get_distributed_model(model)
     model.module.gps_segments = args.gps_segments      # "batch" = the reference's semantics
@@ -276,6 +315,20 @@ def run_b200(args):
         data = to_data(pinned, device, Data, non_blocking=True)
         loss = train_step(model, optimizer, data, compute_grad_energy=forces)[0]
         return float(loss)          # device -> host read of the step's result
+
+    # ---- parity of the benchmarked step itself: the first training step's loss with the initial
+    # weights, dropout switched off so that the step is deterministic (train mode: BatchNorm batch
+    # statistics), against the CPU oracle on the same batch and weights (computed in the cpu_baseline leg)
+    parity = None
+    if headline and rank == 0 and world == 1 and not args.no_cpu_baseline:
+        init_state = {k: v.detach().cpu().clone() for k, v in model.module.state_dict().items()}
+        set_dropout(model.module, 0.0)
+        from hydragnn.globalAtt import graphed_tail as gt
+        with gt.eager():
+            gpu_loss = float(_loss_only(model.module, fresh(resident), forces))
+        set_dropout(model.module, 0.25)
+        model.module.load_state_dict({k: v.to(device) for k, v in init_state.items()})   # BatchNorm buffers back
+        parity = {"gpu_first_step_loss": gpu_loss, "state": init_state}
 
     for _ in range(args.warmup):
         step_resident()
@@ -347,7 +400,7 @@ def run_b200(args):
         "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong" if args.global_batch else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "graphs_per_gpu": per_gpu, "global_batch": graphs_total,
+        "config": {"workload": workload, "graphs_per_gpu": per_gpu, "global_batch": graphs_total,
                    "nodes_per_gpu": int(host["pos"].size(0)),
                    "edges_per_gpu": int(host["edge_index"].size(1)) if "edge_index" in host else None,
                    "gps_segments": args.gps_segments if spec["arch"]["global_attn_engine"] else None,
@@ -366,7 +419,7 @@ def run_b200(args):
         measured = {}
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
-                measured = json.load(fh).get(args.workload, {}).get(top["entry"], {})
+                measured = json.load(fh).get(workload, {}).get(top["entry"], {})
         except Exception:
             pass
         result["roofline"] = {"kernel": top["entry"], "bound": top["bound"], "achieved": top["achieved"],
@@ -376,22 +429,39 @@ def run_b200(args):
         if top["bound"] == "tensor":
             # fp32 parity forces 3xTF32: 3 MMAs per algorithmic product on a pipe that runs tf32 at half
             # the bf16 rate the peak was measured with -> the reachable ceiling is peak / 6
-            result["roofline"]["effective_peak"] = top["peak"] / 6.0
-            result["roofline"]["frac_of_effective_peak"] = top["achieved"] / (top["peak"] / 6.0)
+            result["roofline"]["tf32x3_ceiling"] = top["peak"] / 6.0
+            result["roofline"]["frac_of_tf32x3_ceiling"] = top["achieved"] / (top["peak"] / 6.0)
             result["roofline"]["tensor_pipe_active_pct"] = measured.get("tensor_pipe_active_pct")
         result["kernels"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()
-                              if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs", "gbs_compulsory",
+                              if k in ("entry", "calls_per_step", "ms_per_step", "bound", "gbs_l2", "gbs_compulsory",
                                        "tflops", "frac")}
                              for r in table]
         result["hgk_ms_per_step"] = sum(r["ms_per_step"] for r in table)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if headline and rank == 0 and world == 1 and not args.no_cpu_baseline:
         state = {k: v.detach().cpu() for k, v in model.module.state_dict().items()}
         result["cpu_baseline"] = cpu_baseline(args, spec, host, state, args.cpu_seconds, per_gpu)
-    if rank == 0:
-        print(json.dumps(result))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        if parity is not None:
+            cpu_loss = oracle_first_step_loss(spec, host, parity["state"])
+            result["parity"] = {"gpu_first_step_loss": parity["gpu_first_step_loss"], "cpu_first_step_loss": cpu_loss,
+                                "parity_rel_err": abs(parity["gpu_first_step_loss"] - cpu_loss) / max(abs(cpu_loss), 1e-30),
+                                "mode": "train mode (BatchNorm batch statistics), dropout = 0, initial weights, "
+                                        "the benchmarked batch; tolerance of tests/: rel 1e-5"}
+    if not headline:
+        for k in ("steps", "warmup", "higher_is_better", "vs_baseline", "dtype", "data", "clocks", "n_gpus", "scaling"):
+            result.pop(k, None)
+    del model, optimizer, resident, flush
+    torch.cuda.empty_cache()
+    return result
+
+
+def _loss_only(model, data, forces):
+    """Forward + loss of one batch (no backward, no optimizer): the parity probe of `measure`."""
+    if forces:
+        data.pos.requires_grad_(True)
+        return model.energy_force_loss(model(data), data)[0].detach()
+    with torch.no_grad():
+        pred = model(data)
+        return model.loss(pred, data.y, [torch.arange(data.y.shape[0], device=data.y.device)])[0]
 
 
 # -------------------------------------------------------------- the CPU (oracle) arm ---
@@ -426,6 +496,25 @@ def oracle_step_fn(spec, host, state=None):
     return step
 
 
+def oracle_first_step_loss(spec, host, state):
+    """Loss of the CPU oracle on `host` with weights `state`, train mode, dropout = 0 (no update)."""
+    from oracle import hydragnn_ref as ora
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden as mg
+
+    torch.set_num_threads(os.cpu_count())
+    model = ora.create_model(**spec["arch"])
+    model.load_state_dict(state, strict=True)
+    set_dropout(model, 0.0)
+    model.train()
+    data = mg.Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in host.items()})
+    if spec["forces"]:
+        data.pos.requires_grad_(True)
+        return float(model.energy_force_loss(model(data), data)[0].detach())
+    with torch.no_grad():
+        return float(model.loss(model(data), data.y, [torch.arange(data.y.shape[0])])[0])
+
+
 def cpu_baseline(args, spec, host, state, budget_s, graphs):
     step = oracle_step_fn(spec, host, state)
     t0 = time.perf_counter()
@@ -449,11 +538,11 @@ def run_reference(args):
         return
     from hydragnn.utils import synthetic as syn
 
+    if args.workload == "all":
+        args.workload = "schnet_gps_fesi1024"
     spec = syn.WORKLOADS[args.workload]
     per_gpu = args.graphs_per_gpu or spec["graphs_per_gpu"]
-    sample_graphs = per_gpu
-    if args.workload == "schnet_gps_fesi1024" and not args.graphs_per_gpu:
-        sample_graphs = 2          # bounded sample: 2 of the 8 crystals per step (whole-batch attention)
+    sample_graphs = per_gpu        # the full mini-batch of the B200 arm's `config` (same whole-batch attention)
     graphs = syn.sample_graphs(args.workload, sample_graphs, rank=0)
     host = build_batch_cpu(args.workload, graphs)
     step = oracle_step_fn(spec, host)
@@ -470,7 +559,12 @@ def run_reference(args):
         "impl": "reference", "metric": "train graphs/sec", "value": value, "unit": "graphs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "graphs_per_step": sample_graphs, "parallelism": "cpu"},
+        # the B200 arm's `config` (same workload, same mini-batch, whole-batch attention); one CPU process
+        # stands for one rank -- the reference arm does not emulate multi-rank CPU training
+        "config": {"workload": args.workload, "graphs_per_gpu": per_gpu, "global_batch": sample_graphs,
+                   "nodes_per_gpu": int(host["pos"].size(0)), "edges_per_gpu": int(host["edge_index"].size(1)),
+                   "gps_segments": "batch" if spec["arch"]["global_attn_engine"] else None,
+                   "parallelism": "cpu", "optimizer": "AdamW", "tf32": False},
         "cpu_baseline": {"value": value, "unit": "graphs/s", "cores": os.cpu_count(), "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": "graphs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

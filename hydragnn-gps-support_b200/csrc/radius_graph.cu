@@ -277,14 +277,17 @@ k_rg_count(const ScanArgs p, int32_t* __restrict__ deg_raw, int32_t* __restrict_
 
 __global__ void __launch_bounds__(256)
 k_rg_fill(const ScanArgs p, const int32_t* __restrict__ rowptr_raw,
-          const int32_t* __restrict__ rowptr, Cand* __restrict__ cand,
+          const int32_t* __restrict__ rowptr, Cand* __restrict__ cand, int64_t cand_cap,
           int32_t* __restrict__ src, int32_t* __restrict__ dst,
           int32_t* __restrict__ shift_int, double* __restrict__ dist) {
   const int lane = threadIdx.x & 31;
   const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (j >= p.N) return;
   const int32_t rbeg = rowptr_raw[j];
-  const int32_t rlen = rowptr_raw[j + 1] - rbeg;
+  int32_t rlen = rowptr_raw[j + 1] - rbeg;
+  // never write past the caller's candidate buffer (cand_bytes / 24 records): a row that does not
+  // fit is truncated instead -- its edge count then falls short of rowptr, which the caller sees
+  if ((int64_t)rbeg + rlen > cand_cap) rlen = (int32_t)max((int64_t)0, cand_cap - rbeg);
   int32_t written = 0;
   scan_candidates(p, j, lane, [&](bool match, const Cand& c) {
     const unsigned b = __ballot_sync(0xffffffffu, match);
@@ -417,8 +420,8 @@ extern "C" int hgk_radius_graph_fill(const float* pos, const int32_t* gptr,
   RgWorkspace w;
   rg_carve(N, B, (char*)workspace, &w);
   const ScanArgs s = make_scan(pos, w, N, r, max_nbr, loop, mode);
-  (void)cand_bytes;
   k_rg_fill<<<(unsigned)ceil_div(N * 32, 256), 256, 0, st>>>(s, rowptr_raw, rowptr, (Cand*)cand,
+                                                            cand_bytes / (int64_t)sizeof(Cand),
                                                             src, dst, shift_int, dist);
   return check_launch("radius_graph_fill");
 }

@@ -45,7 +45,15 @@ class GPSConv(torch.nn.Module):
         if attn_type != "multihead":
             # the reference's only other option is PyG's PerformerAttention (gps.py:62-67)
             raise ValueError(f"{attn_type} is not supported")
-        self.attn = torch.nn.MultiheadAttention(channels, heads, batch_first=True, **(attn_kwargs or {}))
+        attn_kwargs = dict(attn_kwargs or {})
+        # the varlen kernel path reads in_proj / out_proj only: options of nn.MultiheadAttention that
+        # would change the result are refused rather than silently ignored
+        unsupported = {k: v for k, v in attn_kwargs.items()
+                       if (k == "dropout" and v) or (k in ("add_bias_kv", "add_zero_attn") and v)
+                       or (k in ("kdim", "vdim") and v not in (None, channels)) or (k == "bias" and not v)}
+        if unsupported:
+            raise ValueError(f"attn_kwargs {sorted(unsupported)} are not supported by the varlen attention path")
+        self.attn = torch.nn.MultiheadAttention(channels, heads, batch_first=True, **attn_kwargs)
         self.mlp = Sequential(
             Linear(channels, channels * 2),
             activation_resolver(act, **(act_kwargs or {})),
@@ -66,6 +74,7 @@ class GPSConv(torch.nn.Module):
         if graph_batch is None:
             cu_seqlens = torch.zeros(2, dtype=torch.int32, device=x.device)
             cu_seqlens[1] = n                              # filled on the device: no blocking host copy
+            cu_seqlens._hgk_sum_sq = n * n                 # known on the host: no sync in the flop accounting
             return cu_seqlens
         counts = torch.bincount(graph_batch)
         cu_seqlens = torch.zeros(counts.numel() + 1, dtype=torch.int32, device=x.device)

@@ -46,8 +46,11 @@ class RadiusInteractionGraph(nn.Module):
 
     def forward(self, pos, batch):
         # cached on the tensor object itself (not on its address, which the allocator reuses)
+        # ... and keyed on the tensor's version counter: an in-place update of the positions (an MD or
+        # relaxation loop, noise augmentation) rebuilds the graph, as the reference does every call
+        key = (self.cutoff, self.max_num_neighbors, pos._version)
         cached = getattr(pos, "_hgk_rgraph", None)
-        if cached is None or cached[0] != (self.cutoff, self.max_num_neighbors):
+        if cached is None or cached[0] != key:
             ptr = getattr(batch, "_hgk_ptr", None)
             if ptr is None:
                 counts = torch.bincount(batch)
@@ -57,7 +60,7 @@ class RadiusInteractionGraph(nn.Module):
             edge_index = g["edge_index"]
             topo = topo_of(edge_index, pos.size(0), sorted_side=1)
             topo.set_csr(1, g["rowptr"], None)
-            cached = ((self.cutoff, self.max_num_neighbors), edge_index)
+            cached = (key, edge_index)
             pos._hgk_rgraph = cached
         edge_index = cached[1]
         vec, length = get_edge_vectors_and_lengths(pos, edge_index, None)

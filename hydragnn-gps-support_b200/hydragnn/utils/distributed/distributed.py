@@ -105,7 +105,14 @@ class GradientAverager:
     the parameters' `.grad` are re-pointed at views of that slice, and the slice is all-reduced
     asynchronously on a side stream while backward continues.  `finish()` waits, divides by the
     world size, and leaves `.grad` = averaged views for the optimizer.  With one rank nothing is
-    packed at all."""
+    packed at all.
+
+    Collectives are matched across ranks by issue order, so the order must not depend on which
+    parameters a rank's local batch happened to reach (a multibranch model runs only the heads
+    present in its batch): chunk k is launched only after chunks 0..k-1, and `finish()` flushes
+    what is left in index order.  A chunk with an unused parameter therefore waits for `finish()`
+    on that rank and holds the later chunks back with it -- same sequence of all-reduces on
+    every rank, whatever each one's autograd graph looked like."""
 
     def __init__(self, params, world_size=None, num_chunks=4, process_group=None):
         self.params = [p for p in params if p.requires_grad]
@@ -130,6 +137,7 @@ class GradientAverager:
             self._close_chunk(start, off, members)
         self._pending = [len(c["members"]) for c in self.chunks]
         self._works = []
+        self._next = 0              # chunks [0, _next) have been launched this step
         self.stream = torch.cuda.Stream(device=dev) if (dev.type == "cuda" and self.enabled) else None
         for p in self.params:
             p.grad = None
@@ -154,6 +162,7 @@ class GradientAverager:
             p.grad = None
         self._pending = [len(c["members"]) for c in self.chunks]
         self._works = []
+        self._next = 0
 
     def _launch(self, idx):
         chunk = self.chunks[idx]
@@ -173,18 +182,20 @@ class GradientAverager:
     def _on_grad_ready(self, p):
         idx = self._chunk_of[p]
         self._pending[idx] -= 1
-        if self._pending[idx] == 0:
-            self._launch(idx)
+        # rank-independent order: only the chunk at the cursor may go, then any completed ones behind it
+        while self._next < len(self.chunks) and self._pending[self._next] == 0:
+            self._launch(self._next)
+            self._next += 1
 
     def finish(self):
         """Wait for the chunk all-reduces, launch any chunk backward never completed (unused
         parameters), scale by 1/world_size.  Call after backward, before optimizer.step()."""
         if not self.enabled:
             return
-        for idx, left in enumerate(self._pending):
-            if left > 0:
-                self._launch(idx)
-                self._pending[idx] = 0
+        while self._next < len(self.chunks):
+            self._launch(self._next)
+            self._pending[self._next] = 0
+            self._next += 1
         for w in self._works:
             w.wait()
         if self.stream is not None:

@@ -248,7 +248,10 @@ int hgk_pna_aggregate_bwd(float* gh, float* gm, const float* gout, const float* 
  *                                  = d2 promoted), E = rowptr[N]
  * workspace (same buffer for 1 and 3, contents must survive in between):
  *   hgk_radius_graph_workspace_bytes(N, B) + for fill 24*E_raw bytes more,
- *   passed separately as `cand` (E_raw = rowptr_raw[N]).
+ *   passed separately as `cand` (E_raw = rowptr_raw[N]).  E_raw lives on the
+ *   device, so `cand_bytes` is enforced there: no candidate record is written
+ *   at or beyond cand + cand_bytes; a destination whose candidates do not fit
+ *   is truncated (its outputs are then incomplete) instead of overrunning.
  * ------------------------------------------------------------------------- */
 enum { HGK_RG_ASE = 0, HGK_RG_CLUSTER = 1 };
 int64_t hgk_radius_graph_workspace_bytes(int64_t N, int64_t B);

@@ -23,6 +23,12 @@ from torch import nn
 from . import pyg_lite as pyg
 
 
+def _fdtype():
+    """The reference writes `.float()` (Base.py:234,599-615).  Under the default dtype (fp32) this is
+    the same cast; tests build an fp64 "truth" run of this oracle by switching the default dtype."""
+    return torch.get_default_dtype()
+
+
 # -- utils/model/operations.py:21-36 ------------------------------------------
 def get_edge_vectors_and_lengths(positions, edge_index, shifts, normalize=False, eps=1e-9):
     vec = positions[edge_index[1]] - positions[edge_index[0]] + shifts
@@ -216,7 +222,7 @@ class Base(nn.Module):
     def _gps_embed(self, data, conv_args):                                     # :229-243
         x = self.pos_emb(data.pe)
         if self.input_dim:
-            x = self.node_lin(torch.cat((self.node_emb(data.x.float()), x), 1))
+            x = self.node_lin(torch.cat((self.node_emb(data.x.to(_fdtype())), x), 1))
         if self.is_edge_model:
             e = self.rel_pos_emb(data.rel_pe)
             if self.use_edge_attr:
@@ -366,13 +372,13 @@ class Base(nn.Module):
     def energy_force_loss(self, pred, data):                                   # :582-636
         assert data.pos.requires_grad
         assert self.num_heads == 1 and self.head_type[0] == "node"
-        e_graph = pyg.scatter_add(pred[0], data.batch, dim=0).squeeze().float()
-        e_true = data.energy.squeeze().float()
+        e_graph = pyg.scatter_add(pred[0], data.batch, dim=0).squeeze().to(_fdtype())
+        e_true = data.energy.squeeze().to(_fdtype())
         w_e = self.loss_weights[0]
         e_loss = self.loss_function(e_graph, e_true)
-        f_true = data.forces.float()
+        f_true = data.forces.to(_fdtype())
         f_pred = -torch.autograd.grad(e_graph, data.pos, grad_outputs=torch.ones_like(e_graph),
-                                      retain_graph=e_graph.requires_grad, create_graph=True)[0].float()
+                                      retain_graph=e_graph.requires_grad, create_graph=True)[0].to(_fdtype())
         w_f = w_e * torch.mean(torch.abs(e_true)) / (torch.mean(torch.abs(f_true)) + 1e-8)
         tot = e_loss * w_e + self.loss_function(f_pred, f_true) * w_f
         self.last_forces_pred = f_pred          # kept for the parity tests

@@ -146,8 +146,8 @@ def pna_aggregate_bwd(gout, out, cmin, cmax, P, Q, R, src, dst, N, M=None):
 def attn_varlen_fwd(q, k, v, cu_seqlens, H, scale):
     N, HD = q.shape
     D = HD // H
-    o = torch.zeros((N, HD), dtype=torch.float32)
-    lse = torch.zeros((N, H), dtype=torch.float32)
+    o = torch.zeros((N, HD), dtype=q.dtype)        # fp32 restatement; fp64 inputs give the tests' truth
+    lse = torch.zeros((N, H), dtype=q.dtype)
     cu = [int(c) for c in cu_seqlens]
     for b, e in zip(cu[:-1], cu[1:]):
         for h in range(H):

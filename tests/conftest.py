@@ -18,8 +18,9 @@ def pytest_configure(config):
 def golden():
     import torch
 
-    path = os.path.join(ROOT, "tests", "golden", "reference_fixtures.pt")
-    return torch.load(path, weights_only=False)
+    import parity_util
+
+    return parity_util.golden()
 
 
 @pytest.fixture(scope="session")

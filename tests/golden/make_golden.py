@@ -207,6 +207,8 @@ def build(ref_or_oracle, kind, cfg):
     torch.manual_seed(0)
     kw = dict(loss_weights=cfg["task_weights"], freeze_conv=False, initial_bias=None,
               num_conv_layers=cfg["num_conv_layers"], num_nodes=cfg.get("num_nodes"))
+    if "dropout" in cfg:        # train-mode fixtures (make_golden_train.py): Base.__init__(dropout=...)
+        kw["dropout"] = cfg["dropout"]
     common = common_args(cfg["input_dim"], cfg["hidden_dim"], cfg["output_dim"], cfg["output_type"],
                          cfg["heads"], cfg.get("pe_dim", 0), cfg.get("engine"), cfg.get("nheads", 0),
                          cfg.get("equivariance", False))

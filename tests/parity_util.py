@@ -29,6 +29,9 @@ def golden():
     if _GOLDEN is None:
         _GOLDEN = torch.load(os.path.join(ROOT, "tests", "golden", "reference_fixtures.pt"),
                              weights_only=False)
+        # GPS models in train mode with dropout = 0 (tests/golden/make_golden_train.py)
+        _GOLDEN.update(torch.load(os.path.join(ROOT, "tests", "golden", "gps_train_fixtures.pt"),
+                                  weights_only=False))
     return _GOLDEN
 
 
@@ -43,6 +46,19 @@ def to_device(batch, device):
 
     fields = {k: (v.clone().to(device) if torch.is_tensor(v) else v) for k, v in batch.items()}
     return Data(**fields)
+
+
+def set_dropout(model, p):
+    """Set the GPS dropout probability after construction (create_model has no dropout argument,
+    as in the reference: hydragnn/models/create.py:85)."""
+    for m in model.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = p
+        elif hasattr(m, "attn") and hasattr(m, "dropout") and isinstance(m.dropout, float):
+            m.dropout = p
+    if hasattr(model, "global_attn_dropout"):
+        model.dropout = model.global_attn_dropout = p
+    return model
 
 
 def run_step(model, data, cfg, ref_out, device):
@@ -64,6 +80,8 @@ def run_step(model, data, cfg, ref_out, device):
     out["grads"] = {n: p.grad.detach().cpu() for n, p in model.named_parameters() if p.grad is not None}
     if cfg.get("forces"):
         out["pos_grad"] = data.pos.grad.detach().cpu()
+    out["buffers"] = {k: v.detach().cpu() for k, v in model.named_buffers()
+                      if k.endswith(("running_mean", "running_var"))}
     return out
 
 
@@ -84,7 +102,10 @@ def run_golden_case(name, device="cuda:0"):
     return {"name": name, "cfg": cfg, "out": out, "ref": fx["out"]}
 
 
-def assert_case_close(res):
+def assert_case_close(res, truth=None):
+    """Loss / predictions / BatchNorm buffers: fp32 rel 1e-5 against the reference's own output.
+    Parameter gradients and forces: with `truth` (oracle_truth_case) the fp64-anchored bound below,
+    otherwise rel 1e-4."""
     out, ref, cfg = res["out"], res["ref"], res["cfg"]
     torch.testing.assert_close(out["loss"], ref["loss"], **TOL_VALUE)
     k = 0
@@ -92,7 +113,101 @@ def assert_case_close(res):
         torch.testing.assert_close(out[f"pred{k}"], ref[f"pred{k}"], **TOL_VALUE)
         k += 1
     assert set(out["grads"]) == set(ref["grads"]), set(out["grads"]) ^ set(ref["grads"])
+    for n, b in ref.get("buffers", {}).items():     # train-mode fixtures: BatchNorm running statistics
+        torch.testing.assert_close(out["buffers"][n], b, msg=lambda m, n=n: f"buffer {n}: {m}", **TOL_VALUE)
+    if truth is not None:
+        assert_case_close_to_truth(res, truth)
+        return
     for n, g in ref["grads"].items():
         torch.testing.assert_close(out["grads"][n], g, msg=lambda m, n=n: f"grad {n}: {m}", **TOL_GRAD)
     if cfg.get("forces"):
         torch.testing.assert_close(out["pos_grad"], ref["pos_grad"], **TOL_GRAD)
+
+
+# ------------------------------------------------------------------ fp64 truth ---
+# north_star: "within fp32 rel 1e-5".  Two fp32 evaluations of the same formula (the reference on
+# the CPU, the kernels on the GPU) differ by rounding noise that grows with the depth of the
+# GEMM / reduction chain; parameter gradients pass through the longest chains.  Where a plain
+# rtol = 1e-5 comparison of the two fp32 results would measure that noise rather than a defect,
+# the tests bound the GPU's error against an fp64 evaluation of the oracle instead:
+#     |gpu - truth|_max  <=  max(SLACK * |cpu_fp32 - truth|_max, 1e-5 * |truth|_max)
+# i.e. the GPU result is within 1e-5 of the exact value relative to the tensor's scale, or at
+# least as close to it as the reference's own fp32 arithmetic gets (up to SLACK).
+import contextlib
+
+TRUTH_SLACK = 4.0
+
+
+@contextlib.contextmanager
+def default_dtype(dtype):
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(dtype)
+    try:
+        yield
+    finally:
+        torch.set_default_dtype(old)
+
+
+def oracle_classes():
+    from oracle import hydragnn_ref as ora
+
+    return {"SCFStack": ora.SCFStack, "EGCLStack": ora.EGCLStack, "PAINNStack": ora.PAINNStack,
+            "PNAStack": ora.PNAStack}
+
+
+def oracle_truth_case(name):
+    """The golden case `name` evaluated by the CPU oracle in fp64 (same weights, same batch, same
+    targets): {"loss", "pred*", "grads", "pos_grad"}."""
+    import make_golden as mg
+
+    fx = golden()[name]
+    kind, cfg, ref = fx["kind"], fx["cfg"], fx["out"]
+    with default_dtype(torch.float64):
+        model = mg.build(oracle_classes(), kind, cfg)
+        model.load_state_dict(fx["state"], strict=True)
+        if cfg.get("eval"):
+            model.eval()
+        batch = {k: (v.double() if torch.is_tensor(v) and v.is_floating_point() else v)
+                 for k, v in fx["batch"].items()}
+        data = mg.Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in batch.items()})
+        out = {}
+        if cfg.get("forces"):
+            data.pos.requires_grad_(True)
+            pred = model(data)
+            loss = model.energy_force_loss(pred, data)[0]
+        else:
+            pred = model(data)
+            loss = model.loss(pred, ref["y"].double(), ref["head_index"])[0]
+        for k, p in enumerate(pred):
+            out[f"pred{k}"] = p.detach()
+        loss.backward()
+        out["loss"] = loss.detach()
+        out["grads"] = {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.grad is not None}
+        if cfg.get("forces"):
+            out["pos_grad"] = data.pos.grad.detach().clone()
+    return out
+
+
+def assert_close_to_truth(gpu, cpu32, truth, what, rel=1e-5, slack=TRUTH_SLACK):
+    gpu, cpu32, truth = gpu.double().cpu(), cpu32.double().cpu(), truth.double().cpu()
+    scale = float(truth.abs().max()) if truth.numel() else 0.0
+    err_gpu = float((gpu - truth).abs().max()) if truth.numel() else 0.0
+    err_cpu = float((cpu32 - truth).abs().max()) if truth.numel() else 0.0
+    bound = max(slack * err_cpu, rel * scale, 1e-12)
+    assert err_gpu <= bound, (f"{what}: |gpu - fp64 truth| = {err_gpu:.3e} exceeds max({slack} x fp32 reference "
+                              f"error {err_cpu:.3e}, {rel} x scale {scale:.3e})")
+
+
+def assert_case_close_to_truth(res, truth):
+    """Every quantity of a golden case within the fp64-anchored bound (see above)."""
+    out, ref = res["out"], res["ref"]
+    assert_close_to_truth(out["loss"], ref["loss"], truth["loss"], "loss")
+    k = 0
+    while f"pred{k}" in ref:
+        assert_close_to_truth(out[f"pred{k}"], ref[f"pred{k}"], truth[f"pred{k}"], f"pred{k}")
+        k += 1
+    assert set(out["grads"]) == set(ref["grads"]), set(out["grads"]) ^ set(ref["grads"])
+    for n, g in ref["grads"].items():
+        assert_close_to_truth(out["grads"][n], g, truth["grads"][n], f"grad {n}")
+    if res["cfg"].get("forces"):
+        assert_close_to_truth(out["pos_grad"], ref["pos_grad"], truth["pos_grad"], "pos_grad (forces)")

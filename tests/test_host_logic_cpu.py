@@ -9,14 +9,17 @@ import parity_util as pu
 from cpu_patch import cpu_kernels
 
 CASES = ["schnet_plain", "schnet_equiv", "schnet_gps", "egnn_gps_edge", "egnn_equiv", "painn_forces",
-         "schnet_forces", "egnn_forces", "pna_multihead", "pna_edge"]
+         "schnet_forces", "egnn_forces", "pna_multihead", "pna_edge",
+         # GPS in train mode (BatchNorm batch statistics), dropout = 0: tests/golden/make_golden_train.py
+         "schnet_gps_train", "egnn_gps_edge_train", "painn_gps_train", "schnet_gps_train_wide",
+         "egnn_gps_train_wide"]
 
 
 @pytest.mark.parametrize("name", CASES)
 def test_product_stack_matches_reference_on_cpu(name):
     with cpu_kernels():
         res = pu.run_golden_case(name, device="cpu")
-    pu.assert_case_close(res)
+    pu.assert_case_close(res, truth=pu.oracle_truth_case(name))
 
 
 def test_batched_laplacian_pe_matches_per_sample():

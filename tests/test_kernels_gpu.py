@@ -9,6 +9,7 @@ import pytest
 import torch
 
 from oracle import kernel_spec as ks
+import parity_util as pu
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -209,7 +210,9 @@ def test_pna_aggregate(ops, N, E, F, hasR, hasM):
 
 # ------------------------------------------------------------------------ attention ---
 @pytest.mark.parametrize("sizes,H,D", [([37], 4, 32), ([5, 64, 1, 130, 23], 4, 32), ([300], 2, 8),
-                                       ([9, 9, 9], 1, 16), ([70, 3], 4, 4), ([1024], 4, 32)])
+                                       ([9, 9, 9], 1, 16), ([70, 3], 4, 4), ([1024], 4, 32),
+                                       # the shapes bench.py times (config 5): whole-batch and per-graph
+                                       ([8192], 4, 32), ([1024] * 8, 4, 32)])
 def test_attn_varlen(ops, sizes, H, D):
     gen = torch.Generator().manual_seed(sum(sizes) + H)
     N = sum(sizes)
@@ -225,8 +228,11 @@ def test_attn_varlen(ops, sizes, H, D):
     dq, dk, dv = ops["attention"]._attn_bwd_raw(do.to(DEV), o, lse, q.to(DEV), k.to(DEV), v.to(DEV),
                                                cu.to(DEV), H, scale)
     rq, rk, rv = ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
-    for got, want in ((dq, rq), (dk, rk), (dv, rv)):
-        torch.testing.assert_close(got.cpu(), want, rtol=1e-4, atol=1e-5)
+    # gradients: within 1e-5 of the dense fp64 result (relative to the tensor's scale), or as close to
+    # it as the dense fp32 CPU evaluation is
+    tq, tk, tv = ks.attn_varlen_bwd(do.double(), q.double(), k.double(), v.double(), cu, H, scale)
+    for what, got, want, truth in (("dq", dq, rq, tq), ("dk", dk, rk, tk), ("dv", dv, rv, tv)):
+        pu.assert_close_to_truth(got, want, truth, what)
 
 
 def test_attn_strided_qkv(ops):
@@ -343,7 +349,7 @@ def test_radius_graph_fesi_full_size_properties(ops):
 
 
 # ------------------------------------------------------------- fused SchNet filter ---
-@pytest.mark.parametrize("E,R", [(1, 8), (127, 8), (1000, 0), (40000, 8)])
+@pytest.mark.parametrize("E,R", [(1, 8), (127, 8), (1000, 0), (40000, 8), (474078, 8)])   # last: config 5's E
 def test_schnet_filter_fwd(ops, E, R):
     """tcgen05 3xTF32 kernel vs the reference op sequence in fp32 on the CPU (and fp64 as the truth):
     the kernel must be as close to fp64 as the fp32 CPU path is, within rel 1e-5 of it."""
@@ -375,7 +381,7 @@ def test_schnet_filter_fwd(ops, E, R):
     assert err_kernel < 4 * err_cpu32 + 1e-6, (err_kernel, err_cpu32)
 
 
-@pytest.mark.parametrize("E,R", [(70, 8), (5000, 0), (40000, 8)])
+@pytest.mark.parametrize("E,R", [(70, 8), (5000, 0), (40000, 8), (474078, 8)])
 def test_schnet_filter_backward_kernels(ops, E, R):
     """hgk_schnet_filter_bwd + hgk_wgrad_tn (through the autograd Function) vs torch autograd of the
     reference op sequence on the CPU."""
@@ -392,21 +398,24 @@ def test_schnet_filter_backward_kernels(ops, E, R):
               torch.randn(F, generator=gen) * 0.1]
     gout = torch.randn(E, F, generator=gen) / E ** 0.5
 
-    cpu = [t.clone().requires_grad_(True) for t in params]
-    w_ref, _ = ks.schnet_filter_fwd(dist, raw, offset, coeff, cutoff, cpu[0], cpu[1][:, :R] if R else None,
-                                    cpu[2], cpu[3], cpu[4])
-    w_ref.backward(gout)
+    def cpu_grads(dtype):
+        cast = lambda t: None if t is None else t.to(dtype)
+        leaves = [t.clone().to(dtype).requires_grad_(True) for t in params]
+        w_ref, _ = ks.schnet_filter_fwd(cast(dist), cast(raw), cast(offset), coeff, cutoff, leaves[0],
+                                        leaves[1][:, :R] if R else None, leaves[2], leaves[3], leaves[4])
+        w_ref.backward(cast(gout))
+        return [t.grad for t in leaves]
 
+    ref32, truth = cpu_grads(torch.float32), cpu_grads(torch.float64)
     dev = lambda t: None if t is None else t.to(DEV)
     gpu = [t.clone().to(DEV).requires_grad_(True) for t in params]
     w = filt.schnet_filter(dev(dist), dev(raw), dev(offset), coeff, cutoff, gpu[0], gpu[1][:, :R] if R else None,
                            gpu[2], gpu[3], gpu[4])
     w.backward(dev(gout))
-    for k, (g, c) in enumerate(zip(gpu, cpu)):
+    for k, g in enumerate(gpu):
         if k == 1 and not R:
             continue
-        scale = float(c.grad.abs().max())
-        torch.testing.assert_close(g.grad.cpu(), c.grad, rtol=1e-4, atol=1e-5 * max(scale, 1.0), msg=lambda m, k=k: f"param {k}: {m}")
+        pu.assert_close_to_truth(g.grad, ref32[k], truth[k], f"param {k}")
 
 
 # ----------------------------------------------------------------------- edge cases ---
@@ -424,8 +433,9 @@ def test_attn_empty_and_tiny_segments(ops):
     torch.testing.assert_close(lse.cpu(), lse_ref, rtol=1e-5, atol=2e-6)
     dq, dk, dv = ops["attention"]._attn_bwd_raw(do.to(DEV), o, lse, q.to(DEV), k.to(DEV), v.to(DEV), cu.to(DEV), H, scale)
     rq, rk, rv = ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
-    for got, want in ((dq, rq), (dk, rk), (dv, rv)):
-        torch.testing.assert_close(got.cpu(), want, rtol=1e-4, atol=1e-5)
+    tq, tk, tv = ks.attn_varlen_bwd(do.double(), q.double(), k.double(), v.double(), cu, H, scale)
+    for what, got, want, truth in (("dq", dq, rq, tq), ("dk", dk, rk, tk), ("dv", dv, rv, tv)):
+        pu.assert_close_to_truth(got, want, truth, what)
 
 
 def test_radius_graph_no_edges_and_single_atoms(ops):

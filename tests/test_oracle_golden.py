@@ -29,7 +29,10 @@ def test_small_functions(golden):
     assert torch.equal(ora.cosine_cutoff(f["dist"], 3.0), f["cutoff"])
 
 
-@pytest.mark.parametrize("name", sorted(mg.MODEL_CASES))
+import make_golden_train as mgt  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(mg.MODEL_CASES) + sorted(mgt.TRAIN_CASES))
 def test_models_match_reference(golden, name):
     fx = golden[name]
     kind, cfg = fx["kind"], fx["cfg"]
@@ -49,6 +52,8 @@ def test_models_match_reference(golden, name):
         torch.testing.assert_close(out["grads"][n], g, rtol=1e-4, atol=1e-6)
     if cfg.get("forces"):
         torch.testing.assert_close(out["pos_grad"], ref["pos_grad"], rtol=1e-4, atol=1e-6)
+    for n, b in ref.get("buffers", {}).items():     # train mode: BatchNorm running statistics after the step
+        torch.testing.assert_close(dict(model.named_buffers())[n], b, **TOL)
 
 
 @pytest.mark.parametrize("case", ["h2_loop0", "h2_loop1", "cr_loop0", "cr_loop1", "tri_loop0",
