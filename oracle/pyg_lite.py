@@ -489,3 +489,37 @@ def reset(value):
     else:
         for child in value.children() if hasattr(value, "children") else []:
             reset(child)
+
+
+# -- torch_geometric.transforms.AddLaplacianEigenvectorPE (2.5.2) ---------------------------------------------
+# reference call site: hydragnn/preprocess/serialized_dataset_loader.py:90-94,183 (k = pe_dim, is_undirected=True)
+def laplacian_eigenvector_pe(edge_index: Tensor, num_nodes: int, k: int, signs: Optional[Tensor] = None):
+    """pe [N, k]: eigenvectors 1..k (ascending eigenvalue; the trivial one skipped) of the symmetric
+    normalised Laplacian  L = I - D^-1/2 A D^-1/2  built the PyG way: get_laplacian(normalization="sym")
+    sums duplicate edges, takes the degree as the ROW sum of A, and zeroes 1/sqrt(deg) of isolated
+    nodes; N < 100 -> numpy.linalg.eigh of the dense matrix, otherwise scipy eigsh(k + 1, which="SA")
+    (is_undirected=True).  PyG then multiplies every column by a RANDOM sign (-1 + 2 randint(0, 2));
+    `signs` ([k] of +-1) stands for that draw, None leaves the solver's signs."""
+    import numpy as np
+
+    N = int(num_nodes)
+    row, col = edge_index[0].numpy(), edge_index[1].numpy()
+    A = np.zeros((N, N), dtype=np.float64)
+    np.add.at(A, (row, col), 1.0)
+    deg = A.sum(1)
+    with np.errstate(divide="ignore"):
+        dis = 1.0 / np.sqrt(deg)
+    dis[np.isinf(dis)] = 0.0
+    L = np.eye(N) - dis[:, None] * A * dis[None, :]
+    if N < 100:
+        vals, vecs = np.linalg.eigh(L)
+    else:
+        from scipy.sparse import csr_matrix
+        from scipy.sparse.linalg import eigsh
+
+        vals, vecs = eigsh(csr_matrix(L), k=k + 1, which="SA", return_eigenvectors=True)
+    vecs = np.real(vecs[:, vals.argsort()])
+    pe = torch.from_numpy(vecs[:, 1:k + 1].copy()).to(torch.float32)
+    if signs is not None:
+        pe = pe * signs.to(pe.dtype)
+    return pe

@@ -36,3 +36,40 @@ def test_batched_laplacian_pe_matches_per_sample():
     ld._laplacian_pe_batched(samples, 3, torch.device("cpu"))
     for d in samples:
         torch.testing.assert_close(d.pe, ld._laplacian_pe(d.edge_index, d.num_nodes, 3), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,k", [(12, 4), (40, 8), (130, 8)])
+def test_laplacian_pe_matches_pyg_transform_up_to_sign(n, k):
+    """preprocess.load_data._laplacian_pe against the restatement of PyG's AddLaplacianEigenvectorPE
+    (oracle/pyg_lite.py; reference: serialized_dataset_loader.py:90-94,183-189) on undirected radius
+    graphs of random points (generic spectrum: no repeated eigenvalues).  PyG multiplies every
+    eigenvector by a random sign, the product fixes the sign (first non-zero entry positive), so the
+    columns agree up to sign and rel_pe = |pe_i - pe_j|, which the convs consume, agrees exactly."""
+    from hydragnn.preprocess import load_data as ld
+    from oracle import pyg_lite as pyg
+
+    for seed in range(n, n + 50):       # a connected graph: a repeated eigenvalue 0 has no unique eigenvectors
+        gen = torch.Generator().manual_seed(seed)
+        pos = torch.rand(n, 3, generator=gen) * (n / 0.4) ** (1.0 / 3.0)
+        ei = pyg.radius_graph_cluster(pos, 2.2, None, False, 32)
+        ei = torch.unique(torch.cat([ei, ei.flip(0)], dim=1), dim=1)      # undirected, no duplicates
+        A = torch.zeros(n, n, dtype=torch.float64)
+        A[ei[0], ei[1]] = 1.0
+        lap = torch.diag(A.sum(1)) - A
+        vals = torch.linalg.eigvalsh(lap)
+        if float(vals[1]) > 1e-6 and float((vals[1:k + 2] - vals[:k + 1]).min()) > 1e-4:
+            break
+    else:
+        pytest.skip("no connected sample found")
+    ours = ld._laplacian_pe(ei, n, k)
+    ref = pyg.laplacian_eigenvector_pe(ei, n, k)
+    sign = torch.sign((ours * ref).sum(0))
+    assert bool((sign != 0).all())
+    torch.testing.assert_close(ours, ref * sign, rtol=1e-4, atol=2e-5)
+    rel_ours = (ours[ei[0]] - ours[ei[1]]).abs()
+    rel_ref = (ref[ei[0]] - ref[ei[1]]).abs()
+    torch.testing.assert_close(rel_ours, rel_ref, rtol=1e-4, atol=2e-5)
+    # the fixed sign convention: first entry with |v| > 1e-9 is positive
+    for j in range(k):
+        col = ours[:, j]
+        assert float(col[torch.nonzero(col.abs() > 1e-9)[0, 0]]) > 0
