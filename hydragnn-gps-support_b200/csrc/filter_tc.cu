@@ -351,9 +351,12 @@ struct WgradArgs {
   const float* b; int64_t ldb;                      // [E, KB] (GAUSS == false)
   const float* d; const float* raw; int64_t ldr;    // GAUSS == true
   const float* offset; float coeff;
-  float* dw_partial;         // [gridDim.x, 128, KB]
-  float* db_partial;         // [gridDim.x, 128]
+  float* dw_partial;         // [gridDim.y, gridDim.x, 128, KB]
+  float* db_partial;         // [gridDim.y, gridDim.x, 128]
   int64_t E;
+  // gridDim.y > 1 (hgk_wgrad_rows): block row y works on the 128-column slice y % num_a_slices of A
+  // and the KB-column slice y / num_a_slices of B
+  int num_a_slices;
 };
 
 template <int KB, bool GAUSS, int G, int R>
@@ -379,6 +382,11 @@ k_wgrad_tn(const WgradArgs p) {
 
   const OperandDesc dA = operand_desc<BE>(AThi, ATlo), dB = operand_desc<BE>(BThi, BTlo);
   constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB);
+  const int a_slice = gridDim.y > 1 ? (int)blockIdx.y % p.num_a_slices : 0;
+  const int b_slice = gridDim.y > 1 ? (int)blockIdx.y / p.num_a_slices : 0;
+  const float* a_base = p.a + a_slice * kFilt;
+  const float* b_base = GAUSS ? nullptr : p.b + b_slice * KB;
+  const int64_t part = (int64_t)blockIdx.y * gridDim.x + blockIdx.x;     // this CTA's partial slot
   Tile<BE, kFilt> ta;                                  // next tile, prefetched in registers
   Tile<BE, KB> tb;
   float dsc[Tile<BE, kFilt>::PER];                     // its row-scale arguments (d_e)
@@ -388,7 +396,7 @@ k_wgrad_tn(const WgradArgs p) {
   auto fetch = [&](int64_t tile) {
     const int32_t row0 = (int32_t)(tile * BE);
     const int32_t row_end = (int32_t)p.E;
-    ta.load(p.a, p.lda, row0, row_end);
+    ta.load(a_base, p.lda, row0, row_end);
     // the row scale is only FETCHED here and applied in stage(): nothing in this function depends
     // on the loads it has just issued
     if (p.scale_d != nullptr) {
@@ -401,7 +409,7 @@ k_wgrad_tn(const WgradArgs p) {
       }
     }
     if (!GAUSS) {
-      tb.load(p.b, p.ldb, row0, row_end);
+      tb.load(b_base, p.ldb, row0, row_end);
     } else {
 #pragma unroll
       for (int it = 0; it < Tile<BE, KB>::PER; ++it) {
@@ -466,7 +474,7 @@ k_wgrad_tn(const WgradArgs p) {
   }
 
   // ---- partial dW: lane n, this thread's KB/2 columns ----
-  float* out = p.dw_partial + ((int64_t)blockIdx.x * kFilt + cs.row_local) * KB + cs.half * (KB / 2);
+  float* out = p.dw_partial + (part * kFilt + cs.row_local) * KB + cs.half * (KB / 2);
   const bool any = (int64_t)blockIdx.x < num_tiles;
 #pragma unroll
   for (int c0 = 0; c0 < KB / 2; c0 += 32) {
@@ -493,7 +501,7 @@ k_wgrad_tn(const WgradArgs p) {
     *reinterpret_cast<float4*>(&cs_s[threadIdx.x >> 7][4 * c]) = colsum;
   }
   __syncthreads();
-  if (threadIdx.x < kFilt) p.db_partial[(int64_t)blockIdx.x * kFilt + threadIdx.x] = cs_s[0][threadIdx.x] + cs_s[1][threadIdx.x];
+  if (threadIdx.x < kFilt) p.db_partial[part * kFilt + threadIdx.x] = cs_s[0][threadIdx.x] + cs_s[1][threadIdx.x];
   cta_teardown(tmem, kCols);
 }
 
@@ -518,6 +526,30 @@ k_wgrad_reduce(float* __restrict__ dw, float* __restrict__ db, const float* __re
   }
   for (; p < P; ++p) acc += __ldg(src + (int64_t)p * stride);
   if (is_w) dw[i] = acc; else db[i - n_w] = acc;
+}
+
+// hgk_wgrad_rows: dW[(ia, n), (ib, k)] = sum_p partial[ib * nA + ia][p][n][k] (CTA order), db[(ia, n)] from
+// the block rows with ib == 0.
+__global__ void __launch_bounds__(256)
+k_wgrad_rows_reduce(float* __restrict__ dw, int64_t lddw, float* __restrict__ db, const float* __restrict__ dw_partial,
+                    const float* __restrict__ db_partial, int P, int nA, int nB) {
+  const int64_t n_w = (int64_t)nA * nB * kFilt * kFilt;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_w + (db != nullptr ? nA * kFilt : 0)) return;
+  if (i < n_w) {
+    const int slice = (int)(i / (kFilt * kFilt)), rem = (int)(i % (kFilt * kFilt));
+    const int ia = slice % nA, ib = slice / nA, n = rem / kFilt, k = rem % kFilt;
+    const float* src = dw_partial + (int64_t)slice * P * kFilt * kFilt + rem;
+    float acc = 0.f;
+    for (int q = 0; q < P; ++q) acc += __ldg(src + (int64_t)q * kFilt * kFilt);
+    dw[(int64_t)(ia * kFilt + n) * lddw + ib * kFilt + k] = acc;
+  } else {
+    const int j = (int)(i - n_w), ia = j / kFilt, n = j % kFilt;
+    const float* src = db_partial + (int64_t)ia * P * kFilt + n;      // slices with ib == 0 come first
+    float acc = 0.f;
+    for (int q = 0; q < P; ++q) acc += __ldg(src + (int64_t)q * kFilt);
+    db[j] = acc;
+  }
 }
 
 }  // namespace tc
@@ -607,7 +639,7 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
     HGK_REQUIRE(ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0, "wgrad_tn: B rows must be 16-byte aligned");
   }
   tc::WgradArgs args{a, lda, scale_d, 3.14159265358979323846f / cutoff, b, ldb, d, raw, ldr, offset, coeff,
-                     dw_partial, db_partial, E};
+                     dw_partial, db_partial, E, 1};
   const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
   cudaStream_t st = (cudaStream_t)stream;
   auto launch = [&](auto kernel, int kb) -> int {
@@ -631,4 +663,40 @@ extern "C" int hgk_wgrad_reduce(float* dw, float* db, const float* dw_partial, c
   const unsigned blocks = (unsigned)ceil_div((int64_t)n_w + n_b, 256);
   tc::k_wgrad_reduce<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw, db, dw_partial, db_partial, (int)P, n_w, n_b);
   return check_launch("wgrad_reduce");
+}
+
+// ---- weight / bias gradients of a node-row Linear of any width (multiples of 128) in two launches ----
+extern "C" int64_t hgk_wgrad_rows_workspace_floats(int64_t M, int32_t NA, int32_t NB) {
+  if (M <= 0 || NA <= 0 || NB <= 0) return 0;
+  const int64_t slices = (int64_t)(NA / tc::kFilt) * (NB / tc::kFilt);
+  return hgk_wgrad_tn_partials(M) * slices * (tc::kFilt * tc::kFilt + tc::kFilt);
+}
+
+extern "C" int hgk_wgrad_rows(float* dw, int64_t lddw, float* db, float* workspace, const float* a, int64_t lda,
+                              int32_t NA, const float* b, int64_t ldb, int32_t NB, int64_t M, void* stream) {
+  HGK_REQUIRE(M >= 1 && NA >= 1 && NB >= 1, "wgrad_rows: bad sizes");
+  if (NA % tc::kFilt != 0 || NB % tc::kFilt != 0)
+    return fail(HGK_ERR_UNSUPPORTED, "wgrad_rows: widths must be multiples of 128 (got %d, %d)", NA, NB);
+  HGK_REQUIRE(dw && workspace && a && b && lddw >= NB, "wgrad_rows: NULL operand");
+  HGK_REQUIRE(lda >= NA && lda % 4 == 0 && ldb >= NB && ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0 &&
+              (reinterpret_cast<uintptr_t>(b) & 15) == 0, "wgrad_rows: rows must be 16-byte aligned");
+  const int nA = NA / tc::kFilt, nB = NB / tc::kFilt;
+  const int64_t P = hgk_wgrad_tn_partials(M);
+  float* dw_partial = workspace;
+  float* db_partial = workspace + P * nA * nB * tc::kFilt * tc::kFilt;
+  tc::WgradArgs args{a, lda, nullptr, 0.f, b, ldb, nullptr, nullptr, 0, nullptr, 0.f, dw_partial, db_partial, M, nA};
+  size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + 128);
+  if (smem < 80 * 1024) smem = 80 * 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(tc::k_wgrad_tn<128, false, 50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_rows: smem opt-in: %s", cudaGetErrorString(err));
+    configured = true;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((unsigned)P, (unsigned)(nA * nB));
+  tc::k_wgrad_tn<128, false, 50, 0><<<grid, tc::kThreads, smem, st>>>(args);
+  const int64_t total = (int64_t)nA * nB * tc::kFilt * tc::kFilt + (db ? nA * tc::kFilt : 0);
+  tc::k_wgrad_rows_reduce<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(dw, lddw, db, dw_partial, db_partial, (int)P, nA, nB);
+  return check_launch("wgrad_rows");
 }

@@ -59,6 +59,31 @@ _SIGNATURES = {
     "hgk_colsum_slabs": (_c_i64, [_c_i64]),
     "hgk_colsum": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
     "hgk_wgrad_reduce": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_i32, _c_ptr]),
+    "hgk_wgrad_rows_workspace_floats": (_c_i64, [_c_i64, _c_i32, _c_i32]),
+    "hgk_wgrad_rows": (_c_i32, [_c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_i64, _c_i32, _c_i64, _c_ptr]),
+    "hgk_linear_tc": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_i32, _c_ptr, _c_ptr, _c_i64, _c_f32,
+         _c_ptr, _c_i64, _c_i64, _c_i32, _c_i32, _c_ptr],
+    ),
+    "hgk_bn_slabs": (_c_i64, [_c_i64]),
+    "hgk_bn_stats": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_f32, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_bn_apply": (
+        _c_i32,
+        [_c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr,
+         _c_ptr, _c_i32, _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_bn_bwd_workspace_floats": (_c_i64, [_c_i64, _c_i32]),
+    "hgk_bn_bwd": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_ptr, _c_ptr,
+         _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr,
+         _c_i64, _c_i32, _c_ptr],
+    ),
+    "hgk_mask_axpy": (_c_i32, [_c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
     "hgk_pna_aggregate_fwd": (
         _c_i32,
         [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
@@ -133,7 +158,8 @@ KERNELS_PER_CALL = {
     "hgk_csr_build": 4, "hgk_csr_build_static": 4, "hgk_contract_node": 1, "hgk_contract_edge_w": 1, "hgk_contract_edge_u": 1,
     "hgk_edge_gather_add": 1, "hgk_schnet_filter_fwd": 1, "hgk_schnet_filter_bwd": 1, "hgk_wgrad_tn": 1, "hgk_wgrad_reduce": 1, "hgk_colsum": 2, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
     "hgk_radius_graph_count": 8, "hgk_radius_graph_fill": 1, "hgk_attn_varlen_fwd": 1,
-    "hgk_attn_varlen_bwd": 3,
+    "hgk_attn_varlen_bwd": 3, "hgk_wgrad_rows": 2, "hgk_linear_tc": 1, "hgk_bn_stats": 2, "hgk_bn_apply": 1,
+    "hgk_bn_bwd": 3, "hgk_mask_axpy": 1,
 }
 
 

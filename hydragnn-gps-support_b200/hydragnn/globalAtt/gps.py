@@ -20,9 +20,15 @@ import torch.nn.functional as F
 from torch import Tensor
 from torch.nn import Dropout, Sequential
 
-from ..nn import Linear, activation_resolver, normalization_resolver
+from ..nn import BatchNorm, Linear, activation_resolver, normalization_resolver
 from ..ops import attn_varlen, linear_rows
+from ..ops import node as node_ops
 from . import graphed_tail
+
+
+# HYDRAGNN_NATIVE_TAIL=0 keeps the torch ops everywhere (A/B runs, debugging)
+import os as _os
+NATIVE_TAIL = _os.environ.get("HYDRAGNN_NATIVE_TAIL", "1") != "0"
 
 
 class GPSConv(torch.nn.Module):
@@ -81,11 +87,42 @@ class GPSConv(torch.nn.Module):
         cu_seqlens[1:] = torch.cumsum(counts, 0)
         return cu_seqlens
 
+    # ------------------------------------------------------------- native node-level part ---
+    def _native(self, x: Tensor) -> bool:
+        """Training step on the kernel library (ops/node.py): tensor-core Linears with fused bias /
+        ReLU / dropout / residual, own BatchNorm.  Taken in train mode for 128-multiple widths, the
+        default block (ReLU MLP, three BatchNorms with running statistics) and a once-differentiable
+        backward; everything else (eval, force loss, other norms / activations) runs the torch ops."""
+        ok = self.__dict__.get("_native_static")
+        if ok is None:
+            norms = (self.norm1, self.norm2, self.norm3)
+            ok = (node_ops.supported_width(self.channels)
+                  and all(isinstance(n, BatchNorm) and n.module.track_running_stats and n.module.momentum is not None
+                          for n in norms)
+                  and isinstance(self.mlp[1], torch.nn.ReLU) and self.attn.in_proj_bias is not None
+                  and self.attn.in_proj_weight is not None)
+            self.__dict__["_native_static"] = ok
+        return (ok and self.training and node_ops.device_ok(x) and x.size(0) > 1
+                and graphed_tail._eager_depth == 0 and NATIVE_TAIL)
+
+    def _bn_args(self):
+        flat, bufs = [], []
+        for norm in (self.norm1, self.norm2, self.norm3):
+            bn = norm.module
+            flat += [bn.weight, bn.bias]
+            bufs.append((bn.running_mean, bn.running_var, bn.num_batches_tracked, bn.momentum, bn.eps))
+        return flat, tuple(bufs)
+
     # The node-level part of the layer (gps.py:116-150 of the reference) in two tensor-only pieces
     # around the attention kernel, so that each piece can be replayed as a CUDA graph
     # (graphed_tail.py) while the attention call stays an ordinary, individually timed launch.
     def _tail_pre(self, x: Tensor, h_local: Optional[Tensor]):
-        """-> (normed local branch or None, projected qkv)."""
+        """-> (local branch or None, projected qkv).  Native path: the local branch is handed on
+        BEFORE its BatchNorm (norm1 is applied together with norm2 in `_tail_post`)."""
+        if self._native(x):
+            out = node_ops.GpsTailPre.apply(x, h_local, self.attn.in_proj_weight, self.attn.in_proj_bias,
+                                            float(self.dropout))
+            return out if h_local is not None else (None, out)
         h1 = None
         if h_local is not None:
             h1 = F.dropout(h_local, p=self.dropout, training=self.training)
@@ -96,6 +133,11 @@ class GPSConv(torch.nn.Module):
         return h1, qkv
 
     def _tail_post(self, x: Tensor, h1: Optional[Tensor], o: Tensor) -> Tensor:
+        if self._native(x):
+            flat, bufs = self._bn_args()
+            return node_ops.GpsTailPost.apply(x, h1, o, self.attn.out_proj.weight, self.attn.out_proj.bias,
+                                              self.mlp[0].weight, self.mlp[0].bias, self.mlp[3].weight,
+                                              self.mlp[3].bias, *flat, bufs, float(self.dropout))
         h = linear_rows(o, self.attn.out_proj.weight, self.attn.out_proj.bias)
         h = F.dropout(h, p=self.dropout, training=self.training)
         h = h + x

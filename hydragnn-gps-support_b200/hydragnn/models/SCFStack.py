@@ -22,6 +22,7 @@ from ..graph import topo_of
 from ..nn import FactoredEdgeAttr, GaussianSmearing, LazyGaussians, Sequential, ShiftedSoftplus
 from ..ops import gather_mul_segment_sum, radius_graph, segment_mean
 from ..ops.filter import fused_filter_ok, schnet_filter
+from ..ops.node import linear_fast
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
 
@@ -124,12 +125,12 @@ class CFConv(nn.Module):
         if isinstance(W, tuple):     # unfused: apply the cosine envelope here (SCFStack.py:268)
             envelope = 0.5 * (torch.cos(edge_weight * math.pi / self.cutoff) + 1.0)
             W = W[0] * envelope.view(-1, 1)
-        x = self.lin1(x)
+        x = linear_fast(x, self.lin1.weight)         # tensor-core kernel at 128-multiple widths
         if self.equivariant:
             unit, _ = get_edge_vectors_and_lengths(pos, edge_index, None, normalize=True, eps=1.0)
             trans = torch.clamp(unit * self.coord_mlp(W), min=-100, max=100)
             pos = pos + segment_mean(trans, topo, 0)
-        x = self.lin2(gather_mul_segment_sum(x, W, topo, side_out=1, side_in=0))
+        x = linear_fast(gather_mul_segment_sum(x, W, topo, side_out=1, side_in=0), self.lin2.weight, self.lin2.bias)
         if self.equivariant:
             return x, pos
         return x

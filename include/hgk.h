@@ -191,6 +191,81 @@ int hgk_wgrad_reduce(float* dw, float* db, const float* dw_partial,
                      const float* db_partial, int64_t P, int32_t KB, int32_t F,
                      void* stream);
 
+/* Weight / bias gradients of a NODE-row Linear of any width (reference: autograd
+ * of the nn.Linear layers of GPSConv and CFConv, hydragnn/globalAtt/gps.py:55-78,
+ * models/SCFStack.py:226-229):  dw[NA, NB] = A^T B,  db[NA] = column sums of A
+ * for A [M, NA], B [M, NB] (row strides lda / ldb), NA and NB multiples of 128.
+ * One launch of the hgk_wgrad_tn kernel over all 128 x 128 blocks plus one
+ * fixed-order reduction; workspace = hgk_wgrad_rows_workspace_floats floats.
+ * db may be NULL. */
+int64_t hgk_wgrad_rows_workspace_floats(int64_t M, int32_t NA, int32_t NB);
+int hgk_wgrad_rows(float* dw, int64_t lddw, float* db, float* workspace,
+                   const float* a, int64_t lda, int32_t NA, const float* b,
+                   int64_t ldb, int32_t NB, int64_t M, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Node-row kernels of the GPS block (reference: hydragnn/globalAtt/gps.py:
+ * 72-83,116-150 = nn.Linear / nn.MultiheadAttention projections, PyG BatchNorm
+ * (nn.BatchNorm1d, batch statistics in training), F.dropout, residual adds).
+ *
+ * hgk_linear_tc:  y[M,N] = residual + scale * mask * [nz != 0] * act(x w^T + bias)
+ *   x [M,K] (row stride ldx); w [N,K] (ldw), or with trans_w != 0 w [K,N]
+ *   (y = x w: the input gradient of a Linear whose weight is w); bias [N];
+ *   relu != 0: act = ReLU; mask [M,N] uint8 contiguous (a dropout keep mask);
+ *   nz [M,N] (ldnz): multiply by scale where nz != 0, by 0 elsewhere (backward
+ *   through dropout + ReLU given their output); residual [M,N] (ldr).  Any of
+ *   bias / mask / nz / residual may be NULL.  tcgen05 with 3xTF32 operand
+ *   splitting (fp32-accurate).  K % 32 == 0, N % 32 == 0 (N % 128 == 0 with
+ *   trans_w), rows 16-byte aligned; otherwise HGK_ERR_UNSUPPORTED.
+ * ------------------------------------------------------------------------- */
+int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
+                  const float* w, int64_t ldw, int32_t trans_w,
+                  const float* bias, int32_t relu, const uint8_t* mask,
+                  const float* nz, int64_t ldnz, float scale,
+                  const float* residual, int64_t ldr, int64_t M, int32_t N,
+                  int32_t K, void* stream);
+
+/* BatchNorm with batch statistics over the N rows of t [N,C] (C % 4 == 0):
+ *   mean[c], rstd[c] = 1 / sqrt(biased var + eps); when running_mean /
+ *   running_var are given they are updated in place with `momentum` (unbiased
+ *   variance), and *num_batches_tracked (int64, may be NULL) is incremented --
+ *   nn.BatchNorm1d in training.  Slabs of 128 rows are reduced with the
+ *   two-pass formula and merged in slab order (Chan et al.): fixed order.
+ *   partial: scratch of 2 * hgk_bn_slabs(N) * C floats. */
+int64_t hgk_bn_slabs(int64_t N);
+int hgk_bn_stats(float* mean, float* rstd, float* running_mean,
+                 float* running_var, int64_t* num_batches_tracked,
+                 float momentum, float eps, float* partial, const float* t,
+                 int64_t ldt, int64_t N, int32_t C, void* stream);
+/* out = act( BN_a(ta) [+ BN_b(tb)] ),  BN(t) = (t - mean) * rstd * gamma + beta
+ * (gamma / beta may be NULL; tb NULL = one input; relu != 0: act = ReLU). */
+int hgk_bn_apply(float* out, int64_t ldo, const float* ta, int64_t ldta,
+                 const float* mean_a, const float* rstd_a, const float* gamma_a,
+                 const float* beta_a, const float* tb, int64_t ldtb,
+                 const float* mean_b, const float* rstd_b, const float* gamma_b,
+                 const float* beta_b, int32_t relu, int64_t N, int32_t C,
+                 void* stream);
+/* Backward of hgk_bn_apply without the activation, for the gradient g [N,C] of
+ * its output (the same g reaches both inputs):
+ *   dt = gamma rstd (g - mean_n(g) - xhat mean_n(g xhat)),  dgamma = sum_n g xhat,
+ *   dbeta = sum_n g; dta / dtb [N,C] contiguous.  dz (optional) = scale * mask *
+ *   dt: the gradient behind the dropout that fed the BatchNorm input.
+ *   workspace: hgk_bn_bwd_workspace_floats(N, C) floats; column sums in slab order. */
+int64_t hgk_bn_bwd_workspace_floats(int64_t N, int32_t C);
+int hgk_bn_bwd(float* dta, float* dza, const uint8_t* mask_a, float scale_a,
+               float* dgamma_a, float* dbeta_a, float* dtb, float* dzb,
+               const uint8_t* mask_b, float scale_b, float* dgamma_b,
+               float* dbeta_b, float* workspace, const float* g, int64_t ldg,
+               const float* ta, int64_t ldta, const float* mean_a,
+               const float* rstd_a, const float* gamma_a, const float* tb,
+               int64_t ldtb, const float* mean_b, const float* rstd_b,
+               const float* gamma_b, int64_t N, int32_t C, void* stream);
+/* out[N,C] = residual + scale * mask * z  (F.dropout + residual add,
+ * gps.py:116-117,134-135; mask / residual may be NULL). */
+int hgk_mask_axpy(float* out, const float* z, int64_t ldz, const uint8_t* mask,
+                  float scale, const float* residual, int64_t ldr, int64_t N,
+                  int32_t C, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * PNA multi-aggregation (reference: PNAStack.py:43-53 -> PyG PNAConv +
  * DegreeScalerAggregation with aggregators mean,min,max,std).

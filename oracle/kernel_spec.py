@@ -229,3 +229,80 @@ def schnet_filter_fwd(dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
     h = torch.nn.functional.softplus(torch.nn.functional.linear(feats, weight, b0)) - math.log(2.0)
     env = 0.5 * (torch.cos(dist * math.pi / cutoff) + 1.0)
     return torch.nn.functional.linear(h, w1, b1) * env.view(-1, 1), h
+
+
+# ---- node-row kernels of the GPS block (csrc/node_tc.cu; reference hydragnn/globalAtt/gps.py:72-83,116-150) ----
+def linear_tc(x, w, bias=None, trans_w=False, relu=False, mask=None, nz=None, scale=1.0, residual=None):
+    """hgk_linear_tc: residual + scale * mask * [nz != 0] * act(x w^T + bias) as the torch ops it replaces."""
+    y = x @ (w if trans_w else w.t())
+    if bias is not None:
+        y = y + bias
+    if relu:
+        y = torch.relu(y)
+    if mask is not None:
+        y = y * mask.to(y.dtype) * scale
+    if nz is not None:
+        y = y * (nz != 0).to(y.dtype) * scale
+    if residual is not None:
+        y = y + residual
+    return y
+
+
+def wgrad_rows(a, b, want_bias=True):
+    """hgk_wgrad_rows: (a^T b, column sums of a)."""
+    return a.t() @ b, (a.sum(0) if want_bias else None)
+
+
+def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, momentum=0.1, eps=1e-5):
+    """hgk_bn_stats: what nn.BatchNorm1d computes in training (biased variance normalises, the unbiased
+    one goes into running_var)."""
+    n = t.size(0)
+    mean = t.mean(0)
+    var = t.var(0, unbiased=False)
+    if running_mean is not None:
+        running_mean.mul_(1 - momentum).add_(momentum * mean)
+        running_var.mul_(1 - momentum).add_(momentum * var * (n / max(n - 1, 1)))
+    if num_batches_tracked is not None:
+        num_batches_tracked.add_(1)
+    return mean, torch.rsqrt(var + eps)
+
+
+def _bn_side(t, p):
+    y = (t - p.mean) * p.rstd
+    if p.gamma is not None:
+        y = y * p.gamma
+    if p.beta is not None:
+        y = y + p.beta
+    return y
+
+
+def bn_apply(ta, pa, tb=None, pb=None, relu=False):
+    y = _bn_side(ta, pa)
+    if tb is not None:
+        y = y + _bn_side(tb, pb)
+    return torch.relu(y) if relu else y
+
+
+def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, scale_b=1.0):
+    """hgk_bn_bwd: the standard BatchNorm backward with batch statistics,
+    dt = gamma rstd (g - mean(g) - xhat mean(g xhat))."""
+    n = ta.size(0)
+    out = {}
+    for key, t, p, mask, scale in (("a", ta, pa, mask_a, scale_a), ("b", tb, pb, mask_b, scale_b)):
+        if t is None:
+            continue
+        xhat = (t - p.mean) * p.rstd
+        s0, sx = g.sum(0), (g * xhat).sum(0)
+        dt = p.rstd * (g - s0 / n - xhat * (sx / n))
+        if p.gamma is not None:
+            dt = dt * p.gamma
+        out["dt" + key] = dt
+        out["dz" + key] = dt if mask is None else dt * mask.to(dt.dtype) * scale
+        out["dgamma_" + key] = sx if p.gamma is not None else None
+        out["dbeta_" + key] = s0
+    return out
+
+
+def mask_axpy(z, mask=None, scale=1.0, residual=None):
+    y = z if mask is None else z * mask.to(z.dtype) * scale
+    return y if residual is None else y + residual

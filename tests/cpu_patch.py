@@ -81,7 +81,7 @@ def _radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=N
 
 @contextlib.contextmanager
 def cpu_kernels():
-    from hydragnn.ops import attention, contract, pna, topo
+    from hydragnn.ops import attention, contract, node, pna, topo
     import importlib
 
     import hydragnn.ops as ops_pkg
@@ -95,6 +95,10 @@ def cpu_kernels():
         (pna, "_pna_fwd_raw", _pna_fwd_raw), (pna, "_pna_bwd_raw", _pna_bwd_raw),
         (attention, "_attn_fwd_raw", _attn_fwd_raw), (attention, "_attn_bwd_raw", _attn_bwd_raw),
         (topo, "build_csr", _build_csr), (ops_pkg, "radius_graph", _radius_graph),
+        # node-row kernels of the GPS block: the autograd Functions of ops/node.py run over their restatement
+        (node, "linear_tc", ks.linear_tc), (node, "wgrad_rows", ks.wgrad_rows), (node, "bn_stats", ks.bn_stats),
+        (node, "bn_apply", ks.bn_apply), (node, "bn_bwd", ks.bn_bwd), (node, "mask_axpy", ks.mask_axpy),
+        (node, "device_ok", lambda t: t.dtype == torch.float32),
         (scf_mod, "radius_graph", _radius_graph), (radius_mod, "radius_graph", _radius_graph),
     ]
     saved = [(m, n, getattr(m, n)) for m, n, _ in patches]
