@@ -16,6 +16,8 @@
 //     dQ kernel  : lanes = queries;  S, dP (SS)  ->  dS (hi, lo) to TMEM  ->  dQ += dS K     (TS)
 //     dK/dV kern.: lanes = keys;   S^T, dP^T (SS) -> P^T, dS^T to TMEM -> dV += P^T dO, dK += dS^T Q (TS)
 //   Deterministic: every output element is produced by exactly one CTA, no float atomics.
+#include <mutex>
+
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
 
@@ -1087,11 +1089,24 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
 }
 
 // ---------------------------------------------------------------------------------- launch ---
+// cudaFuncSetAttribute is per function and costs host microseconds on a host-bound step: done once per
+// kernel (a handful of kernels: linear scan of a small table, guarded for concurrent host threads)
 template <typename K>
 int opt_in_smem(K kernel, size_t bytes, const char* what) {
+  static std::mutex mu;
+  static const void* done[16];
+  static int n_done = 0;
+  const void* key = reinterpret_cast<const void*>(kernel);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < n_done; ++i)
+      if (done[i] == key) return HGK_OK;
+  }
   cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (err != cudaSuccess)
     return fail(HGK_ERR_CUDA, "%s: smem opt-in (%zu B) failed: %s", what, bytes, cudaGetErrorString(err));
+  std::lock_guard<std::mutex> lock(mu);
+  if (n_done < 16) done[n_done++] = key;
   return HGK_OK;
 }
 

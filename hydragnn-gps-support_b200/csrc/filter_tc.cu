@@ -242,7 +242,9 @@ namespace tc {
 // One persistent CTA per SM walks 128-edge tiles: dZ1 (hi, lo) goes to TMEM as the A operand,
 // W1^T (hi, lo) is resident in shared memory, dZ0 is written to HBM for the weight-gradient kernel.
 struct FilterBwdArgs {
-  const float* gw;     // [E, 128] gradient of the filter
+  const float* gw;     // [E, 128] gradient of the filter, or NULL: gw[e] = g[gi[e]] * x[xi[e]] formed here
+  const float* g; int64_t ldg; const int32_t* gi;     // (the two node tables stay in L2; nothing [E, 128]
+  const float* x; int64_t ldx; const int32_t* xi;     //  is read for the filter gradient)
   const float* h;      // [E, 128] saved hidden activations
   const float* d;      // [E]
   float pi_over_cutoff;
@@ -281,12 +283,30 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
     const float dist = ok ? __ldg(p.d + e) : 0.f;
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);
     {
-      const float* grow = p.gw + e * kFilt + c0;
+      const bool gathered = p.gw == nullptr;
+      const float* grow = nullptr;
+      const float* xrow = nullptr;
+      if (ok) {
+        if (gathered) {
+          grow = p.g + (int64_t)__ldg(p.gi + e) * p.ldg + c0;
+          xrow = p.x + (int64_t)__ldg(p.xi + e) * p.ldx + c0;
+        } else {
+          grow = p.gw + e * kFilt + c0;
+        }
+      }
       uint32_t hi[32], lo[32];
 #pragma unroll
       for (int j = 0; j < 32; j += 8) {
         float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
-        if (ok) ld_global_nc_v8(grow + j, g0, g1);
+        if (ok) {
+          ld_global_nc_v8(grow + j, g0, g1);
+          if (gathered) {
+            float4 x0, x1;
+            ld_global_nc_v8(xrow + j, x0, x1);
+            g0.x *= x0.x; g0.y *= x0.y; g0.z *= x0.z; g0.w *= x0.w;
+            g1.x *= x1.x; g1.y *= x1.y; g1.z *= x1.z; g1.w *= x1.w;
+          }
+        }
         const float x[8] = {g0.x * env, g0.y * env, g0.z * env, g0.w * env, g1.x * env, g1.y * env, g1.z * env, g1.w * env};
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -345,7 +365,7 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
 // Each CTA reduces its share of 64-edge tiles into a TMEM accumulator and writes ONE partial; the
 // partials are summed in a fixed order afterwards (deterministic, no atomics).
 struct WgradArgs {
-  const float* a; int64_t lda;   // [E, 128], row stride lda
+  const float* a; int64_t lda;   // [E, 128], row stride lda; with a_idx: A[e] = a[a_idx[e]] * a2[a2_idx[e]]
   const float* scale_d;      // [E] or NULL: multiply row e of A by 0.5 (cos(d_e pi / r_c) + 1)
   float pi_over_cutoff;
   const float* b; int64_t ldb;                      // [E, KB] (GAUSS == false)
@@ -357,6 +377,8 @@ struct WgradArgs {
   // gridDim.y > 1 (hgk_wgrad_rows): block row y works on the 128-column slice y % num_a_slices of A
   // and the KB-column slice y / num_a_slices of B
   int num_a_slices;
+  // gathered A operand (CFConv filter gradient formed on the fly): both NULL = plain rows of a
+  const int32_t* a_idx; const float* a2; int64_t lda2; const int32_t* a2_idx;
 };
 
 template <int KB, bool GAUSS, int G, int R>
@@ -396,7 +418,22 @@ k_wgrad_tn(const WgradArgs p) {
   auto fetch = [&](int64_t tile) {
     const int32_t row0 = (int32_t)(tile * BE);
     const int32_t row_end = (int32_t)p.E;
-    ta.load(a_base, p.lda, row0, row_end);
+    if (p.a_idx == nullptr) {
+      ta.load(a_base, p.lda, row0, row_end);
+    } else {
+#pragma unroll
+      for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
+        int r, c;
+        Tile<BE, kFilt>::coord(it, r, c);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < row_end) {
+          const float4 ga = __ldg(reinterpret_cast<const float4*>(a_base + (int64_t)__ldg(p.a_idx + row0 + r) * p.lda + 4 * c));
+          const float4 xa = __ldg(reinterpret_cast<const float4*>(p.a2 + (int64_t)__ldg(p.a2_idx + row0 + r) * p.lda2 + 4 * c));
+          v = make_float4(ga.x * xa.x, ga.y * xa.y, ga.z * xa.z, ga.w * xa.w);
+        }
+        ta.v[it] = v;
+      }
+    }
     // the row scale is only FETCHED here and applied in stage(): nothing in this function depends
     // on the loads it has just issued
     if (p.scale_d != nullptr) {
@@ -586,16 +623,29 @@ extern "C" int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const f
   const unsigned grid = (unsigned)imin64(tiles, kNumSM);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t err;
-  if (R == 8) {
-    err = cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static bool configured[2] = {false, false};
+  if (!configured[R == 8 ? 1 : 0]) {
+    err = R == 8 ? cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                 : cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in: %s", cudaGetErrorString(err));
-    tc::k_schnet_filter_fwd<50, 8><<<grid, tc::kFiltThreads, smem, st>>>(a);
-  } else {
-    err = cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in: %s", cudaGetErrorString(err));
-    tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kFiltThreads, smem, st>>>(a);
+    configured[R == 8 ? 1 : 0] = true;
   }
+  if (R == 8) tc::k_schnet_filter_fwd<50, 8><<<grid, tc::kFiltThreads, smem, st>>>(a);
+  else tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kFiltThreads, smem, st>>>(a);
   return check_launch("schnet_filter_fwd");
+}
+
+static int filter_bwd_launch(const tc::FilterBwdArgs& a, void* stream) {
+  const size_t smem = sizeof(float) * 2 * tc::kFilt * tc::kFilt;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(tc::k_schnet_filter_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_bwd: smem opt-in: %s", cudaGetErrorString(err));
+    configured = true;
+  }
+  const unsigned grid = (unsigned)imin64(ceil_div(a.E, tc::kFilt), kNumSM);
+  tc::k_schnet_filter_bwd<<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a);
+  return check_launch("schnet_filter_bwd");
 }
 
 extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h, const float* d,
@@ -604,13 +654,21 @@ extern "C" int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h
   if (E == 0) return HGK_OK;
   HGK_REQUIRE(dz0 && gw && h && d && w1t, "schnet_filter_bwd: NULL operand");
   if (F != tc::kFilt) return fail(HGK_ERR_UNSUPPORTED, "schnet_filter_bwd: built for F=128 (got %d)", F);
-  tc::FilterBwdArgs a{gw, h, d, 3.14159265358979323846f / cutoff, w1t, dz0, E};
-  const size_t smem = sizeof(float) * 2 * tc::kFilt * tc::kFilt;
-  cudaError_t err = cudaFuncSetAttribute(tc::k_schnet_filter_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_bwd: smem opt-in: %s", cudaGetErrorString(err));
-  const unsigned grid = (unsigned)imin64(ceil_div(E, tc::kFilt), kNumSM);
-  tc::k_schnet_filter_bwd<<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a);
-  return check_launch("schnet_filter_bwd");
+  tc::FilterBwdArgs a{gw, nullptr, 0, nullptr, nullptr, 0, nullptr, h, d, 3.14159265358979323846f / cutoff, w1t, dz0, E};
+  return filter_bwd_launch(a, stream);
+}
+
+extern "C" int hgk_cfconv_filter_bwd(float* dz0, const float* g, int64_t ldg, const int32_t* gi, const float* x,
+                                     int64_t ldx, const int32_t* xi, const float* h, const float* d, float cutoff,
+                                     const float* w1t, int64_t E, int32_t F, void* stream) {
+  HGK_REQUIRE(E >= 0, "cfconv_filter_bwd: negative E");
+  if (E == 0) return HGK_OK;
+  HGK_REQUIRE(dz0 && g && gi && x && xi && h && d && w1t, "cfconv_filter_bwd: NULL operand");
+  if (F != tc::kFilt) return fail(HGK_ERR_UNSUPPORTED, "cfconv_filter_bwd: built for F=128 (got %d)", F);
+  HGK_REQUIRE(ldg % 8 == 0 && ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(g) & 31) == 0 &&
+              (reinterpret_cast<uintptr_t>(x) & 31) == 0, "cfconv_filter_bwd: node rows must be 32-byte aligned");
+  tc::FilterBwdArgs a{nullptr, g, ldg, gi, x, ldx, xi, h, d, 3.14159265358979323846f / cutoff, w1t, dz0, E};
+  return filter_bwd_launch(a, stream);
 }
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
@@ -620,10 +678,35 @@ extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   return imin64(ceil_div(E, 64), 2 * (int64_t)kNumSM);
 }
 
+static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, int64_t lda, const int32_t* a_idx,
+                         const float* a2, int64_t lda2, const int32_t* a2_idx,
+                         const float* scale_d, float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
+                         const float* raw, int64_t ldr, int32_t R, const float* offset, int32_t G,
+                         float coeff, int64_t E, int32_t F, void* stream);
+
 extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a, int64_t lda,
                             const float* scale_d, float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
                             const float* raw, int64_t ldr, int32_t R, const float* offset, int32_t G,
                             float coeff, int64_t E, int32_t F, void* stream) {
+  return wgrad_tn_impl(dw_partial, db_partial, a, lda, nullptr, nullptr, 0, nullptr, scale_d, cutoff, b, ldb, KB, d, raw,
+                       ldr, R, offset, G, coeff, E, F, stream);
+}
+
+/* A[e] = g[gi[e]] * x[xi[e]] * envelope(scale_d[e]) formed on the fly, B = h [E, 128] */
+extern "C" int hgk_cfconv_wgrad(float* dw_partial, float* db_partial, const float* g, int64_t ldg, const int32_t* gi,
+                                const float* x, int64_t ldx, const int32_t* xi, const float* scale_d, float cutoff,
+                                const float* b, int64_t ldb, int64_t E, int32_t F, void* stream) {
+  HGK_REQUIRE(g && gi && x && xi && b, "cfconv_wgrad: NULL operand");
+  HGK_REQUIRE(ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "cfconv_wgrad: x rows must be 16-byte aligned");
+  return wgrad_tn_impl(dw_partial, db_partial, g, ldg, gi, x, ldx, xi, scale_d, cutoff, b, ldb, 128, nullptr, nullptr, 0,
+                       0, nullptr, 0, 0.f, E, F, stream);
+}
+
+static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, int64_t lda, const int32_t* a_idx,
+                         const float* a2, int64_t lda2, const int32_t* a2_idx,
+                         const float* scale_d, float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
+                         const float* raw, int64_t ldr, int32_t R, const float* offset, int32_t G,
+                         float coeff, int64_t E, int32_t F, void* stream) {
   HGK_REQUIRE(E >= 0, "wgrad_tn: negative E");
   if (E == 0) return HGK_OK;
   HGK_REQUIRE(dw_partial && db_partial && a, "wgrad_tn: NULL operand");
@@ -639,20 +722,24 @@ extern "C" int hgk_wgrad_tn(float* dw_partial, float* db_partial, const float* a
     HGK_REQUIRE(ldb % 4 == 0 && (reinterpret_cast<uintptr_t>(b) & 15) == 0, "wgrad_tn: B rows must be 16-byte aligned");
   }
   tc::WgradArgs args{a, lda, scale_d, 3.14159265358979323846f / cutoff, b, ldb, d, raw, ldr, offset, coeff,
-                     dw_partial, db_partial, E, 1};
+                     dw_partial, db_partial, E, 1, a_idx, a2, lda2, a2_idx};
   const unsigned grid = (unsigned)hgk_wgrad_tn_partials(E);
   cudaStream_t st = (cudaStream_t)stream;
-  auto launch = [&](auto kernel, int kb) -> int {
+  static bool configured[3] = {false, false, false};      // the smem opt-in is per function: once is enough
+  auto launch = [&](auto kernel, int kb, int slot) -> int {
     size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + kb);
     if (smem < 80 * 1024) smem = 80 * 1024;    // caps the occupancy at 2 CTAs per SM (register budget)
-    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
+    if (!configured[slot]) {
+      cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
+      configured[slot] = true;
+    }
     kernel<<<grid, tc::kThreads, smem, st>>>(args);
     return check_launch("wgrad_tn");
   };
-  if (!gauss) return launch(tc::k_wgrad_tn<128, false, 50, 0>, 128);
-  if (R == 8) return launch(tc::k_wgrad_tn<64, true, 50, 8>, 64);
-  return launch(tc::k_wgrad_tn<64, true, 50, 0>, 64);
+  if (!gauss) return launch(tc::k_wgrad_tn<128, false, 50, 0>, 128, 0);
+  if (R == 8) return launch(tc::k_wgrad_tn<64, true, 50, 8>, 64, 1);
+  return launch(tc::k_wgrad_tn<64, true, 50, 0>, 64, 2);
 }
 
 extern "C" int hgk_wgrad_reduce(float* dw, float* db, const float* dw_partial, const float* db_partial,
@@ -684,7 +771,8 @@ extern "C" int hgk_wgrad_rows(float* dw, int64_t lddw, float* db, float* workspa
   const int64_t P = hgk_wgrad_tn_partials(M);
   float* dw_partial = workspace;
   float* db_partial = workspace + P * nA * nB * tc::kFilt * tc::kFilt;
-  tc::WgradArgs args{a, lda, nullptr, 0.f, b, ldb, nullptr, nullptr, 0, nullptr, 0.f, dw_partial, db_partial, M, nA};
+  tc::WgradArgs args{a, lda, nullptr, 0.f, b, ldb, nullptr, nullptr, 0, nullptr, 0.f, dw_partial, db_partial, M, nA,
+                     nullptr, nullptr, 0, nullptr};
   size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + 128);
   if (smem < 80 * 1024) smem = 80 * 1024;
   static bool configured = false;

@@ -50,6 +50,10 @@ _SIGNATURES = {
          _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_schnet_filter_bwd": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i32, _c_ptr]),
+    "hgk_cfconv_filter_bwd": (_c_i32, [_c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_f32,
+                                       _c_ptr, _c_i64, _c_i32, _c_ptr]),
+    "hgk_cfconv_wgrad": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_f32,
+                                  _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
     "hgk_wgrad_tn_partials": (_c_i64, [_c_i64]),
     "hgk_wgrad_tn": (
         _c_i32,

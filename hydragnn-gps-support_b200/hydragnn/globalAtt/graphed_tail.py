@@ -48,14 +48,20 @@ class _Piece(torch.nn.Module):
     """`layer._tail_pre` / `_tail_post` as a module of tensors only.  It shares the layer's parameter
     objects and is deliberately NOT registered as a child of the layer (no extra state_dict keys)."""
 
-    def __init__(self, layer, which, has_local):
+    def __init__(self, layer, which, has_local, native=False):
         super().__init__()
+        # register exactly the parameters the piece uses: make_graphed_callables differentiates the
+        # captured backward with respect to every parameter of the module.  On the kernel-library path
+        # (GPSConv._native) norm1 is applied in the second piece, together with norm2.
         if which == "pre":
-            self.norm1 = layer.norm1
+            if not native:
+                self.norm1 = layer.norm1
             self.in_w, self.in_b = layer.attn.in_proj_weight, layer.attn.in_proj_bias
         else:
             self.out_proj, self.mlp = layer.attn.out_proj, layer.mlp
             self.norm2, self.norm3 = layer.norm2, layer.norm3
+            if native and has_local:
+                self.norm1 = layer.norm1
         self._layer = [layer]
         self.which, self.has_local = which, has_local
 
@@ -81,12 +87,12 @@ def _batchnorm_state(layer):
     return out
 
 
-def _capture(layer, which, has_local, args):
+def _capture(layer, which, has_local, args, native=False):
     """Graph one piece for this input signature.  The warm-up passes of make_graphed_callables run
     real forwards: BatchNorm running statistics are restored afterwards (the random stream does
     advance -- dropout masks are not reproducible across devices anyway)."""
     saved = _batchnorm_state(layer)
-    piece = _Piece(layer, which, has_local)
+    piece = _Piece(layer, which, has_local, native)
     piece.train()
     sample = tuple(a.detach().clone().requires_grad_(True) for a in args)
     graphed = torch.cuda.make_graphed_callables(piece, sample)
@@ -121,8 +127,9 @@ def run(layer, which, x, *rest):
         ready = sum(1 for e in cache.values() if e["graphed"] is not None)
         if entry["seen"] < CAPTURE_AFTER or ready >= MAX_GRAPHS_PER_LAYER or not all(a.requires_grad for a in args):
             return _eager(layer, which, x, *rest)
-        if not all(p.requires_grad for p in _Piece(layer, which, has_local).parameters()):
+        native = bool(layer._native(x))
+        if not all(p.requires_grad for p in _Piece(layer, which, has_local, native).parameters()):
             entry["seen"] = -(1 << 30)                 # frozen parameters (freeze_conv): never capture this one
             return _eager(layer, which, x, *rest)
-        entry["graphed"] = _capture(layer, which, has_local, args)
+        entry["graphed"] = _capture(layer, which, has_local, args, native)
     return entry["graphed"](*args)

@@ -21,7 +21,7 @@ from torch import nn
 from ..graph import topo_of
 from ..nn import FactoredEdgeAttr, GaussianSmearing, LazyGaussians, Sequential, ShiftedSoftplus
 from ..ops import gather_mul_segment_sum, radius_graph, segment_mean
-from ..ops.filter import fused_filter_ok, schnet_filter
+from ..ops.filter import cfconv_fused, fused_filter_ok, schnet_filter
 from ..ops.node import linear_fast
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
@@ -119,8 +119,30 @@ class CFConv(nn.Module):
             h = self.nn(feats)
         return h, dist
 
+    def _fused_args(self, edge_rbf, edge_attr):
+        """Arguments of the fused filter kernel when it applies (see `_filter`), else None."""
+        first, last = self.nn[0], self.nn[2]
+        if not isinstance(edge_rbf, LazyGaussians):
+            return None
+        G = edge_rbf.offset.numel()
+        factored = isinstance(edge_attr, FactoredEdgeAttr)
+        raw = edge_attr.raw if factored else None
+        if not ((edge_attr is None or factored) and fused_filter_ok(edge_rbf.dist, raw, first.out_features, G)
+                and last.in_features == last.out_features == first.out_features):
+            return None
+        w0r = first.weight[:, G:] @ edge_attr.matrix if factored else None
+        return (edge_rbf.dist, raw, edge_rbf.offset, edge_rbf.coeff, self.cutoff, first.weight[:, :G], w0r,
+                first.bias, last.weight, last.bias)
+
     def forward(self, x, pos, edge_index, edge_weight, edge_rbf, edge_attr=None):
         topo = topo_of(edge_index, x.size(0))
+        if not self.equivariant:
+            fused = self._fused_args(edge_rbf, edge_attr)
+            if fused is not None:
+                # filter network + envelope + aggregation as one autograd node: its backward forms the
+                # filter gradient inside the kernels instead of writing and re-reading an [E, F] tensor
+                x1 = linear_fast(x, self.lin1.weight)
+                return linear_fast(cfconv_fused(x1, topo, *fused), self.lin2.weight, self.lin2.bias)
         W = self._filter(edge_rbf, edge_attr)
         if isinstance(W, tuple):     # unfused: apply the cosine envelope here (SCFStack.py:268)
             envelope = 0.5 * (torch.cos(edge_weight * math.pi / self.cutoff) + 1.0)

@@ -110,3 +110,87 @@ class SchnetFilter(torch.autograd.Function):
 
 def schnet_filter(dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
     return SchnetFilter.apply(dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1)
+
+
+# ------------------------------------------------------------ filter network + aggregation ---
+def _cfconv_filter_bwd_raw(g, x1, topo, h, dist, cutoff, w1t):
+    """dZ0 with the filter gradient gW[e] = g[dst(e)] * x1[src(e)] formed inside the kernel."""
+    E, F = h.shape
+    dz0 = torch.empty_like(h)
+    g_t, ldg = _hgk.rows(g)
+    x_t, ldx = _hgk.rows(x1)
+    _hgk.call("hgk_cfconv_filter_bwd", _hgk.ptr(dz0), _hgk.ptr(g_t), ldg, _hgk.ptr(topo.idx[1]), _hgk.ptr(x_t), ldx,
+              _hgk.ptr(topo.idx[0]), _hgk.ptr(h), _hgk.ptr(dist), float(cutoff), _hgk.ptr(w1t), E, F,
+              cost=(E * (8 * F + 12) + 2 * g.size(0) * 4 * F, 2 * E * F * F))
+    return dz0
+
+
+def _cfconv_wgrad_raw(g, x1, topo, dist, cutoff, h):
+    """(dW1, db1) = ((gW * envelope)^T h, column sums) with gW formed on the fly."""
+    E, F = h.shape
+    L = _hgk.lib()
+    P = L.hgk_wgrad_tn_partials(E)
+    dw = torch.empty((P, F, F), dtype=torch.float32, device=h.device)
+    db = torch.empty((P, F), dtype=torch.float32, device=h.device)
+    g_t, ldg = _hgk.rows(g)
+    x_t, ldx = _hgk.rows(x1)
+    _hgk.call("hgk_cfconv_wgrad", _hgk.ptr(dw), _hgk.ptr(db), _hgk.ptr(g_t), ldg, _hgk.ptr(topo.idx[1]), _hgk.ptr(x_t),
+              ldx, _hgk.ptr(topo.idx[0]), _hgk.ptr(dist), float(cutoff), _hgk.ptr(h), h.stride(0), E, F,
+              cost=(E * (4 * F + 12) + 2 * g.size(0) * 4 * F, 2 * E * F * F))
+    gw = torch.empty((F, F), dtype=torch.float32, device=h.device)
+    gb = torch.empty(F, dtype=torch.float32, device=h.device)
+    _hgk.call("hgk_wgrad_reduce", _hgk.ptr(gw), _hgk.ptr(gb), _hgk.ptr(dw), _hgk.ptr(db), P, F, F,
+              cost=(4 * P * F * (F + 1), 0))
+    return gw, gb
+
+
+class CFConvFused(torch.autograd.Function):
+    """out[t] = sum_{e: dst(e) = t} x1[src(e)] * W_e with W = filter network(d, raw) * envelope
+    (reference SCFStack.py:268-293: the `nn` Sequential, the cosine cutoff and PyG's propagate) as ONE
+    autograd node.  Forward: the fused filter kernel, then the CSR aggregation.  Backward: the filter
+    gradient gW[e] = g[dst(e)] * x1[src(e)] is never written to memory -- the dZ0 kernel and the dW1
+    kernel both form it from the two node tables (4 MB each, L2-resident) while they stage their
+    operands, which removes one [E, F] write and two [E, F] reads per layer and the kernel that
+    produced it.  First derivatives only (same condition as `schnet_filter`)."""
+
+    @staticmethod
+    def forward(ctx, x1, topo, dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
+        from .contract import _node_raw
+
+        F, G = w0g.shape
+        GP = (G + 3) // 4 * 4
+        w0p = torch.zeros((F, 64), dtype=torch.float32, device=dist.device)
+        w0p[:, :G] = w0g
+        if raw is not None:
+            raw = raw.contiguous()
+            w0p[:, GP:GP + raw.size(1)] = w0r
+        dist = dist.contiguous()
+        x1 = x1.contiguous()
+        w, h = _filter_fwd_raw(dist, raw, offset, coeff, cutoff, w0p, b0.contiguous(), w1.contiguous(), b1.contiguous())
+        out = _node_raw(topo, 1, x1, 0, w, None, 1, 1, F)
+        ctx.save_for_backward(x1, dist, raw, offset, h, w, w1)
+        ctx.topo, ctx.coeff, ctx.cutoff = topo, coeff, cutoff
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g):
+        from .contract import _node_raw
+
+        x1, dist, raw, offset, h, w, w1 = ctx.saved_tensors
+        topo = ctx.topo
+        F = h.size(1)
+        G = offset.numel()
+        GP = (G + 3) // 4 * 4
+        g = g.contiguous()
+        dx1 = _node_raw(topo, 0, g, 1, w, None, 1, 1, F) if ctx.needs_input_grad[0] else None
+        dz0 = _cfconv_filter_bwd_raw(g, x1, topo, h, dist, ctx.cutoff, w1.t().contiguous())
+        gw1, gb1 = _cfconv_wgrad_raw(g, x1, topo, dist, ctx.cutoff, h)
+        gw0p, gb0 = _wgrad_raw(dz0, None, ctx.cutoff, gauss=(dist, raw, offset, ctx.coeff))
+        gw0g = gw0p[:, :G]
+        gw0r = gw0p[:, GP:GP + raw.size(1)] if raw is not None else None
+        return dx1, None, None, None, None, None, None, gw0g, gw0r, gb0, gw1, gb1
+
+
+def cfconv_fused(x1, topo, dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
+    return CFConvFused.apply(x1, topo, dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1)

@@ -170,6 +170,18 @@ int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const float* raw,
 int hgk_schnet_filter_bwd(float* dz0, const float* gw, const float* h,
                           const float* d, float cutoff, const float* w1t,
                           int64_t E, int32_t F, void* stream);
+/* hgk_schnet_filter_bwd for a filter that feeds CFConv's aggregation out[t] = sum_e x[src(e)] * w[e]
+ * (reference: autograd through SCFStack.py:285-293 and :268-272 together): the filter gradient
+ * gw[e] = g[gi[e]] * x[xi[e]] (g = gradient of the aggregate, gi = destination ids, xi = source ids) is
+ * formed inside the kernel from the two node tables and never stored. */
+int hgk_cfconv_filter_bwd(float* dz0, const float* g, int64_t ldg, const int32_t* gi, const float* x,
+                          int64_t ldx, const int32_t* xi, const float* h, const float* d, float cutoff,
+                          const float* w1t, int64_t E, int32_t F, void* stream);
+/* hgk_wgrad_tn with A[e] = g[gi[e]] * x[xi[e]] * envelope(scale_d[e]) formed on the fly and B = b [E,128]
+ * (the second filter Linear's weight / bias gradient).  Same partial layout as hgk_wgrad_tn. */
+int hgk_cfconv_wgrad(float* dw_partial, float* db_partial, const float* g, int64_t ldg, const int32_t* gi,
+                     const float* x, int64_t ldx, const int32_t* xi, const float* scale_d, float cutoff,
+                     const float* b, int64_t ldb, int64_t E, int32_t F, void* stream);
 /* Weight / bias gradients of an edge-row Linear (reference: autograd of
  * nn.Linear on [E, .] inputs):  dW[n,k] = sum_e A[e,n] B[e,k],  db[n] =
  * sum_e A[e,n].  A is [E,128] (row stride lda, so a 128-column slice of a

@@ -306,3 +306,41 @@ def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, s
 def mask_axpy(z, mask=None, scale=1.0, residual=None):
     y = z if mask is None else z * mask.to(z.dtype) * scale
     return y if residual is None else y + residual
+
+
+# ---- launcher-level restatements of hydragnn/ops/filter.py (padded-weight layout of the fused kernels) ----
+def _envelope(dist, cutoff):
+    return 0.5 * (torch.cos(dist * math.pi / cutoff) + 1.0)
+
+
+def _filter_input_padded(dist, raw, offset, coeff):
+    """[gauss(d) | pad to a multiple of 4 | raw | pad to 64]: the input layout of hgk_schnet_filter_fwd."""
+    G = offset.numel()
+    GP = (G + 3) // 4 * 4
+    x = dist.new_zeros((dist.numel(), 64))
+    x[:, :G] = torch.exp(coeff * torch.pow(dist.view(-1, 1) - offset.view(1, -1), 2))
+    if raw is not None:
+        x[:, GP:GP + raw.size(1)] = raw
+    return x
+
+
+def filter_fwd_padded(dist, raw, offset, coeff, cutoff, w0p, b0, w1, b1):
+    """hgk_schnet_filter_fwd on the padded first-layer weight w0p [F, 64] -> (w, h)."""
+    h = torch.nn.functional.softplus(_filter_input_padded(dist, raw, offset, coeff) @ w0p.t() + b0) - math.log(2.0)
+    return (h @ w1.t() + b1) * _envelope(dist, cutoff).view(-1, 1), h
+
+
+def filter_bwd(gw, h, dist, cutoff, w1t):
+    """hgk_schnet_filter_bwd: dZ0 = ((gw * envelope) W1) * sigmoid(Z0), sigmoid(z0) = 1 - exp(-(h + ln 2))."""
+    dz1 = gw * _envelope(dist, cutoff).view(-1, 1)
+    return (dz1 @ w1t.t()) * (1.0 - torch.exp(-(h + math.log(2.0))))
+
+
+def wgrad_edges(a, scale_d, cutoff, b=None, gauss=None):
+    """hgk_wgrad_tn + hgk_wgrad_reduce: (A^T B, column sums of A), A optionally scaled by the envelope,
+    B = b or the padded filter input."""
+    if scale_d is not None:
+        a = a * _envelope(scale_d, cutoff).view(-1, 1)
+    if b is None:
+        b = _filter_input_padded(*gauss)
+    return a.t() @ b, a.sum(0)

@@ -79,9 +79,41 @@ def _radius_graph(pos, ptr, r, max_num_neighbors=0, loop=False, cell=None, pbc=N
     return out
 
 
+# ---- fused SchNet filter network (hydragnn/ops/filter.py) ----
+def _filter_fwd_raw(dist, raw, offset, coeff, cutoff, w0p, b0, w1, b1):
+    return ks.filter_fwd_padded(dist, raw, offset, coeff, cutoff, w0p, b0, w1, b1)
+
+
+def _filter_bwd_raw(gw, h, dist, cutoff, w1t):
+    return ks.filter_bwd(gw, h, dist, cutoff, w1t)
+
+
+def _wgrad_raw(a, scale_d, cutoff, b=None, gauss=None):
+    return ks.wgrad_edges(a, scale_d, cutoff, b, gauss)
+
+
+def _cfconv_filter_bwd_raw(g, x1, topo, h, dist, cutoff, w1t):
+    gw = g[topo.idx[1].long()] * x1[topo.idx[0].long()]
+    return ks.filter_bwd(gw, h, dist, cutoff, w1t)
+
+
+def _cfconv_wgrad_raw(g, x1, topo, dist, cutoff, h):
+    gw = g[topo.idx[1].long()] * x1[topo.idx[0].long()]
+    return ks.wgrad_edges(gw, dist, cutoff, b=h)
+
+
+def _fused_filter_ok(dist, raw, num_filters, num_gaussians):
+    from hydragnn.ops import filter as filt
+    if dist.requires_grad or dist.dtype != torch.float32 or (raw is not None and raw.requires_grad):
+        return False
+    r = 0 if raw is None else raw.size(1)
+    return (num_filters == filt.SUPPORTED["F"] and num_gaussians == filt.SUPPORTED["G"] and r in filt.SUPPORTED["R"])
+
+
 @contextlib.contextmanager
 def cpu_kernels():
     from hydragnn.ops import attention, contract, node, pna, topo
+    from hydragnn.ops import filter as filt
     import importlib
 
     import hydragnn.ops as ops_pkg
@@ -99,6 +131,10 @@ def cpu_kernels():
         (node, "linear_tc", ks.linear_tc), (node, "wgrad_rows", ks.wgrad_rows), (node, "bn_stats", ks.bn_stats),
         (node, "bn_apply", ks.bn_apply), (node, "bn_bwd", ks.bn_bwd), (node, "mask_axpy", ks.mask_axpy),
         (node, "device_ok", lambda t: t.dtype == torch.float32),
+        (filt, "_filter_fwd_raw", _filter_fwd_raw), (filt, "_filter_bwd_raw", _filter_bwd_raw),
+        (filt, "_wgrad_raw", _wgrad_raw), (filt, "_cfconv_filter_bwd_raw", _cfconv_filter_bwd_raw),
+        (filt, "_cfconv_wgrad_raw", _cfconv_wgrad_raw), (filt, "fused_filter_ok", _fused_filter_ok),
+        (scf_mod, "fused_filter_ok", _fused_filter_ok),
         (scf_mod, "radius_graph", _radius_graph), (radius_mod, "radius_graph", _radius_graph),
     ]
     saved = [(m, n, getattr(m, n)) for m, n, _ in patches]

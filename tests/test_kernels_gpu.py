@@ -517,3 +517,32 @@ def test_colsum(ops, n, c, strided):
     assert got.shape == (c,)
     torch.testing.assert_close(got.double(), want, rtol=1e-5, atol=1e-4 * max(1.0, n ** 0.5))
     assert torch.equal(got, colsum(x))
+
+
+@pytest.mark.parametrize("N,E", [(50, 700), (8192, 474078)])
+def test_cfconv_gathered_backward_kernels(ops, N, E):
+    """hgk_cfconv_filter_bwd / hgk_cfconv_wgrad (filter gradient gW[e] = g[dst(e)] * x1[src(e)] formed
+    inside the kernel) against the two-step path they replace: hgk_contract_edge_w writes gW, then
+    hgk_schnet_filter_bwd / hgk_wgrad_tn read it.  Same arithmetic on the same values: bit-exact."""
+    from hydragnn.ops import filter as filt
+
+    gen = torch.Generator().manual_seed(N + E)
+    F, cutoff = 128, 5.0
+    ei = random_graph(gen, N, E, sorted_dst=True)
+    topo = make_topo(ops, ei, N, sorted_side=1)
+    g = torch.randn(N, F, generator=gen).to(DEV)
+    x1 = torch.randn(N, F, generator=gen).to(DEV)
+    h = torch.randn(E, F, generator=gen).to(DEV)
+    dist = (torch.rand(E, generator=gen) * 4.9 + 0.05).to(DEV)
+    w1t = (torch.randn(F, F, generator=gen) / F ** 0.5).to(DEV)
+    gw = ops["contract"]._edge_w_raw(topo, g, 1, x1, 0, None, 1, F)
+    dz0_ref = filt._filter_bwd_raw(gw, h, dist, cutoff, w1t)
+    dz0 = filt._cfconv_filter_bwd_raw(g, x1, topo, h, dist, cutoff, w1t)
+    assert torch.equal(dz0, dz0_ref)
+    gw1_ref, gb1_ref = filt._wgrad_raw(gw, dist, cutoff, b=h)
+    gw1, gb1 = filt._cfconv_wgrad_raw(g, x1, topo, dist, cutoff, h)
+    assert torch.equal(gw1, gw1_ref) and torch.equal(gb1, gb1_ref)
+    # and against plain torch on the CPU
+    gw_cpu = g.cpu()[ei[1]] * x1.cpu()[ei[0]]
+    ref = ks.filter_bwd(gw_cpu, h.cpu(), dist.cpu(), cutoff, w1t.cpu())
+    torch.testing.assert_close(dz0.cpu(), ref, rtol=1e-4, atol=1e-5)
