@@ -304,14 +304,26 @@ class Base(Module):
     def _attention_segments(self, data, num_nodes, device):
         """cu_seqlens for the GPS layers, built once per forward (with the host-side sum of
         squared segment lengths attached for the kernel's flop accounting -- no device sync)."""
+        bounds = None
         if self.gps_segments == "graph" and getattr(data, "ptr", None) is not None:
             cu = data.ptr.to(device=device, dtype=torch.int32)
             sum_sq = getattr(data, "sum_sq_nodes", None)
+            sizes = getattr(data, "graph_sizes", None)              # host copy kept by Batch.from_data_list
+            if sizes is not None:
+                bounds = [0]
+                for n in sizes:
+                    bounds.append(bounds[-1] + int(n))
+                sum_sq = sum(int(n) * int(n) for n in sizes)
+            elif not data.ptr.is_cuda:
+                bounds = [int(v) for v in data.ptr.tolist()]
         else:
             cu = _whole_batch_segment(num_nodes, device)
             sum_sq = num_nodes * num_nodes
+            bounds = [0, int(num_nodes)]
         if sum_sq is not None:
             cu._hgk_sum_sq = int(sum_sq)
+        if bounds is not None:
+            cu._hgk_bounds = bounds        # host-side segment boundaries: no sync in the differentiable backward
         return cu
 
     def forward(self, data):

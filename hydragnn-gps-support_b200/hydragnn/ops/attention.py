@@ -58,24 +58,62 @@ def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
     return dq, dk, dv
 
 
+def _segment_bounds(cu):
+    """Segment boundaries as host integers.  Callers that know them attach `_hgk_bounds` to the tensor
+    (Base._attention_segments does); otherwise this is a device -> host read."""
+    b = getattr(cu, "_hgk_bounds", None)
+    if b is None:
+        b = [int(c) for c in cu.tolist()]
+    return b
+
+
+# rows of one score block of the differentiable backward: memory is H * _DENSE_BLOCK * L floats per
+# temporary instead of H * L * L (1 GB per temporary at H = 4, L = 8192)
+_DENSE_BLOCK = 1024
+
+
+def _dense_block(do_b, q_b, ks, vs, scale):
+    """Backward terms of one block of query rows, all heads: (dq_b, dk partial, dv partial).
+    q_b, do_b: [H, B, D]; ks, vs: [H, L, D].  Needs the softmax statistics of complete rows only,
+    so a block of query rows is self-contained."""
+    p = torch.softmax((q_b @ ks.transpose(1, 2)) * scale, dim=-1)          # [H, B, L]
+    dp = do_b @ vs.transpose(1, 2)
+    ds = p * (dp - (dp * p).sum(dim=-1, keepdim=True))
+    return (ds @ ks) * scale, (ds.transpose(1, 2) @ q_b) * scale, p.transpose(1, 2) @ do_b
+
+
 def _dense_backward(do, q, k, v, cu, H, scale):
-    """(dq, dk, dv) from differentiable torch ops, segment by segment.  Only used when the backward
-    pass is itself being differentiated (create_graph=True: a force loss on a model whose attention
-    inputs depend on the positions) -- the kernels provide first derivatives only.  Reads the
-    segment boundaries on the host (one sync) and materialises the [H, L, L] score block per segment."""
+    """(dq, dk, dv) from differentiable torch ops.  Only used when the backward pass is itself being
+    differentiated (create_graph=True: a force loss on a model whose attention inputs depend on the
+    positions) -- the kernels provide first derivatives only.  Works segment by segment and, inside a
+    segment, in blocks of `_DENSE_BLOCK` query rows under activation checkpointing: the [H, B, L] score
+    blocks are recomputed when the second derivative is taken instead of being kept alive, so memory
+    stays O(H * B * L) per block rather than O(H * L^2) per layer."""
+    from torch.utils.checkpoint import checkpoint
+
     N, HD = q.shape
     D = HD // H
-    bounds = [int(c) for c in cu.tolist()]
+    bounds = _segment_bounds(cu)
     dq, dk, dv = [], [], []
     for b, e in zip(bounds[:-1], bounds[1:]):
         L = e - b
+        if L == 0:
+            continue
         qs, ks, vs, gs = (t[b:e].reshape(L, H, D).transpose(0, 1) for t in (q, k, v, do))      # [H, L, D]
-        p = torch.softmax((qs @ ks.transpose(1, 2)) * scale, dim=-1)
-        dp = gs @ vs.transpose(1, 2)
-        ds = p * (dp - (dp * p).sum(dim=-1, keepdim=True))
-        dq.append(((ds @ ks) * scale).transpose(0, 1).reshape(L, HD))
-        dk.append(((ds.transpose(1, 2) @ qs) * scale).transpose(0, 1).reshape(L, HD))
-        dv.append((p.transpose(1, 2) @ gs).transpose(0, 1).reshape(L, HD))
+        dq_s, dk_s, dv_s = [], None, None
+        for r0 in range(0, L, _DENSE_BLOCK):
+            r1 = min(L, r0 + _DENSE_BLOCK)
+            if L > _DENSE_BLOCK:
+                dq_b, dk_b, dv_b = checkpoint(_dense_block, gs[:, r0:r1], qs[:, r0:r1], ks, vs, scale,
+                                              use_reentrant=False)
+            else:
+                dq_b, dk_b, dv_b = _dense_block(gs[:, r0:r1], qs[:, r0:r1], ks, vs, scale)
+            dq_s.append(dq_b)
+            dk_s = dk_b if dk_s is None else dk_s + dk_b
+            dv_s = dv_b if dv_s is None else dv_s + dv_b
+        dq.append(torch.cat(dq_s, dim=1).transpose(0, 1).reshape(L, HD))
+        dk.append(dk_s.transpose(0, 1).reshape(L, HD))
+        dv.append(dv_s.transpose(0, 1).reshape(L, HD))
     if not dq:
         z = q * 0.0
         return z, z, z
@@ -88,12 +126,15 @@ class AttnVarlen(torch.autograd.Function):
         o, lse, q_t, k_t, v_t = _attn_fwd_raw(q, k, v, cu_seqlens, H, scale)
         ctx.save_for_backward(q, k, v, o, lse, cu_seqlens)
         ctx.H, ctx.scale = H, scale
+        ctx.bounds = getattr(cu_seqlens, "_hgk_bounds", None)     # python attributes do not survive save_for_backward
         return o
 
     @staticmethod
     def backward(ctx, do):
         q, k, v, o, lse, cu = ctx.saved_tensors
         if torch.is_grad_enabled():        # create_graph=True: stay differentiable
+            if ctx.bounds is not None:
+                cu._hgk_bounds = ctx.bounds
             dq, dk, dv = _dense_backward(do, q, k, v, cu, ctx.H, ctx.scale)
         else:
             dq, dk, dv = _attn_bwd_raw(do, o, lse, q, k, v, cu, ctx.H, ctx.scale)
