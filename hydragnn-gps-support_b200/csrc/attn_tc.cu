@@ -34,6 +34,14 @@ struct AttnTcArgs {
 
 namespace tc {
 
+// Long accumulation chains in TMEM lose precision: every tcgen05.mma adds into the fp32 accumulator
+// with truncation, so the error of a sum grows linearly with the number of MMAs behind it (measured,
+// profiles/precision_probe.py: 6e-5 of the tensor's scale after the 3072 MMAs of an 8192-key segment,
+// against 1e-6 for plain fp32).  The pipelined kernels therefore restart their output accumulators
+// every kPromote of a group's steps (48 MMAs) and add the finished partial sums to fp32 totals in
+// shared memory with ordinary (round-to-nearest) adds.
+constexpr int kPromote = 4;
+
 constexpr int BM = 128;          // rows per CTA (= TMEM lanes)
 constexpr int BN = 64;           // columns per iteration
 constexpr int HALF = BN / 2;     // columns per thread
@@ -257,7 +265,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
       fence_after_sync();
       if (elect_one_sync()) {
         mma3_ts<BK>(tmem + kColO + (uint32_t)g * D, tmem + kColS + (uint32_t)g * BK, tmem + kColPlo + (uint32_t)g * BK,
-                    at_stage(dVt, s % NST), kIdescO, s >= G);      // O_g += P_s V_s
+                    at_stage(dVt, s % NST), kIdescO, ((s / G) % kPromote) != 0);   // O_g (+)= P_s V_s
         if (s + G < nsub) issue_scores(s + G);
         mma_commit(&bar[g]);
         if (s == nsub - 1) mma_commit(&bar[G]);
@@ -299,11 +307,27 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
     const uint32_t t_s = tmem + cs.lane_base + kColS + (uint32_t)g * BK;
     const uint32_t t_plo = tmem + cs.lane_base + kColPlo + (uint32_t)g * BK;
     const uint32_t t_o = tmem + cs.lane_base + kColO + (uint32_t)g * D;
+    // fp32 totals of the finished accumulator chains of this group: [D][BM] floats behind the stages
+    float* tot = smem + NST * kStage + g * (D * BM) + cs.row_local;
     uint32_t par = 0;
     for (int s = g; s < nsub; s += G) {
       mbar_wait(&bar[g], par);                         // S_s is ready; P V of my previous step is complete
       par ^= 1;
       fence_after_sync();
+      const int ls = s / G;                            // index of this step among the group's steps
+      if (ls > 0 && ls % kPromote == 0) {              // the issuer restarts the accumulator with this step's P V
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 16) {
+          uint32_t ot[16];
+          tmem_ld16(t_o + c0, ot);
+          tmem_ld_wait();
+#pragma unroll
+          for (int d = 0; d < 16; ++d) {
+            float* slot = tot + (c0 + d) * BM;
+            *slot = ls == kPromote ? __uint_as_float(ot[d]) : *slot + __uint_as_float(ot[d]);
+          }
+        }
+      }
       uint32_t sv[BK];
       tmem_ld32(t_s, sv);
       tmem_ld_wait();
@@ -332,6 +356,10 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
 #pragma unroll
           for (int d = 0; d < 16; ++d) ot[d] = __float_as_uint(__uint_as_float(ot[d]) * f);
           tmem_st16(t_o + c0, ot);
+        }
+        if (ls >= kPromote) {                          // the totals follow the reference maximum
+#pragma unroll
+          for (int d = 0; d < D; ++d) tot[d * BM] *= f;
         }
       }
       float rs4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -366,8 +394,9 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
       uint32_t ot[D];
       tmem_ld32(t_o, ot);
       tmem_ld_wait();
+      const bool promoted = (nsub - g + G - 1) / G > kPromote;     // the group had more than kPromote steps
 #pragma unroll
-      for (int d = 0; d < D; ++d) acc[d] = __uint_as_float(ot[d]);
+      for (int d = 0; d < D; ++d) acc[d] = __uint_as_float(ot[d]) + (promoted ? tot[d * BM] : 0.f);
     } else {
 #pragma unroll
       for (int d = 0; d < D; ++d) acc[d] = 0.f;
@@ -756,9 +785,12 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   constexpr int oGThi = 6 * kTile, oGTlo = 7 * kTile;  // dO^T [D x BQ]  (B of dV)
 
   constexpr uint32_t kCols = 512;
-  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColDV = 256, kColDK = 256 + D;
-  constexpr uint32_t kColKhi = 256 + 2 * D, kColKlo = 256 + 3 * D, kColVhi = 256 + 4 * D, kColVlo = 256 + 5 * D;
-  static_assert(256 + 6 * D <= 512, "TMEM budget");
+  // one (dV, dK) accumulator pair per compute group: columns kColAcc + g * 2D (dV) and + D (dK); a group's
+  // chain of updates is ordered by its own hand-offs, so the group can move it into the fp32 totals
+  // every kPromote steps without stalling the other group
+  constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColAcc = 256;
+  constexpr uint32_t kColKhi = 256 + 4 * D, kColKlo = 256 + 5 * D, kColVhi = 256 + 6 * D, kColVlo = 256 + 7 * D;
+  static_assert(256 + 8 * D <= 512, "TMEM budget");
   if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }   // bar[0]: cta_setup, which also publishes all three
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
@@ -781,8 +813,10 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     };
     auto issue_updates = [&](int s) {                  // dV += P^T dO, dK += dS^T Q of step s
       const uint32_t set = (uint32_t)(s & 1) * BQ;
-      mma3_ts<BQ>(tmem + kColDV, tmem + kColST + set, tmem + kColPlo + set, at_stage(dGt, s & (NST - 1)), kIdescD, s > 0);
-      mma3_ts<BQ>(tmem + kColDK, tmem + kColDPT + set, tmem + kColDSlo + set, at_stage(dQt, s & (NST - 1)), kIdescD, s > 0);
+      const bool accumulate = ((s >> 1) % kPromote) != 0;
+      const uint32_t acc = tmem + kColAcc + (uint32_t)(s & 1) * 2 * D;
+      mma3_ts<BQ>(acc, tmem + kColST + set, tmem + kColPlo + set, at_stage(dGt, s & (NST - 1)), kIdescD, accumulate);
+      mma3_ts<BQ>(acc + D, tmem + kColDPT + set, tmem + kColDSlo + set, at_stage(dQt, s & (NST - 1)), kIdescD, accumulate);
     };
     named_bar_sync(1, kKvPipeThreads);                 // K / V rows are in TMEM, stages 0 and 1 are written
     fence_after_sync();
@@ -858,6 +892,9 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     named_bar_arrive(1, kKvPipeThreads);
     if (g + 2 < nsub) load(seg_beg + (g + 2) * BQ);    // after the fence: it would wait for these loads
 
+    // fp32 totals of the group's finished accumulator chains: [2 groups][dV | dK][D][BM] floats behind the
+    // stages; this thread takes dV (ch == 0) or dK (ch == 1) of its group, all D columns of its row
+    float* tot = smem + NST * kStage + (g * 2 + ch) * (D * BM) + cs.row_local;
     uint32_t par = 0;
     KV_PROF_DECL
     for (int s = g; s < nsub; s += 2) {
@@ -866,6 +903,20 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       par ^= 1;
       fence_after_sync();
       KV_PROF(0)
+      const int ls = s >> 1;                           // index of this step among the group's steps
+      if (ls > 0 && ls % kPromote == 0) {              // the issuer restarts the group's dV / dK with this step
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 16) {
+          uint32_t va[16];
+          tmem_ld16(tmem + cs.lane_base + kColAcc + (uint32_t)g * 2 * D + (uint32_t)ch * D + c0, va);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float* slot = tot + (c0 + j) * BM;
+            *slot = ls == kPromote ? __uint_as_float(va[j]) : *slot + __uint_as_float(va[j]);
+          }
+        }
+      }
 
       const int st = s & (NST - 1);
       const int col0 = ch * QC;
@@ -908,23 +959,34 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     fence_after_sync();
     KV_PROF_FLUSH
 
+    named_bar_sync(9, kKvThreads);                     // both groups' totals are in shared memory
     static_assert(D == 32, "epilogue column split");
     constexpr int EC = D / 2;                          // columns per thread
     const int32_t krow = key0 + cs.row_local;
     const bool ok = krow < seg_end;
     const bool is_k = part >= 2;
     const int chalf = part & 1;
-    uint32_t t[16];
-    tmem_ld16(tmem + cs.lane_base + (is_k ? kColDK : kColDV) + chalf * EC, t);
-    tmem_ld_wait();
+    // dv / dk = sum over the groups of (last accumulator chain in TMEM + fp32 totals of the earlier ones)
+    float accv[EC];
+#pragma unroll
+    for (int j = 0; j < EC; ++j) accv[j] = 0.f;
+#pragma unroll
+    for (int gg = 0; gg < 2; ++gg) {
+      const int steps = gg < nsub ? (nsub - gg + 1) / 2 : 0;       // steps of group gg (CTA uniform)
+      if (steps == 0) continue;                        // its accumulators were never written
+      uint32_t t[16];
+      tmem_ld16(tmem + cs.lane_base + kColAcc + (uint32_t)gg * 2 * D + (is_k ? D : 0) + chalf * EC, t);
+      tmem_ld_wait();
+      const float* tg = smem + NST * kStage + (gg * 2 + (is_k ? 1 : 0)) * (D * BM) + (chalf * EC) * BM + cs.row_local;
+#pragma unroll
+      for (int j = 0; j < EC; ++j) accv[j] += __uint_as_float(t[j]) + (steps > kPromote ? tg[j * BM] : 0.f);
+    }
     if (ok) {
       const float mul = is_k ? kLn2 : 1.f;             // Q was staged as q * scale * log2(e)
       float* orow = (is_k ? dk : dv) + ((int64_t)krow * p.H + h) * D + chalf * EC;
 #pragma unroll
       for (int j = 0; j < EC; j += 4)
-        *reinterpret_cast<float4*>(orow + j) =
-            make_float4(__uint_as_float(t[j]) * mul, __uint_as_float(t[j + 1]) * mul,
-                        __uint_as_float(t[j + 2]) * mul, __uint_as_float(t[j + 3]) * mul);
+        *reinterpret_cast<float4*>(orow + j) = make_float4(accv[j] * mul, accv[j + 1] * mul, accv[j + 2] * mul, accv[j + 3] * mul);
     }
   }
   cta_teardown(tmem, kCols);
@@ -955,9 +1017,11 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr int oKThi = 4 * kTile, oKTlo = 5 * kTile;  // K^T [D x BK]   (B of dQ)
 
   constexpr uint32_t kCols = 512;
+  // one dQ accumulator per compute group (columns kColDQ + g * D): a group's chain of updates is then
+  // ordered by its own hand-offs, and the group can move it into the fp32 totals every kPromote steps
   constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;
-  constexpr uint32_t kColQhi = 128 + D, kColQlo = 128 + 2 * D, kColGhi = 128 + 3 * D, kColGlo = 128 + 4 * D;
-  static_assert(128 + 5 * D <= 512, "TMEM budget");
+  constexpr uint32_t kColQhi = 128 + 2 * D, kColQlo = 128 + 3 * D, kColGhi = 128 + 4 * D, kColGlo = 128 + 5 * D;
+  static_assert(128 + 6 * D <= 512, "TMEM budget");
   if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
@@ -991,7 +1055,8 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       fence_after_sync();
       if (elect_one_sync()) {
         const uint32_t set = (uint32_t)g * BK;
-        mma3_ts<BK>(tmem + kColDQ, tmem + kColS + set, tmem + kColDP + set, at_stage(dKt, s & (NST - 1)), kIdescQ, s > 0);
+        mma3_ts<BK>(tmem + kColDQ + (uint32_t)g * D, tmem + kColS + set, tmem + kColDP + set,
+                    at_stage(dKt, s & (NST - 1)), kIdescQ, ((s >> 1) % kPromote) != 0);
         if (s + 2 < nsub) issue_scores(s + 2);
         mma_commit(&bar[g]);
         if (s == nsub - 1) mma_commit(&bar[2]);
@@ -1035,11 +1100,23 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     named_bar_arrive(1, kKvPipeThreads);
     if (g + 2 < nsub) load(seg_beg + (g + 2) * BK);
 
+    // fp32 totals of the group's finished accumulator chains: [2][D][BM] floats behind the stages;
+    // this thread's 16 of the group's 32 columns
+    float* tot = smem + NST * kStage + g * (D * BM) + (ch * KC) * BM + cs.row_local;
     uint32_t par = 0;
     for (int s = g; s < nsub; s += 2) {
       mbar_wait(&bar[g], par);
       par ^= 1;
       fence_after_sync();
+      const int ls = s >> 1;                           // index of this step among the group's steps
+      if (ls > 0 && ls % kPromote == 0) {              // the issuer restarts dQ_g with this step's update
+        uint32_t qa[KC];
+        tmem_ld16(tmem + cs.lane_base + kColDQ + (uint32_t)g * D + ch * KC, qa);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < KC; ++j)
+          tot[j * BM] = ls == kPromote ? __uint_as_float(qa[j]) : tot[j * BM] + __uint_as_float(qa[j]);
+      }
 
       const int col0 = ch * KC;
       const uint32_t set = (uint32_t)g * BK;
@@ -1071,18 +1148,29 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     mbar_wait(&bar[2], 0);
     fence_after_sync();
 
-    // four threads per row: D/4 columns each.  tcgen05.ld is warp-collective: everyone loads
+    named_bar_sync(9, kKvThreads);                     // both groups' totals are in shared memory
+    // four threads per row: D/4 columns each.  tcgen05.ld is warp-collective: everyone loads.
+    // dq = sum over the groups of (last accumulator chain in TMEM + fp32 totals of the earlier ones)
     constexpr int EC = D / 4;
     static_assert(EC == 8, "epilogue column split");
-    uint32_t t[8];
-    tmem_ld8(tmem + cs.lane_base + kColDQ + part * EC, t);
-    tmem_ld_wait();
+    float acc[EC];
+#pragma unroll
+    for (int j = 0; j < EC; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int gg = 0; gg < 2; ++gg) {
+      const int steps = gg < nsub ? (nsub - gg + 1) / 2 : 0;       // steps of group gg (CTA uniform)
+      if (steps == 0) continue;                        // its accumulator was never written
+      uint32_t t[EC];
+      tmem_ld8(tmem + cs.lane_base + kColDQ + (uint32_t)gg * D + part * EC, t);
+      tmem_ld_wait();
+      const float* tg = smem + NST * kStage + gg * (D * BM) + (part * EC) * BM + cs.row_local;
+#pragma unroll
+      for (int j = 0; j < EC; ++j) acc[j] += __uint_as_float(t[j]) + (steps > kPromote ? tg[j * BM] : 0.f);
+    }
     if (row_ok) {
       float* drow = dq + ((int64_t)row * p.H + h) * D + part * EC;
-      *reinterpret_cast<float4*>(drow) = make_float4(__uint_as_float(t[0]) * p.scale, __uint_as_float(t[1]) * p.scale,
-                                                     __uint_as_float(t[2]) * p.scale, __uint_as_float(t[3]) * p.scale);
-      *reinterpret_cast<float4*>(drow + 4) = make_float4(__uint_as_float(t[4]) * p.scale, __uint_as_float(t[5]) * p.scale,
-                                                         __uint_as_float(t[6]) * p.scale, __uint_as_float(t[7]) * p.scale);
+      *reinterpret_cast<float4*>(drow) = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
+      *reinterpret_cast<float4*>(drow + 4) = make_float4(acc[4] * p.scale, acc[5] * p.scale, acc[6] * p.scale, acc[7] * p.scale);
     }
   }
   cta_teardown(tmem, kCols);
@@ -1112,8 +1200,8 @@ int opt_in_smem(K kernel, size_t bytes, const char* what) {
 
 template <int D>
 int launch_fwd_pipe(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
-  // one CTA per SM (512 TMEM columns): 8 operand stages of 16 KB
-  size_t smem = sizeof(float) * (2 * kFwdGroups * 4 * 32 * D);
+  // one CTA per SM (512 TMEM columns): 8 operand stages of 16 KB + the groups' fp32 totals [G][D][128]
+  size_t smem = sizeof(float) * (2 * kFwdGroups * 4 * 32 * D + kFwdGroups * D * BM);
   if (smem < 120 * 1024) smem = 120 * 1024;
   int rc = opt_in_smem(k_attn_fwd_pipe<D>, smem, "attn_fwd_pipe");
   if (rc) return rc;
@@ -1139,7 +1227,7 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
                cudaStream_t st) {
   dim3 grid((unsigned)(ceil_div(N, BM) + a.S), (unsigned)a.H);
   // 512 TMEM columns: one CTA per SM; ask for more than half of the shared memory to enforce it
-  size_t smem_kv = sizeof(float) * (2 * 8 * BN * D);
+  size_t smem_kv = sizeof(float) * (2 * 8 * BN * D + 4 * D * BM);      // 4 stages + the groups' fp32 totals
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;
   // HGK_ATTN_BWD_SERIAL=1 selects the unpipelined backward kernels (A/B runs); read once
   static const bool serial = [] { const char* e = getenv("HGK_ATTN_BWD_SERIAL"); return e && e[0] == '1'; }();
@@ -1161,7 +1249,7 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
   } else {
     // 512 TMEM columns: one CTA per SM, enforced through the shared-memory request as well
-    size_t smem_q = sizeof(float) * (4 * 6 * 32 * D);
+    size_t smem_q = sizeof(float) * (4 * 6 * 32 * D + 2 * D * BM);     // 4 stages + the groups' fp32 totals
     if (smem_q < 120 * 1024) smem_q = 120 * 1024;
     rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
     if (rc) return rc;

@@ -395,10 +395,33 @@ k_wgrad_tn(const WgradArgs p) {
   // for its global loads or its MMAs, the other transposes its tile.
   float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
   float* BThi = ATlo + kFilt * BE;   float* BTlo = BThi + KB * BE;
-  constexpr uint32_t kCols = KB < 32 ? 32 : KB;
+  // Columns [0, KB): the running accumulator of the tensor cores; [KB, 2 KB): fp32 totals.  A tcgen05
+  // accumulation chain loses ~2^-24 of the sum per MMA (truncating adds; profiles/precision_probe.py),
+  // so every kWgradPromote iterations (48 MMAs) the accumulator is added to the totals by the CUDA cores
+  // (round-to-nearest) and restarted.
+  constexpr int kWgradPromote = 4;
+  constexpr uint32_t kCols = 2 * KB;
+  constexpr uint32_t kColTot = KB;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
+  // this thread's KB / 2 columns of the accumulator -> totals (first time: the totals are undefined)
+  auto promote = [&](bool first_time) {
+#pragma unroll
+    for (int c0 = 0; c0 < KB / 2; c0 += 16) {
+      const uint32_t col = cs.lane_base + cs.half * (KB / 2) + c0;
+      uint32_t a16[16], t16[16];
+      tmem_ld16(tmem + col, a16);
+      if (!first_time) tmem_ld16(tmem + kColTot + col, t16);
+      tmem_ld_wait();
+      if (!first_time) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) a16[j] = __float_as_uint(__uint_as_float(a16[j]) + __uint_as_float(t16[j]));
+      }
+      tmem_st16(tmem + kColTot + col, a16);
+    }
+    tmem_st_wait();
+  };
   if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
   __syncthreads();
 
@@ -493,21 +516,30 @@ k_wgrad_tn(const WgradArgs p) {
   const int64_t num_tiles = (p.E + BE - 1) / BE;
   const int64_t stride = gridDim.x;
   uint32_t parity = 0;
-  bool first = true;
+  int in_chain = 0;            // iterations accumulated since the accumulator was last restarted
+  int promotions = 0;
   if ((int64_t)blockIdx.x < num_tiles) fetch(blockIdx.x);
   for (int64_t tile = blockIdx.x; tile < num_tiles; tile += stride) {
     stage();
-    publish_operands();
+    publish_operands();        // also orders the promotion's TMEM reads before the restarting MMA
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<BE>(tmem, dA, dB, kIdesc, !first);
+      mma3_ss<BE>(tmem, dA, dB, kIdesc, in_chain > 0);
       mma_commit(&bar);
     }
-    first = false;
     if (tile + stride < num_tiles) fetch(tile + stride);       // in flight during the MMAs
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
+    if (++in_chain == kWgradPromote) {
+      promote(promotions == 0);
+      ++promotions;
+      in_chain = 0;
+    }
+  }
+  if (in_chain > 0) {          // the unfinished chain
+    promote(promotions == 0);
+    ++promotions;
   }
 
   // ---- partial dW: lane n, this thread's KB/2 columns ----
@@ -516,7 +548,7 @@ k_wgrad_tn(const WgradArgs p) {
 #pragma unroll
   for (int c0 = 0; c0 < KB / 2; c0 += 32) {
     uint32_t t[32];
-    tmem_ld32(tmem + cs.lane_base + cs.half * (KB / 2) + c0, t);
+    tmem_ld32(tmem + kColTot + cs.lane_base + cs.half * (KB / 2) + c0, t);
     tmem_ld_wait();
 #pragma unroll
     for (int j = 0; j < 32; j += 4)

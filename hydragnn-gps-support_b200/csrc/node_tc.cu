@@ -32,6 +32,10 @@ struct LinearArgs {
   int relu;
   float* y; int64_t ldy;             // [M, N]
   int64_t M; int N; int K;
+  // K is cut into `chunks` pieces of `chunk_k` (a multiple of 32), each accumulated in its own 128
+  // TMEM columns and added up in fp32 registers at the end: a tcgen05 accumulation chain loses
+  // ~2^-24 of the sum per MMA (truncating adds), so chains are kept to 128 k (48 MMAs)
+  int chunk_k; int chunks; uint32_t tmem_cols;
 };
 
 constexpr int kBK = 32;
@@ -44,7 +48,7 @@ k_linear_tc(const LinearArgs p) {
   __shared__ uint32_t tmem_slot;
   float* Ahi = smem;              float* Alo = Ahi + 128 * kBK;
   float* Bhi = Alo + 128 * kBK;   float* Blo = Bhi + 128 * kBK;
-  constexpr uint32_t kCols = 128;
+  const uint32_t kCols = p.tmem_cols;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
@@ -76,7 +80,8 @@ k_linear_tc(const LinearArgs p) {
     publish_operands();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<kBK>(tmem, dA, dB, kIdesc, k0 > 0);
+      const int chunk = k0 / p.chunk_k;
+      mma3_ss<kBK>(tmem + (uint32_t)chunk * 128, dA, dB, kIdesc, k0 > chunk * p.chunk_k);
       mma_commit(&bar);
     }
     if (k0 + kBK < p.K) fetch(k0 + kBK);        // in flight during the MMAs
@@ -91,14 +96,16 @@ k_linear_tc(const LinearArgs p) {
 #pragma unroll
   for (int cc = 0; cc < 64; cc += 32) {
     const int c_tile = cs.half * 64 + cc;               // column inside the tile
-    uint32_t t[32];
-    tmem_ld32(tmem + cs.lane_base + c_tile, t);
-    tmem_ld_wait();
+    float v[32];
+    for (int chunk = 0; chunk < p.chunks; ++chunk) {    // CTA uniform: tcgen05.ld is warp collective
+      uint32_t t[32];
+      tmem_ld32(tmem + cs.lane_base + (uint32_t)chunk * 128 + c_tile, t);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = chunk == 0 ? __uint_as_float(t[j]) : v[j] + __uint_as_float(t[j]);
+    }
     const int col = col0 + c_tile;
     if (row_ok && col < p.N) {                          // N is a multiple of 32: whole chunk in or out
-      float v[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(t[j]);
       if (p.bias != nullptr) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
@@ -158,7 +165,7 @@ k_linear_tc(const LinearArgs p) {
 // then the sum of squared deviations from that mean), the slabs are merged in slab order with the
 // pairwise update of Chan et al.  Numerically this is the two-pass algorithm inside a slab and a
 // stable merge across slabs; the order is fixed by (N, C) alone.
-constexpr int kBnSlabRows = 128;
+constexpr int kBnSlabRows = 256;
 
 __global__ void __launch_bounds__(256)
 k_bn_stats_partial(float* __restrict__ part_mean, float* __restrict__ part_m2, const float* __restrict__ t,
@@ -209,15 +216,27 @@ k_bn_stats_final(float* __restrict__ mean_out, float* __restrict__ rstd_out, flo
   if (c == 0 && num_batches != nullptr) *num_batches += 1;
   if (c >= C) return;
   float n_a = 0.f, mean = 0.f, m2 = 0.f;
-  for (int s = 0; s < S; ++s) {
-    const int64_t beg = (int64_t)s * kBnSlabRows;
-    const float n_b = (float)((beg + kBnSlabRows < N ? beg + kBnSlabRows : N) - beg);
-    const float mean_b = part_mean[(int64_t)s * C + c], m2_b = part_m2[(int64_t)s * C + c];
-    const float n = n_a + n_b;
-    const float delta = mean_b - mean;
-    mean += delta * (n_b / n);
-    m2 += m2_b + delta * delta * (n_a * n_b / n);
-    n_a = n;
+  for (int s0 = 0; s0 < S; s0 += 8) {                   // the slabs' statistics are fetched eight at a time
+    float mb[8], qb[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const bool in = s0 + j < S;
+      mb[j] = in ? __ldg(part_mean + (int64_t)(s0 + j) * C + c) : 0.f;
+      qb[j] = in ? __ldg(part_m2 + (int64_t)(s0 + j) * C + c) : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int s = s0 + j;
+      if (s < S) {
+        const int64_t beg = (int64_t)s * kBnSlabRows;
+        const float n_b = (float)((beg + kBnSlabRows < N ? beg + kBnSlabRows : N) - beg);
+        const float n = n_a + n_b;
+        const float delta = mb[j] - mean;
+        mean += delta * (n_b / n);
+        m2 += qb[j] + delta * delta * (n_a * n_b / n);
+        n_a = n;
+      }
+    }
   }
   const float var = m2 / (float)N;                      // biased: what normalises the batch
   mean_out[c] = mean;
@@ -302,7 +321,8 @@ k_bn_bwd_final(float* __restrict__ sums, float* __restrict__ dgamma_a, float* __
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     float t = 0.f;
-    for (int s = 0; s < S; ++s) t += partial[((int64_t)k * S + s) * C + c];
+#pragma unroll 8
+    for (int s = 0; s < S; ++s) t += __ldg(partial + ((int64_t)k * S + s) * C + c);
     acc[k] = t;
     sums[(int64_t)k * C + c] = t;
   }
@@ -403,13 +423,23 @@ extern "C" int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
   HGK_REQUIRE(!mask || aligned16(mask), "linear_tc: mask must be 16-byte aligned");
   HGK_REQUIRE(!nz || (ldnz % 4 == 0 && ldnz >= N && aligned16(nz)), "linear_tc: nz rows must be 16-byte aligned");
   HGK_REQUIRE(!residual || (ldr % 4 == 0 && ldr >= N && aligned16(residual)), "linear_tc: residual rows must be 16-byte aligned");
-  tc::LinearArgs a{x, ldx, w, ldw, bias, mask, nz, ldnz, residual, ldr, scale, relu, y, ldy, M, N, K};
-  const size_t smem = sizeof(float) * 4 * 128 * tc::kBK;        // 64 KB
+  // accumulation chains of at most 128 k while four accumulators suffice (K <= 512), longer beyond
+  int chunks = (int)ceil_div(K, 128);
+  if (chunks > 4) chunks = 4;
+  const int chunk_k = (int)(ceil_div(ceil_div(K, chunks), tc::kBK) * tc::kBK);
+  chunks = (int)ceil_div(K, chunk_k);
+  const uint32_t tmem_cols = chunks == 1 ? 128u : (chunks == 2 ? 256u : 512u);
+  tc::LinearArgs a{x, ldx, w, ldw, bias, mask, nz, ldnz, residual, ldr, scale, relu, y, ldy, M, N, K,
+                   chunk_k, chunks, tmem_cols};
+  // 64 KB of operand tiles; with 512 TMEM columns only one CTA fits an SM, which the shared-memory
+  // request then says as well (a second resident CTA would only spin in tcgen05.alloc)
+  const size_t smem_max = 120 * 1024;
+  const size_t smem = tmem_cols == 512 ? smem_max : sizeof(float) * 4 * 128 * tc::kBK;
   static bool configured[2] = {false, false};                   // the attribute is per function, set once
   cudaError_t err = cudaSuccess;
   if (!configured[trans_w ? 1 : 0]) {
-    err = trans_w ? cudaFuncSetAttribute(tc::k_linear_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                  : cudaFuncSetAttribute(tc::k_linear_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    err = trans_w ? cudaFuncSetAttribute(tc::k_linear_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max)
+                  : cudaFuncSetAttribute(tc::k_linear_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "linear_tc: smem opt-in: %s", cudaGetErrorString(err));
     configured[trans_w ? 1 : 0] = true;
   }
@@ -438,7 +468,7 @@ extern "C" int hgk_bn_stats(float* mean, float* rstd, float* running_mean, float
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((unsigned)ceil_div(C, 32), (unsigned)S);
   k_bn_stats_partial<<<grid, 256, 0, st>>>(partial, partial + (int64_t)S * C, t, ldt, N, C);
-  k_bn_stats_final<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(mean, rstd, running_mean, running_var,
+  k_bn_stats_final<<<(unsigned)ceil_div(C, 32), 32, 0, st>>>(mean, rstd, running_mean, running_var,
                                                                (long long*)num_batches_tracked, momentum, eps, partial,
                                                                partial + (int64_t)S * C, S, N, C);
   return check_launch("bn_stats");
@@ -479,7 +509,7 @@ extern "C" int hgk_bn_bwd(float* dta, float* dza, const uint8_t* mask_a, float s
   float* sums = workspace + 3 * (int64_t)S * C;     // [3, C]
   dim3 grid((unsigned)ceil_div(C, 32), (unsigned)S);
   k_bn_bwd_partial<<<grid, 256, 0, st>>>(partial, g, ldg, a, b, N, C, S);
-  k_bn_bwd_final<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(sums, dgamma_a, dbeta_a, tb ? dgamma_b : nullptr,
+  k_bn_bwd_final<<<(unsigned)ceil_div(C, 32), 32, 0, st>>>(sums, dgamma_a, dbeta_a, tb ? dgamma_b : nullptr,
                                                              tb ? dbeta_b : nullptr, partial, S, C);
   const BnBwdOut oa{dta, dza, mask_a, scale_a}, ob{dtb, dzb, mask_b, scale_b};
   const int64_t total = N * (C / 4);

@@ -144,14 +144,23 @@ def _cfconv_wgrad_raw(g, x1, topo, dist, cutoff, h):
     return gw, gb
 
 
+# HYDRAGNN_CFCONV_GATHER=1: form the filter gradient inside the dZ0 / dW1 kernels instead of materialising it
+import os as _os
+GATHER_IN_KERNEL = _os.environ.get("HYDRAGNN_CFCONV_GATHER", "0") == "1"
+
+
 class CFConvFused(torch.autograd.Function):
     """out[t] = sum_{e: dst(e) = t} x1[src(e)] * W_e with W = filter network(d, raw) * envelope
     (reference SCFStack.py:268-293: the `nn` Sequential, the cosine cutoff and PyG's propagate) as ONE
-    autograd node.  Forward: the fused filter kernel, then the CSR aggregation.  Backward: the filter
-    gradient gW[e] = g[dst(e)] * x1[src(e)] is never written to memory -- the dZ0 kernel and the dW1
-    kernel both form it from the two node tables (4 MB each, L2-resident) while they stage their
-    operands, which removes one [E, F] write and two [E, F] reads per layer and the kernel that
-    produced it.  First derivatives only (same condition as `schnet_filter`)."""
+    autograd node (one python-level backward instead of five).  Forward: the fused filter kernel, then
+    the CSR aggregation.  Backward, two variants of the filter gradient gW[e] = g[dst(e)] * x1[src(e)]:
+      * default: hgk_contract_edge_w writes it once, the dZ0 and dW1 kernels stream it;
+      * GATHER_IN_KERNEL: never written -- hgk_cfconv_filter_bwd / hgk_cfconv_wgrad form it from the
+        two node tables (4 MB each, L2-resident) while they stage their operands: one [E, F] write and
+        two [E, F] reads less per layer (730 MB at config 5), but measured SLOWER on B200 (dZ0 0.21 ->
+        0.26 ms, dW1 0.15 -> 0.23 ms per layer at E = 474k): the two dependent gathers per row sit on
+        the staging path that already limits those kernels (LSU, not HBM).
+    First derivatives only (same condition as `schnet_filter`)."""
 
     @staticmethod
     def forward(ctx, x1, topo, dist, raw, offset, coeff, cutoff, w0g, w0r, b0, w1, b1):
@@ -184,8 +193,14 @@ class CFConvFused(torch.autograd.Function):
         GP = (G + 3) // 4 * 4
         g = g.contiguous()
         dx1 = _node_raw(topo, 0, g, 1, w, None, 1, 1, F) if ctx.needs_input_grad[0] else None
-        dz0 = _cfconv_filter_bwd_raw(g, x1, topo, h, dist, ctx.cutoff, w1.t().contiguous())
-        gw1, gb1 = _cfconv_wgrad_raw(g, x1, topo, dist, ctx.cutoff, h)
+        if GATHER_IN_KERNEL:
+            dz0 = _cfconv_filter_bwd_raw(g, x1, topo, h, dist, ctx.cutoff, w1.t().contiguous())
+            gw1, gb1 = _cfconv_wgrad_raw(g, x1, topo, dist, ctx.cutoff, h)
+        else:
+            from .contract import _edge_w_raw
+            gw = _edge_w_raw(topo, g, 1, x1, 0, None, 1, F)
+            dz0 = _filter_bwd_raw(gw, h, dist, ctx.cutoff, w1.t().contiguous())
+            gw1, gb1 = _wgrad_raw(gw, dist, ctx.cutoff, b=h)
         gw0p, gb0 = _wgrad_raw(dz0, None, ctx.cutoff, gauss=(dist, raw, offset, ctx.coeff))
         gw0g = gw0p[:, :G]
         gw0r = gw0p[:, GP:GP + raw.size(1)] if raw is not None else None

@@ -241,7 +241,7 @@ int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
  *   mean[c], rstd[c] = 1 / sqrt(biased var + eps); when running_mean /
  *   running_var are given they are updated in place with `momentum` (unbiased
  *   variance), and *num_batches_tracked (int64, may be NULL) is incremented --
- *   nn.BatchNorm1d in training.  Slabs of 128 rows are reduced with the
+ *   nn.BatchNorm1d in training.  Slabs of 256 rows are reduced with the
  *   two-pass formula and merged in slab order (Chan et al.): fixed order.
  *   partial: scratch of 2 * hgk_bn_slabs(N) * C floats. */
 int64_t hgk_bn_slabs(int64_t N);
