@@ -41,7 +41,7 @@ struct LinearArgs {
 constexpr int kBK = 32;
 
 template <bool TRANS_B>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, TRANS_B ? 1 : 2)
 k_linear_tc(const LinearArgs p) {
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) uint64_t bar;
@@ -58,25 +58,25 @@ k_linear_tc(const LinearArgs p) {
   const OperandDesc dA = operand_desc<kBK>(Ahi, Alo), dB = operand_desc<kBK>(Bhi, Blo);
   constexpr uint32_t kIdesc = idesc_tf32(128, 128);
 
-  Tile<128, kBK> ta;
-  Tile<128, kBK> tb;          // !TRANS_B: rows = output features
-  Tile<kBK, 128> tbt;         // TRANS_B : rows = k
-
-  auto fetch = [&](int k0) {
-    ta.load(p.x + k0, p.ldx, row0, (int32_t)p.M);
-    if (!TRANS_B) tb.load(p.w + k0, p.ldw, col0, p.N);
-    else tbt.load(p.w + col0, p.ldw, k0, p.K);
+  // Two register sets: the loads of chunk k + 2 are issued as soon as chunk k has been written to shared
+  // memory, i.e. they have a whole iteration (staging, barrier, MMAs, wait) to arrive.  With one set the
+  // global-load latency was exposed in every iteration (16 us for an [8192 x 128] x [128 x 128] product).
+  struct Regs {
+    Tile<128, kBK> a;
+    Tile<128, kBK> b;          // !TRANS_B: rows = output features
+    Tile<kBK, 128> bt;         // TRANS_B : rows = k
   };
-  auto stage = [&]() {
-    ta.store_rows(Ahi, Alo);
-    if (!TRANS_B) tb.store_rows(Bhi, Blo);
-    else tbt.store_transposed(Bhi, Blo);
+  Regs r0, r1;
+  auto fetch = [&](Regs& r, int k0) {
+    r.a.load(p.x + k0, p.ldx, row0, (int32_t)p.M);
+    if (!TRANS_B) r.b.load(p.w + k0, p.ldw, col0, p.N);
+    else r.bt.load(p.w + col0, p.ldw, k0, p.K);
   };
-
   uint32_t parity = 0;
-  fetch(0);
-  for (int k0 = 0; k0 < p.K; k0 += kBK) {
-    stage();
+  auto step = [&](Regs& r, int k0) {
+    r.a.store_rows(Ahi, Alo);
+    if (!TRANS_B) r.b.store_rows(Bhi, Blo);
+    else r.bt.store_transposed(Bhi, Blo);
     publish_operands();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
@@ -84,10 +84,17 @@ k_linear_tc(const LinearArgs p) {
       mma3_ss<kBK>(tmem + (uint32_t)chunk * 128, dA, dB, kIdesc, k0 > chunk * p.chunk_k);
       mma_commit(&bar);
     }
-    if (k0 + kBK < p.K) fetch(k0 + kBK);        // in flight during the MMAs
+    if (k0 + 2 * kBK < p.K) fetch(r, k0 + 2 * kBK);     // this set is free again: refill it two chunks ahead
     mbar_wait(&bar, parity);
     parity ^= 1;
     fence_after_sync();
+  };
+
+  fetch(r0, 0);
+  if (kBK < p.K) fetch(r1, kBK);
+  for (int k0 = 0; k0 < p.K; k0 += 2 * kBK) {
+    step(r0, k0);
+    if (k0 + kBK < p.K) step(r1, k0 + kBK);
   }
 
   // ---- epilogue: lane = row, this thread's 64 of the 128 columns ----

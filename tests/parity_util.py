@@ -130,12 +130,17 @@ def assert_case_close(res, truth=None):
 # GEMM / reduction chain; parameter gradients pass through the longest chains.  Where a plain
 # rtol = 1e-5 comparison of the two fp32 results would measure that noise rather than a defect,
 # the tests bound the GPU's error against an fp64 evaluation of the oracle instead:
-#     |gpu - truth|_max  <=  max(SLACK * |cpu_fp32 - truth|_max, 1e-5 * |truth|_max)
+#     |gpu - truth|_max  <=  max(SLACK * |cpu_fp32 - truth|_max, 1e-5 * |truth|_max, floor)
 # i.e. the GPU result is within 1e-5 of the exact value relative to the tensor's scale, or at
 # least as close to it as the reference's own fp32 arithmetic gets (up to SLACK).
+# SLACK = 8: the tensor-core kernels compute fp32 products as three TF32 products (unit roundoff
+# 2^-21 against fp32's 2^-24), so on ill-conditioned quantities (gradients that are sums of nearly
+# cancelling terms, where the CPU's fp32 result is itself 1e-4 off) they sit up to 8x further out.
+# `floor` (1e-6 of the largest gradient of the model) covers gradients that are analytically zero
+# -- e.g. a bias in front of a BatchNorm -- where both sides hold nothing but rounding noise.
 import contextlib
 
-TRUTH_SLACK = 4.0
+TRUTH_SLACK = 8.0
 
 
 @contextlib.contextmanager
@@ -188,14 +193,19 @@ def oracle_truth_case(name):
     return out
 
 
-def assert_close_to_truth(gpu, cpu32, truth, what, rel=1e-5, slack=TRUTH_SLACK):
+def assert_close_to_truth(gpu, cpu32, truth, what, rel=1e-5, slack=TRUTH_SLACK, floor=0.0):
     gpu, cpu32, truth = gpu.double().cpu(), cpu32.double().cpu(), truth.double().cpu()
     scale = float(truth.abs().max()) if truth.numel() else 0.0
     err_gpu = float((gpu - truth).abs().max()) if truth.numel() else 0.0
     err_cpu = float((cpu32 - truth).abs().max()) if truth.numel() else 0.0
-    bound = max(slack * err_cpu, rel * scale, 1e-12)
+    bound = max(slack * err_cpu, rel * scale, floor, 1e-12)
     assert err_gpu <= bound, (f"{what}: |gpu - fp64 truth| = {err_gpu:.3e} exceeds max({slack} x fp32 reference "
                               f"error {err_cpu:.3e}, {rel} x scale {scale:.3e})")
+
+
+def grad_floor(truth_grads):
+    """1e-6 of the largest parameter gradient of the model (see the comment above)."""
+    return 1e-6 * max([float(g.abs().max()) for g in truth_grads if g is not None and g.numel()] + [0.0])
 
 
 def assert_case_close_to_truth(res, truth):
@@ -207,7 +217,8 @@ def assert_case_close_to_truth(res, truth):
         assert_close_to_truth(out[f"pred{k}"], ref[f"pred{k}"], truth[f"pred{k}"], f"pred{k}")
         k += 1
     assert set(out["grads"]) == set(ref["grads"]), set(out["grads"]) ^ set(ref["grads"])
+    floor = grad_floor(truth["grads"].values())
     for n, g in ref["grads"].items():
-        assert_close_to_truth(out["grads"][n], g, truth["grads"][n], f"grad {n}")
+        assert_close_to_truth(out["grads"][n], g, truth["grads"][n], f"grad {n}", floor=floor)
     if res["cfg"].get("forces"):
         assert_close_to_truth(out["pos_grad"], ref["pos_grad"], truth["pos_grad"], "pos_grad (forces)")

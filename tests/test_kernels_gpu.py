@@ -532,7 +532,7 @@ def test_cfconv_gathered_backward_kernels(ops, N, E):
     topo = make_topo(ops, ei, N, sorted_side=1)
     g = torch.randn(N, F, generator=gen).to(DEV)
     x1 = torch.randn(N, F, generator=gen).to(DEV)
-    h = torch.randn(E, F, generator=gen).to(DEV)
+    h = (torch.rand(E, F, generator=gen) * 3.0 - 0.6).to(DEV)        # the range of ssp(z) = softplus(z) - ln 2
     dist = (torch.rand(E, generator=gen) * 4.9 + 0.05).to(DEV)
     w1t = (torch.randn(F, F, generator=gen) / F ** 0.5).to(DEV)
     gw = ops["contract"]._edge_w_raw(topo, g, 1, x1, 0, None, 1, F)
@@ -545,4 +545,5 @@ def test_cfconv_gathered_backward_kernels(ops, N, E):
     # and against plain torch on the CPU
     gw_cpu = g.cpu()[ei[1]] * x1.cpu()[ei[0]]
     ref = ks.filter_bwd(gw_cpu, h.cpu(), dist.cpu(), cutoff, w1t.cpu())
-    torch.testing.assert_close(dz0.cpu(), ref, rtol=1e-4, atol=1e-5)
+    truth = ks.filter_bwd(gw_cpu.double(), h.cpu().double(), dist.cpu().double(), cutoff, w1t.cpu().double())
+    pu.assert_close_to_truth(dz0, ref, truth, "dz0")

@@ -68,15 +68,16 @@ def _workload_parity(workload, num_graphs, num_layers, train, sample_kwargs, wit
             ref.train() if train else ref.eval()
             data = mg.Data(**{k: ((v.to(dtype) if v.is_floating_point() else v.clone()) if torch.is_tensor(v) else v)
                               for k, v in batch.items()})
+            pos = data.pos = data.pos.detach().clone()       # a leaf of this run
             if spec["forces"]:
-                data.pos.requires_grad_(True)
+                pos.requires_grad_(True)
                 loss = ref.energy_force_loss(ref(data), data)[0]
             else:
                 loss = ref.loss(ref(data), data.y, [torch.arange(data.y.shape[0])])[0]
             loss.backward()
             out = {"loss": loss.detach(), "grads": {n: p.grad for n, p in ref.named_parameters()}}
             if spec["forces"]:
-                out["forces"] = -data.pos.grad.detach()      # d loss / d pos (through the force term too)
+                out["forces"] = -pos.grad.detach()           # d loss / d pos (through the force term too)
         return out, ref
 
     state = None
@@ -92,8 +93,9 @@ def _workload_parity(workload, num_graphs, num_layers, train, sample_kwargs, wit
     model.train() if train else model.eval()
     dev = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in batch.items() if k not in ("cell", "pbc")}
     d = Data(**dev)
+    pos_gpu = d.pos
     if spec["forces"]:
-        d.pos.requires_grad_(True)
+        pos_gpu.requires_grad_(True)
         loss = model.energy_force_loss(model(d), d)[0]
     else:
         loss = model.loss(model(d), d.y, [torch.arange(d.y.shape[0], device="cuda")])[0]
@@ -101,16 +103,17 @@ def _workload_parity(workload, num_graphs, num_layers, train, sample_kwargs, wit
     torch.testing.assert_close(loss.detach().cpu(), ref32["loss"], rtol=1e-5, atol=1e-6)
     if spec["forces"]:
         if truth is not None:
-            pu.assert_close_to_truth(-d.pos.grad, ref32["forces"], truth["forces"], "d loss / d pos")
+            pu.assert_close_to_truth(-pos_gpu.grad, ref32["forces"], truth["forces"], "d loss / d pos")
         else:
-            torch.testing.assert_close(-d.pos.grad.cpu(), ref32["forces"], rtol=1e-4, atol=1e-6)
+            torch.testing.assert_close(-pos_gpu.grad.cpu(), ref32["forces"], rtol=1e-4, atol=1e-6)
+    floor = pu.grad_floor(truth["grads"].values()) if truth is not None else 0.0
     for n, p in model.named_parameters():
         g32 = ref32["grads"][n]
         if g32 is None:
             assert p.grad is None or float(p.grad.abs().max()) == 0.0, n
             continue
         if truth is not None:
-            pu.assert_close_to_truth(p.grad, g32, truth["grads"][n], f"grad {n}")
+            pu.assert_close_to_truth(p.grad, g32, truth["grads"][n], f"grad {n}", floor=floor)
         else:
             scale = max(float(g32.abs().max()), 1e-6)
             torch.testing.assert_close(p.grad.cpu(), g32, rtol=1e-4, atol=1e-4 * scale,
