@@ -1222,6 +1222,29 @@ int launch_fwd(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N
   return check_launch("attn_varlen_fwd(tcgen05)");
 }
 
+// one side stream + fork / join events per device, created on first use
+struct SideStream {
+  cudaStream_t stream;
+  cudaEvent_t fork, join;
+};
+static SideStream* side_stream() {
+  static std::mutex mu;
+  static SideStream table[64];
+  static bool ready[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ready[dev]) {
+    SideStream s{};
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    table[dev] = s;
+    ready[dev] = true;
+  }
+  return &table[dev];
+}
+
 template <int D>
 int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk, float* dv, int64_t N,
                cudaStream_t st) {
@@ -1236,24 +1259,33 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     rc = opt_in_smem(k_attn_bwd_kv_tc<D>, smem_kv, "attn_bwd_kv_tc");
     if (rc) return rc;
     k_attn_bwd_kv_tc<D><<<grid, kKvThreads, smem_kv, st>>>(a, b, dk, dv);
-  } else {
-    rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
-    if (rc) return rc;
-    k_attn_bwd_kv_pipe<D><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv);
-  }
-  if (serial) {
     size_t smem_q = sizeof(float) * (2 * BM * D + 6 * BN * D);
     if (smem_q < 80 * 1024) smem_q = 80 * 1024;
     rc = opt_in_smem(k_attn_bwd_q_tc<D>, smem_q, "attn_bwd_q_tc");
     if (rc) return rc;
     k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
-  } else {
-    // 512 TMEM columns: one CTA per SM, enforced through the shared-memory request as well
-    size_t smem_q = sizeof(float) * (4 * 6 * 32 * D + 2 * D * BM);     // 4 stages + the groups' fp32 totals
-    if (smem_q < 120 * 1024) smem_q = 120 * 1024;
-    rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
-    if (rc) return rc;
-    k_attn_bwd_q_pipe<D><<<grid, kKvPipeThreads, smem_q, st>>>(a, b, dq);
+    return check_launch("attn_varlen_bwd(tcgen05)");
+  }
+  rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
+  if (rc) return rc;
+  size_t smem_q = sizeof(float) * (4 * 6 * 32 * D + 2 * D * BM);       // 4 stages + the groups' fp32 totals
+  if (smem_q < 120 * 1024) smem_q = 120 * 1024;
+  rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
+  if (rc) return rc;
+  // The dK/dV and dQ kernels are independent and each runs one CTA per SM: 256 + 256 CTAs on 148 SMs are
+  // two partly empty second waves when the kernels run back to back.  With the dQ kernel on a second
+  // stream its CTAs start on the SMs that the dK/dV kernel's last wave leaves idle.  Fork / join with
+  // events around the pair; the side stream and the events are created once per device (the first call
+  // on a device should therefore not be inside a stream capture).  HGK_ATTN_BWD_OVERLAP=0: one stream.
+  static const bool overlap = [] { const char* e = getenv("HGK_ATTN_BWD_OVERLAP"); return !(e && e[0] == '0'); }();
+  SideStream* ss = overlap ? side_stream() : nullptr;
+  const bool forked = ss != nullptr && cudaEventRecord(ss->fork, st) == cudaSuccess &&
+                      cudaStreamWaitEvent(ss->stream, ss->fork, 0) == cudaSuccess;
+  k_attn_bwd_kv_pipe<D><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv);
+  k_attn_bwd_q_pipe<D><<<grid, kKvPipeThreads, smem_q, forked ? ss->stream : st>>>(a, b, dq);
+  if (forked) {
+    if (cudaEventRecord(ss->join, ss->stream) != cudaSuccess || cudaStreamWaitEvent(st, ss->join, 0) != cudaSuccess)
+      return fail(HGK_ERR_CUDA, "attn_varlen_bwd: joining the side stream failed: %s", cudaGetErrorString(cudaGetLastError()));
   }
   return check_launch("attn_varlen_bwd(tcgen05)");
 }
