@@ -88,6 +88,8 @@ _SIGNATURES = {
          _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_mask_axpy": (_c_i32, [_c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
+    "hgk_collate_rows": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_i64, _c_ptr]),
+    "hgk_collate_edges": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_ptr]),
     "hgk_pna_aggregate_fwd": (
         _c_i32,
         [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr,
@@ -208,7 +210,7 @@ def call(name, *args, cost=(0, 0)):
     if cost != (0, 0):
         b, f, d = stats.cost.get(name, (0, 0, 0))
         stats.cost[name] = (b + cost[0], f + cost[1], d + (cost[2] if len(cost) > 2 else cost[0]))
-    if stats.timing:
+    if stats.timing and not torch.cuda.is_current_stream_capturing():   # events recorded in a capture cannot be timed
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)
         e0.record()

@@ -252,8 +252,25 @@ def split_dataset(dataset, perc_train, stratify_splitting=False):
 
 def create_dataloaders(trainset, valset, testset, batch_size, train_sampler_shuffle=True,
                        test_sampler_shuffle=True):
+    """Loaders of the three splits.  HYDRAGNN_DEVICE_COLLATE=1: every split is uploaded once into packed
+    device arenas and the mini-batches are collated on the GPU (preprocess/packed_dataset.py) instead of
+    on the host per batch."""
     size, rank = get_comm_size_and_rank()
     loaders = []
+    if os.environ.get("HYDRAGNN_DEVICE_COLLATE", "0") == "1" and torch.cuda.is_available():
+        from .packed_dataset import PackedDataset
+        device = get_device()
+        for samples, shuffle in ((trainset, train_sampler_shuffle), (valset, test_sampler_shuffle),
+                                 (testset, test_sampler_shuffle)):
+            samples = samples.dataset if isinstance(samples, ListDataset) else list(samples)
+            ds = PackedDataset(samples, device)
+            sampler = None
+            if size > 1:
+                sampler = torch.utils.data.distributed.DistributedSampler(ds, num_replicas=size, rank=rank,
+                                                                          shuffle=shuffle)
+            loaders.append(torch.utils.data.DataLoader(ds, batch_size=batch_size, shuffle=(sampler is None and shuffle),
+                                                       sampler=sampler, collate_fn=ds.collate))
+        return tuple(loaders)
     for samples, shuffle in ((trainset, train_sampler_shuffle), (valset, test_sampler_shuffle),
                              (testset, test_sampler_shuffle)):
         ds = samples if isinstance(samples, torch.utils.data.Dataset) else ListDataset(samples)

@@ -24,7 +24,8 @@ _EQUIVARIANT_MODELS = ("EGNN", "SchNet", "PNAEq", "PAINN", "MACE")
 
 
 def _dataset_of(loader):
-    return loader.dataset
+    ds = loader.dataset
+    return getattr(ds, "samples", ds)          # PackedDataset keeps the host samples next to its device arenas
 
 
 def _graph_size_variable(*loaders):

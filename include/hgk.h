@@ -358,6 +358,28 @@ int hgk_radius_graph_fill(const float* pos, const int32_t* gptr,
                           int64_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------- *
+ * Device-side collate (reference: torch_geometric Batch.from_data_list on the
+ * host for every mini-batch, hydragnn/preprocess/load_data.py:225-326 and
+ * serialized_dataset_loader.py:110-212).  The samples of a split live in packed
+ * device arenas, one row matrix per field; a mini-batch gathers the row ranges
+ * of its samples:
+ *   out rows out_ptr[b] .. out_ptr[b+1] = arena rows src_off[b] .. (same count),
+ *   b < B; rows are row_bytes wide (a multiple of 4); seg_id (optional, int64
+ *   [total_rows]) receives b for every output row (the `batch` vector).
+ * hgk_collate_edges does the same for edge lists stored as (src, dst) int64
+ * pairs with sample-local node ids and writes edge_index [2, E_out] with the
+ * batch's node offsets node_ptr[b] added.  out_ptr / src_off / node_ptr are
+ * device arrays of int64.  Byte / index work: bit-exact.
+ * ------------------------------------------------------------------------- */
+int hgk_collate_rows(void* out, const void* arena, const int64_t* out_ptr,
+                     const int64_t* src_off, int64_t B, int32_t row_bytes,
+                     int64_t* seg_id, int64_t total_rows, void* stream);
+int hgk_collate_edges(int64_t* edge_index, const int64_t* pairs,
+                      const int64_t* out_ptr, const int64_t* src_off,
+                      const int64_t* node_ptr, int64_t B, int64_t E_out,
+                      void* stream);
+
+/* ------------------------------------------------------------------------- *
  * GPS global attention, variable-length segments (reference:
  * hydragnn/globalAtt/gps.py:126-133 = to_dense_batch + nn.MultiheadAttention
  * core + unpad).  q,k,v,o: [N, H, D] fp32 (row stride ld* floats, head h at
