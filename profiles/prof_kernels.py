@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "hydragnn-gps-support_b200"))
 
 from hydragnn import ops  # noqa: E402
-from hydragnn.ops import attention, contract, filter as filt  # noqa: E402
+from hydragnn.ops import attention, contract, node, filter as filt  # noqa: E402
 from hydragnn.ops.topo import Topo  # noqa: E402
 
 
@@ -52,6 +52,13 @@ def main(reps=3):
         contract._edge_w_raw(topo, x, 1, x, 0, None, 1, F)           # its backward w.r.t. W
         o, lse, q, k, v = attention._attn_fwd_raw(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu, H, D ** -0.5)
         attention._attn_bwd_raw(do, o, lse, q, k, v, cu, H, D ** -0.5)
+        # node-row kernels of the GPS block: QKV projection, its input gradient, its weight gradient, BatchNorm
+        win = (torch.randn(3 * c, c, generator=gen) * 0.1).to(dev)
+        y = node.linear_tc(x, win, torch.zeros(3 * c, device=dev))
+        node.linear_tc(y, win, trans_w=True, residual=x)
+        node.wgrad_rows(y, x)
+        mean, rstd = node.bn_stats(x)
+        node.bn_apply(x, node.BnParams(mean, rstd, None, None))
     torch.cuda.synchronize()
     print("ok")
 
