@@ -41,26 +41,26 @@ struct LinearArgs {
 constexpr int kBK = 32;
 
 template <bool TRANS_B>
-__global__ void __launch_bounds__(kThreads, TRANS_B ? 1 : 2)
+__global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc(const LinearArgs p) {
   extern __shared__ __align__(128) float smem[];
-  __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t bar[2];             // [s]: the MMAs that read operand stage s are complete
   __shared__ uint32_t tmem_slot;
-  float* Ahi = smem;              float* Alo = Ahi + 128 * kBK;
-  float* Bhi = Alo + 128 * kBK;   float* Blo = Bhi + 128 * kBK;
+  constexpr int kStage = 4 * 128 * kBK;                // floats per stage: A hi, A lo, B hi, B lo
   const uint32_t kCols = p.tmem_cols;
-  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  if (threadIdx.x == 0) mbar_init(&bar[1], 1);         // bar[0]: cta_setup, which also publishes both
+  const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
 
   const int32_t row0 = (int32_t)blockIdx.x * 128;
   const int32_t col0 = (int32_t)blockIdx.y * 128;
-  const OperandDesc dA = operand_desc<kBK>(Ahi, Alo), dB = operand_desc<kBK>(Bhi, Blo);
   constexpr uint32_t kIdesc = idesc_tf32(128, 128);
 
-  // Two register sets: the loads of chunk k + 2 are issued as soon as chunk k has been written to shared
-  // memory, i.e. they have a whole iteration (staging, barrier, MMAs, wait) to arrive.  With one set the
-  // global-load latency was exposed in every iteration (16 us for an [8192 x 128] x [128 x 128] product).
+  // Two operand stages in shared memory and two register sets.  Chunk k is written to stage k & 1 while the
+  // MMAs of chunk k - 1 (other stage) execute; the loads of chunk k + 2 are issued as soon as chunk k has
+  // left its registers.  Per iteration the CTA pays max(staging, MMAs) instead of their sum plus the
+  // global-load latency.
   struct Regs {
     Tile<128, kBK> a;
     Tile<128, kBK> b;          // !TRANS_B: rows = output features
@@ -72,29 +72,44 @@ k_linear_tc(const LinearArgs p) {
     if (!TRANS_B) r.b.load(p.w + k0, p.ldw, col0, p.N);
     else r.bt.load(p.w + col0, p.ldw, k0, p.K);
   };
-  uint32_t parity = 0;
-  auto step = [&](Regs& r, int k0) {
-    r.a.store_rows(Ahi, Alo);
-    if (!TRANS_B) r.b.store_rows(Bhi, Blo);
-    else r.bt.store_transposed(Bhi, Blo);
+  uint32_t parity[2] = {0, 0};
+  int uses[2] = {0, 0};                                 // chunks issued from each stage so far
+  auto step = [&](Regs& r, int k0, int st) {
+    float* base = smem + st * kStage;
+    if (uses[st] > 0) {                                 // the previous chunk of this stage has been consumed
+      mbar_wait(&bar[st], parity[st]);
+      parity[st] ^= 1;
+      fence_after_sync();
+    }
+    r.a.store_rows(base, base + 128 * kBK);
+    if (!TRANS_B) r.b.store_rows(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
+    else r.bt.store_transposed(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
     publish_operands();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
+      const OperandDesc dA = operand_desc<kBK>(base, base + 128 * kBK);
+      const OperandDesc dB = operand_desc<kBK>(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
       const int chunk = k0 / p.chunk_k;
       mma3_ss<kBK>(tmem + (uint32_t)chunk * 128, dA, dB, kIdesc, k0 > chunk * p.chunk_k);
-      mma_commit(&bar);
+      mma_commit(&bar[st]);
     }
-    if (k0 + 2 * kBK < p.K) fetch(r, k0 + 2 * kBK);     // this set is free again: refill it two chunks ahead
-    mbar_wait(&bar, parity);
-    parity ^= 1;
-    fence_after_sync();
+    ++uses[st];
+    if (k0 + 2 * kBK < p.K) fetch(r, k0 + 2 * kBK);     // this register set is free again
   };
 
   fetch(r0, 0);
   if (kBK < p.K) fetch(r1, kBK);
   for (int k0 = 0; k0 < p.K; k0 += 2 * kBK) {
-    step(r0, k0);
-    if (k0 + kBK < p.K) step(r1, k0 + kBK);
+    step(r0, k0, 0);
+    if (k0 + kBK < p.K) step(r1, k0 + kBK, 1);
+  }
+  // every MMA complete before the accumulators are read: the last commit of each stage
+#pragma unroll
+  for (int st = 0; st < 2; ++st) {
+    if (uses[st] > 0) {
+      mbar_wait(&bar[st], parity[st]);
+      fence_after_sync();
+    }
   }
 
   // ---- epilogue: lane = row, this thread's 64 of the 128 columns ----
@@ -438,10 +453,9 @@ extern "C" int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
   const uint32_t tmem_cols = chunks == 1 ? 128u : (chunks == 2 ? 256u : 512u);
   tc::LinearArgs a{x, ldx, w, ldw, bias, mask, nz, ldnz, residual, ldr, scale, relu, y, ldy, M, N, K,
                    chunk_k, chunks, tmem_cols};
-  // 64 KB of operand tiles; with 512 TMEM columns only one CTA fits an SM, which the shared-memory
-  // request then says as well (a second resident CTA would only spin in tcgen05.alloc)
-  const size_t smem_max = 120 * 1024;
-  const size_t smem = tmem_cols == 512 ? smem_max : sizeof(float) * 4 * 128 * tc::kBK;
+  // two operand stages of 64 KB: one CTA per SM
+  const size_t smem_max = sizeof(float) * 2 * 4 * 128 * tc::kBK;
+  const size_t smem = smem_max;
   static bool configured[2] = {false, false};                   // the attribute is per function, set once
   cudaError_t err = cudaSuccess;
   if (!configured[trans_w ? 1 : 0]) {

@@ -138,6 +138,10 @@ class GradientAverager:
         self._pending = [len(c["members"]) for c in self.chunks]
         self._works = []
         self._next = 0              # chunks [0, _next) have been launched this step
+        # NCCL averages inside the collective (ReduceOp.AVG): no separate scaling pass over the buffer after
+        # the last chunk has arrived; gloo (CPU tests) has no AVG: SUM, then one multiply in finish()
+        self._avg_in_collective = bool(self.enabled and dev.type == "cuda" and dist.is_initialized()
+                                       and dist.get_backend(self.group) == "nccl")
         self.stream = torch.cuda.Stream(device=dev) if (dev.type == "cuda" and self.enabled) else None
         for p in self.params:
             p.grad = None
@@ -171,12 +175,13 @@ class GradientAverager:
         torch.cat(parts, out=chunk["view"])
         for p, v in zip(chunk["members"], chunk["views"]):
             p.grad = v
+        op = dist.ReduceOp.AVG if self._avg_in_collective else dist.ReduceOp.SUM
         if self.stream is not None:
             self.stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.stream):
-                work = dist.all_reduce(chunk["view"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                work = dist.all_reduce(chunk["view"], op=op, group=self.group, async_op=True)
         else:
-            work = dist.all_reduce(chunk["view"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            work = dist.all_reduce(chunk["view"], op=op, group=self.group, async_op=True)
         self._works.append(work)
 
     def _on_grad_ready(self, p):
@@ -200,7 +205,8 @@ class GradientAverager:
             w.wait()
         if self.stream is not None:
             torch.cuda.current_stream().wait_stream(self.stream)
-        self.flat.mul_(1.0 / self.world_size)
+        if not self._avg_in_collective:
+            self.flat.mul_(1.0 / self.world_size)
         self._works = []
 
 
