@@ -59,8 +59,13 @@ class PainnMessage(nn.Module):
         topo = getattr(edge, "_hgk_topo", None)
         if topo is None:   # `edge` is edge_index.T ([E,2]); receivers are column 0
             topo = topo_of(edge.t().contiguous(), node_scalar.size(0))
-        fw = self.filter_layer(sinc_expansion(edge_dist, self.edge_size, self.cutoff))
-        fw = fw * cosine_cutoff(edge_dist, self.cutoff)
+        # fw = (W sinc(d) + b) * fcut(d)  (PAINNStack.py:230-235) with the cutoff folded into the radial basis:
+        # fw = [sinc(d) fcut(d) | fcut(d)] [W | b]^T.  The cutoff is then applied to R + 1 columns instead of
+        # 3F, and neither the forward nor the (double) backward has an elementwise pass over [E, 3F].
+        cut = cosine_cutoff(edge_dist, self.cutoff)
+        basis = torch.cat((sinc_expansion(edge_dist, self.edge_size, self.cutoff) * cut, cut), dim=1)
+        fw = torch.nn.functional.linear(
+            basis, torch.cat((self.filter_layer.weight, self.filter_layer.bias.unsqueeze(1)), dim=1))
         if edge_attr is not None and self.edge_dim is not None:
             first = self.edge_filter[0]
             gate = edge_linear(edge_attr, first.weight, first.bias)
