@@ -40,77 +40,132 @@ struct LinearArgs {
 
 constexpr int kBK = 32;
 
+// cp.async (LDGSTS): 16 bytes global -> shared without a register; src_bytes = 0 zero-fills
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool ok) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;"
+               :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(ok ? 16 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+constexpr int kLinDepth = 4;                             // K chunks in flight (raw copies in shared memory)
+
 template <bool TRANS_B>
 __global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc(const LinearArgs p) {
   extern __shared__ __align__(128) float smem[];
-  __shared__ __align__(8) uint64_t bar[2];             // [s]: the MMAs that read operand stage s are complete
+  __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
-  constexpr int kStage = 4 * 128 * kBK;                // floats per stage: A hi, A lo, B hi, B lo
+  // shared memory: operand tiles (A hi, A lo, B hi, B lo: 64 KB), then kLinDepth raw chunk slots of
+  // 32 KB (A rows [128 x 32] and B rows [128 x 32] or, TRANS_B, [32 x 128])
+  float* Ahi = smem;              float* Alo = Ahi + 128 * kBK;
+  float* Bhi = Alo + 128 * kBK;   float* Blo = Bhi + 128 * kBK;
+  float* raw = Blo + 128 * kBK;
+  constexpr int kRawSlot = 2 * 128 * kBK;                // floats per raw chunk slot
   const uint32_t kCols = p.tmem_cols;
-  if (threadIdx.x == 0) mbar_init(&bar[1], 1);         // bar[0]: cta_setup, which also publishes both
-  const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
   const uint32_t tmem = cs.tmem;
   const int warp_u = warp_id_uniform();
 
   const int32_t row0 = (int32_t)blockIdx.x * 128;
   const int32_t col0 = (int32_t)blockIdx.y * 128;
+  const OperandDesc dA = operand_desc<kBK>(Ahi, Alo), dB = operand_desc<kBK>(Bhi, Blo);
   constexpr uint32_t kIdesc = idesc_tf32(128, 128);
 
-  // Two operand stages in shared memory and two register sets.  Chunk k is written to stage k & 1 while the
-  // MMAs of chunk k - 1 (other stage) execute; the loads of chunk k + 2 are issued as soon as chunk k has
-  // left its registers.  Per iteration the CTA pays max(staging, MMAs) instead of their sum plus the
-  // global-load latency.
-  struct Regs {
-    Tile<128, kBK> a;
-    Tile<128, kBK> b;          // !TRANS_B: rows = output features
-    Tile<kBK, 128> bt;         // TRANS_B : rows = k
+  // The global-load latency used to be paid in every K iteration (ncu: long-scoreboard stalls dominate,
+  // 16 us for [8192 x 128] x [128 x 128]).  Now the first kLinDepth chunks are requested at once with
+  // cp.async into shared-memory slots; every thread copies exactly the 16-byte pieces it will itself
+  // split into the hi / lo operand tiles, so its own cp.async.wait_group is the only synchronisation the
+  // raw slots need, and a slot is refilled (chunk k + kLinDepth) as soon as its owner has read it.
+  using TA = Tile<128, kBK>;
+  using TB = Tile<128, kBK>;            // !TRANS_B: rows = output features
+  using TBT = Tile<kBK, 128>;           // TRANS_B : rows = k
+  const int nchunks = p.K / kBK;
+  auto request = [&](int chunk) {       // one commit group per call (possibly empty: keeps the count uniform)
+    if (chunk < nchunks) {
+      const int k0 = chunk * kBK;
+      float* slot = raw + (chunk % kLinDepth) * kRawSlot;
+#pragma unroll
+      for (int it = 0; it < TA::PER; ++it) {
+        int r, c;
+        TA::coord(it, r, c);
+        const bool ok = row0 + r < (int32_t)p.M;
+        cp_async16(slot + r * kBK + 4 * c, p.x + (int64_t)(ok ? row0 + r : 0) * p.ldx + k0 + 4 * c, ok);
+      }
+      float* bslot = slot + 128 * kBK;
+      if (!TRANS_B) {
+#pragma unroll
+        for (int it = 0; it < TB::PER; ++it) {
+          int r, c;
+          TB::coord(it, r, c);
+          const bool ok = col0 + r < p.N;
+          cp_async16(bslot + r * kBK + 4 * c, p.w + (int64_t)(ok ? col0 + r : 0) * p.ldw + k0 + 4 * c, ok);
+        }
+      } else {
+#pragma unroll
+        for (int it = 0; it < TBT::PER; ++it) {
+          int r, c;
+          TBT::coord(it, r, c);            // r: k row of the chunk, c: 16-byte column of the 128 outputs
+          cp_async16(bslot + r * 128 + 4 * c, p.w + (int64_t)(k0 + r) * p.ldw + col0 + 4 * c, true);
+        }
+      }
+    }
+    cp_async_commit();
   };
-  Regs r0, r1;
-  auto fetch = [&](Regs& r, int k0) {
-    r.a.load(p.x + k0, p.ldx, row0, (int32_t)p.M);
-    if (!TRANS_B) r.b.load(p.w + k0, p.ldw, col0, p.N);
-    else r.bt.load(p.w + col0, p.ldw, k0, p.K);
-  };
-  uint32_t parity[2] = {0, 0};
-  int uses[2] = {0, 0};                                 // chunks issued from each stage so far
-  auto step = [&](Regs& r, int k0, int st) {
-    float* base = smem + st * kStage;
-    if (uses[st] > 0) {                                 // the previous chunk of this stage has been consumed
-      mbar_wait(&bar[st], parity[st]);
-      parity[st] ^= 1;
+
+#pragma unroll
+  for (int d = 0; d < kLinDepth; ++d) request(d);
+  uint32_t parity = 0;
+  for (int chunk = 0; chunk < nchunks; ++chunk) {
+    cp_async_wait<kLinDepth - 1>();                     // this thread's pieces of `chunk` have landed
+    const float* slot = raw + (chunk % kLinDepth) * kRawSlot;
+    TA ta;
+    TB tb;
+    TBT tbt;
+#pragma unroll
+    for (int it = 0; it < TA::PER; ++it) {
+      int r, c;
+      TA::coord(it, r, c);
+      ta.v[it] = *reinterpret_cast<const float4*>(slot + r * kBK + 4 * c);
+    }
+    if (!TRANS_B) {
+#pragma unroll
+      for (int it = 0; it < TB::PER; ++it) {
+        int r, c;
+        TB::coord(it, r, c);
+        tb.v[it] = *reinterpret_cast<const float4*>(slot + 128 * kBK + r * kBK + 4 * c);
+      }
+    } else {
+#pragma unroll
+      for (int it = 0; it < TBT::PER; ++it) {
+        int r, c;
+        TBT::coord(it, r, c);
+        tbt.v[it] = *reinterpret_cast<const float4*>(slot + 128 * kBK + r * 128 + 4 * c);
+      }
+    }
+    if (chunk > 0) {                                     // the MMAs of the previous chunk have read the tiles
+      mbar_wait(&bar, parity);
+      parity ^= 1;
       fence_after_sync();
     }
-    r.a.store_rows(base, base + 128 * kBK);
-    if (!TRANS_B) r.b.store_rows(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
-    else r.bt.store_transposed(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
+    ta.store_rows(Ahi, Alo);
+    if (!TRANS_B) tb.store_rows(Bhi, Blo);
+    else tbt.store_transposed(Bhi, Blo);
+    // the slot is free again: its only reader has consumed the values (the stores above depend on them)
+    request(chunk + kLinDepth);
     publish_operands();
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      const OperandDesc dA = operand_desc<kBK>(base, base + 128 * kBK);
-      const OperandDesc dB = operand_desc<kBK>(base + 2 * 128 * kBK, base + 3 * 128 * kBK);
-      const int chunk = k0 / p.chunk_k;
-      mma3_ss<kBK>(tmem + (uint32_t)chunk * 128, dA, dB, kIdesc, k0 > chunk * p.chunk_k);
-      mma_commit(&bar[st]);
-    }
-    ++uses[st];
-    if (k0 + 2 * kBK < p.K) fetch(r, k0 + 2 * kBK);     // this register set is free again
-  };
-
-  fetch(r0, 0);
-  if (kBK < p.K) fetch(r1, kBK);
-  for (int k0 = 0; k0 < p.K; k0 += 2 * kBK) {
-    step(r0, k0, 0);
-    if (k0 + kBK < p.K) step(r1, k0 + kBK, 1);
-  }
-  // every MMA complete before the accumulators are read: the last commit of each stage
-#pragma unroll
-  for (int st = 0; st < 2; ++st) {
-    if (uses[st] > 0) {
-      mbar_wait(&bar[st], parity[st]);
-      fence_after_sync();
+      const int k0 = chunk * kBK;
+      const int acc = k0 / p.chunk_k;
+      mma3_ss<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, k0 > acc * p.chunk_k);
+      mma_commit(&bar);
     }
   }
+  cp_async_wait<0>();
+  mbar_wait(&bar, parity);                               // the last chunk's MMAs (K >= 32: at least one chunk)
+  fence_after_sync();
 
   // ---- epilogue: lane = row, this thread's 64 of the 128 columns ----
   const int64_t row = (int64_t)row0 + cs.row_local;
@@ -453,8 +508,8 @@ extern "C" int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
   const uint32_t tmem_cols = chunks == 1 ? 128u : (chunks == 2 ? 256u : 512u);
   tc::LinearArgs a{x, ldx, w, ldw, bias, mask, nz, ldnz, residual, ldr, scale, relu, y, ldy, M, N, K,
                    chunk_k, chunks, tmem_cols};
-  // two operand stages of 64 KB: one CTA per SM
-  const size_t smem_max = sizeof(float) * 2 * 4 * 128 * tc::kBK;
+  // 64 KB of operand tiles + kLinDepth raw chunk slots of 32 KB: one CTA per SM
+  const size_t smem_max = sizeof(float) * (4 * 128 * tc::kBK + tc::kLinDepth * 2 * 128 * tc::kBK);
   const size_t smem = smem_max;
   static bool configured[2] = {false, false};                   // the attribute is per function, set once
   cudaError_t err = cudaSuccess;

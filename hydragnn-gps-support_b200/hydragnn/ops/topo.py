@@ -61,10 +61,10 @@ class Topo:
         if self._csr[side] is None:
             key = self.idx[side]
             if self.sorted_side == side:
-                # already grouped: rowptr from counts, identity permutation
-                counts = torch.bincount(key.long(), minlength=self.num_rows[side])
-                rowptr = torch.zeros(self.num_rows[side] + 1, dtype=torch.int32, device=key.device)
-                rowptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+                # already grouped (ascending): rowptr[n] = first position with key >= n, identity
+                # permutation.  A binary search per row: no device -> host sync (bincount has one)
+                bounds = torch.arange(self.num_rows[side] + 1, dtype=key.dtype, device=key.device)
+                rowptr = torch.searchsorted(key, bounds, out_int32=True)
                 self._csr[side] = (rowptr, None)
             else:
                 self._csr[side] = build_csr(key, self.num_rows[side])
