@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "hydragnn-gps-support_b200"))
 
 from hydragnn import _hgk  # noqa: E402
-from hydragnn.ops import attention, contract, filter as filt, pna, radius  # noqa: E402
+from hydragnn.ops import attention, contract, filter as filt, node, pna, radius  # noqa: E402
 from hydragnn.ops.topo import Topo, build_csr  # noqa: E402
 
 DEV = torch.device("cuda:0")
@@ -124,6 +124,32 @@ def main():
         o, lse, q, k, v = st["r"]
         run(f"GPS attention backward, {name}", f"cfg5 N={N} H={H} D={D}",
             lambda: attention._attn_bwd_raw(do, o, lse, q, k, v, cu, H, D ** -0.5), reps, flush)
+
+    # node-row kernels of the GPS block at config 5 (N = 8192 rows, C = 128)
+    shape_n = f"cfg5 N={N} C={F}"
+    w_qkv = (torch.randn(3 * F, F, generator=gen) * 0.1).to(DEV)
+    w_sq = (torch.randn(F, F, generator=gen) * 0.1).to(DEV)
+    w_ff2 = (torch.randn(F, 2 * F, generator=gen) * 0.1).to(DEV)
+    b_qkv = torch.zeros(3 * F, device=DEV)
+    u2 = torch.randn(N, 2 * F, generator=gen).to(DEV)
+    mask = (torch.rand(N, F, generator=gen) < 0.75).to(torch.uint8).to(DEV)
+    run("Linear 128 -> 128 (+ bias)", shape_n, lambda: node.linear_tc(x, w_sq, b1), reps, flush)
+    run("QKV projection 128 -> 384 (+ bias)", shape_n, lambda: node.linear_tc(x, w_qkv, b_qkv), reps, flush)
+    run("FFN second Linear 256 -> 128 (+ bias, dropout mask, residual)", shape_n,
+        lambda: node.linear_tc(u2, w_ff2, b1, mask=mask, scale=4.0 / 3.0, residual=x), reps, flush)
+    run("input gradient of the QKV projection (transposed weight, K = 384, + residual)", shape_n,
+        lambda: node.linear_tc(qkv, w_qkv, trans_w=True, residual=x), reps, flush)
+    run("weight + bias gradient of the QKV projection ([384 x 128] over 8192 rows)", shape_n,
+        lambda: node.wgrad_rows(qkv, x), reps, flush)
+    st_bn = {}
+
+    def bn_s():
+        st_bn["p"] = node.BnParams(*node.bn_stats(x), b1 + 1.0, b1)
+    run("BatchNorm batch statistics", shape_n, bn_s, reps, flush)
+    run("BatchNorm apply (sum of two normalised inputs)", shape_n,
+        lambda: node.bn_apply(x, st_bn["p"], do, st_bn["p"]), reps, flush)
+    run("BatchNorm backward (two inputs, one dropout mask)", shape_n,
+        lambda: node.bn_bwd(do, x, st_bn["p"], do, st_bn["p"], mask_b=mask, scale_b=4.0 / 3.0), reps, flush)
 
     # periodic radius graph of config 5: 8 jittered BCC 8x8x8 cells, r = 5.0
     a = 2.8
