@@ -207,8 +207,7 @@ k_attn_fwd_tc(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* __r
 // top of step s has covered.
 constexpr int kFwdGroups = 4;
 constexpr int kFwdGroup = 128;
-constexpr int kFwdIssuers = 2;                          // MMA-issuing warps: warp G*4 + i serves the groups g = i (mod 2)
-constexpr int kFwdThreads = kFwdGroups * kFwdGroup + 32 * kFwdIssuers;
+constexpr int kFwdThreads = kFwdGroups * kFwdGroup + 32;
 
 template <int D>
 __global__ void __launch_bounds__(kFwdThreads, 1)
@@ -223,12 +222,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
   const int warp_u = warp_id_uniform();
-  // One thread issues a tcgen05.mma every ~20 cycles, an [128 x 32 x 8] MMA executes in ~17: a single issuing
-  // thread was the limiter (tensor pipe ~50 % active).  Two issuing warps, each serving every other group --
-  // the groups' column sets, accumulators, stages and mbarriers are disjoint, so their MMA streams need
-  // no ordering between them.
-  const bool issuer = warp_u >= G * kFwdGroup / 32;    // the last two warps
-  const int gi = warp_u - G * kFwdGroup / 32;          // issuer index (issuers only)
+  const bool issuer = warp_u == G * kFwdGroup / 32;    // the last warp
 
   constexpr int kTile = BK * D;
   constexpr int kStage = 4 * kTile;                    // K rows hi/lo, V^T hi/lo
@@ -240,8 +234,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   static_assert(kColQlo + D <= kCols, "TMEM budget");
   if (threadIdx.x == 0) {
 #pragma unroll
-    for (int i = 1; i < G; ++i) mbar_init(&bar[i], 1);
-    mbar_init(&bar[G], kFwdIssuers);                   // "everything done": one arrival per issuing warp
+    for (int i = 1; i <= G; ++i) mbar_init(&bar[i], 1);
   }
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4 = group (G: issuer)
   const uint32_t tmem = cs.tmem;
@@ -263,10 +256,10 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
     named_bar_sync(1, kFwdThreads);                    // Q rows are in TMEM, the first G stages are written
     fence_after_sync();
     if (elect_one_sync()) {
-      for (int s = gi; s < G && s < nsub; s += kFwdIssuers) { issue_scores(s); mma_commit(&bar[s]); }
+      for (int s = 0; s < G && s < nsub; ++s) { issue_scores(s); mma_commit(&bar[s]); }
     }
     __syncwarp();
-    for (int s = gi; s < nsub; s += kFwdIssuers) {     // G is a multiple of kFwdIssuers: s % G keeps my parity
+    for (int s = 0; s < nsub; ++s) {
       const int g = s % G;
       named_bar_sync(2 + g, kFwdGroup + 32);           // P_s is in TMEM, stage of step s+G is written
       fence_after_sync();
@@ -275,13 +268,11 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
                     at_stage(dVt, s % NST), kIdescO, ((s / G) % kPromote) != 0);   // O_g (+)= P_s V_s
         if (s + G < nsub) issue_scores(s + G);
         mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[G]);
       }
       __syncwarp();
     }
-    if (elect_one_sync()) mma_commit(&bar[G]);         // after my last MMA (arrives at once if I issued none)
-    __syncwarp();
   } else {
-    static_assert(kFwdGroups % kFwdIssuers == 0, "an issuer serves whole groups");
     const int g = cs.half;                             // my group; it owns the steps s = g (mod G)
     const int32_t row = row0 + cs.row_local;
     const bool row_ok = row < seg_end;
@@ -757,10 +748,9 @@ __device__ __forceinline__ unsigned long long prof_clock() {
 //    s = g (mod 2) and column set g: while one group is waiting (TMEM load latency, the mbarrier,
 //    the proxy fence) the other one computes, and the tensor pipe runs the other group's
 //    dV / dK updates and S^T / dP^T products meanwhile;
-//  * two more warps do nothing but issue MMAs, one per compute group.  Issuing the 48 tcgen05.mma of one
-//    step costs an issuing thread ~1000 cycles (measured, profiles/kv_phase_profile.py) -- more than the
-//    ~820 cycles they execute -- so with one issuing warp the tensor pipe sat at ~50 %; the two groups'
-//    column sets, accumulators, stages and mbarriers are disjoint, so their MMA streams are independent.
+//  * a 17th warp does nothing but issue MMAs.  Issuing the 48 tcgen05.mma of one step costs the
+//    issuing thread ~1000 cycles (measured, profiles/kv_phase_profile.py); when that thread was
+//    also a compute thread every other warp waited for it at the next barrier.
 // Hand-offs: group g -> issuer through named barrier 2+g (bar.arrive, the group does not wait);
 // issuer -> group g through mbarrier g (tcgen05.commit).  For step s the issuer queues
 // [dV += P_s^T dO_s,  dK += dS_s^T Q_s,  S^T_{s+2} = K Q_{s+2}^T,  dP^T_{s+2} = V dO_{s+2}^T];
@@ -768,7 +758,7 @@ __device__ __forceinline__ unsigned long long prof_clock() {
 // dV / dK of step s have read P_s / dS_s from it.  Four shared-memory stages: the stage written
 // during step s (for step s+2, same group) was last read by the MMAs of step s-2, which the
 // mbarrier wait at the top of step s has covered.
-constexpr int kKvPipeThreads = kKvThreads + 64;        // + two MMA-issuing warps, one per compute group
+constexpr int kKvPipeThreads = kKvThreads + 32;
 constexpr int kKvGroup = 256;                          // threads per compute group
 
 template <int D>
@@ -785,8 +775,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
   const int h = blockIdx.y;
   const int warp_u = warp_id_uniform();
-  const bool issuer = warp_u >= kKvThreads / 32;       // warps 16 and 17
-  const int gi = warp_u - kKvThreads / 32;             // the compute group an issuing warp serves
+  const bool issuer = warp_u == kKvThreads / 32;       // warp 16
 
   constexpr int kTile = BQ * D;                        // floats per operand tile
   constexpr int kStage = 8 * kTile;                    // floats per stage
@@ -802,7 +791,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColAcc = 256;
   constexpr uint32_t kColKhi = 256 + 4 * D, kColKlo = 256 + 5 * D, kColVhi = 256 + 6 * D, kColVlo = 256 + 7 * D;
   static_assert(256 + 8 * D <= 512, "TMEM budget");
-  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 2); }   // bar[0]: cta_setup, which also publishes all three
+  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }   // bar[0]: cta_setup, which also publishes all three
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BQ - 1) / BQ;
@@ -831,23 +820,24 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     };
     named_bar_sync(1, kKvPipeThreads);                 // K / V rows are in TMEM, stages 0 and 1 are written
     fence_after_sync();
-    if (gi < nsub && elect_one_sync()) {
-      issue_scores(gi);
-      mma_commit(&bar[gi]);
+    if (elect_one_sync()) {
+      issue_scores(0);
+      mma_commit(&bar[0]);
+      if (nsub > 1) { issue_scores(1); mma_commit(&bar[1]); }
     }
     __syncwarp();
-    for (int s = gi; s < nsub; s += 2) {
-      named_bar_sync(2 + gi, kKvGroup + 32);           // P_s, dS_s are in TMEM, stage of step s+2 is written
+    for (int s = 0; s < nsub; ++s) {
+      const int g = s & 1;
+      named_bar_sync(2 + g, kKvGroup + 32);            // P_s, dS_s are in TMEM, stage of step s+2 is written
       fence_after_sync();
       if (elect_one_sync()) {
         issue_updates(s);
         if (s + 2 < nsub) issue_scores(s + 2);
-        mma_commit(&bar[gi]);
+        mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[2]);
       }
       __syncwarp();
     }
-    if (elect_one_sync()) mma_commit(&bar[2]);         // after my last MMA; bar[2] counts both issuers
-    __syncwarp();
   } else {
     // ------------------------------------------------------------- compute groups 0 and 1 ---
     const int g = warp_u >> 3;                         // my group; it owns the steps s = g (mod 2)
@@ -1018,8 +1008,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
   const int h = blockIdx.y;
   const int warp_u = warp_id_uniform();
-  const bool issuer = warp_u >= kKvThreads / 32;       // warps 16 and 17
-  const int gi = warp_u - kKvThreads / 32;             // the compute group an issuing warp serves
+  const bool issuer = warp_u == kKvThreads / 32;       // warp 16
 
   constexpr int kTile = BK * D;                        // floats per operand tile
   constexpr int kStage = 6 * kTile;                    // floats per stage
@@ -1033,7 +1022,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;
   constexpr uint32_t kColQhi = 128 + 2 * D, kColQlo = 128 + 3 * D, kColGhi = 128 + 4 * D, kColGlo = 128 + 5 * D;
   static_assert(128 + 6 * D <= 512, "TMEM budget");
-  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 2); }     // bar[2]: one arrival per issuing warp
+  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BK - 1) / BK;
@@ -1054,25 +1043,26 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     };
     named_bar_sync(1, kKvPipeThreads);                 // Q / dO rows are in TMEM, stages 0 and 1 are written
     fence_after_sync();
-    if (gi < nsub && elect_one_sync()) {
-      issue_scores(gi);
-      mma_commit(&bar[gi]);
+    if (elect_one_sync()) {
+      issue_scores(0);
+      mma_commit(&bar[0]);
+      if (nsub > 1) { issue_scores(1); mma_commit(&bar[1]); }
     }
     __syncwarp();
-    for (int s = gi; s < nsub; s += 2) {
-      named_bar_sync(2 + gi, kKvGroup + 32);           // dS_s is in TMEM, stage of step s+2 is written
+    for (int s = 0; s < nsub; ++s) {
+      const int g = s & 1;
+      named_bar_sync(2 + g, kKvGroup + 32);            // dS_s is in TMEM, stage of step s+2 is written
       fence_after_sync();
       if (elect_one_sync()) {
-        const uint32_t set = (uint32_t)gi * BK;
-        mma3_ts<BK>(tmem + kColDQ + (uint32_t)gi * D, tmem + kColS + set, tmem + kColDP + set,
+        const uint32_t set = (uint32_t)g * BK;
+        mma3_ts<BK>(tmem + kColDQ + (uint32_t)g * D, tmem + kColS + set, tmem + kColDP + set,
                     at_stage(dKt, s & (NST - 1)), kIdescQ, ((s >> 1) % kPromote) != 0);
         if (s + 2 < nsub) issue_scores(s + 2);
-        mma_commit(&bar[gi]);
+        mma_commit(&bar[g]);
+        if (s == nsub - 1) mma_commit(&bar[2]);
       }
       __syncwarp();
     }
-    if (elect_one_sync()) mma_commit(&bar[2]);         // after my last MMA; bar[2] counts both issuers
-    __syncwarp();
   } else {
     const int g = warp_u >> 3;                         // my group; it owns the steps s = g (mod 2)
     const int part = cs.half;                          // warp / 4: 0..3
