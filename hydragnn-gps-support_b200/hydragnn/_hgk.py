@@ -88,6 +88,9 @@ _SIGNATURES = {
          _c_i64, _c_i32, _c_ptr],
     ),
     "hgk_mask_axpy": (_c_i32, [_c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
+    "hgk_edge_geom_fwd": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_i64, _c_ptr]),
+    "hgk_edge_geom_bwd": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_i64, _c_ptr]),
+    "hgk_edge_geom_bwd2": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_i64, _c_ptr]),
     "hgk_collate_rows": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i32, _c_ptr, _c_i64, _c_ptr]),
     "hgk_collate_edges": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_ptr]),
     "hgk_pna_aggregate_fwd": (

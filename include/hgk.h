@@ -128,6 +128,33 @@ int hgk_contract_edge_u(float* EU, const float* G, int64_t ldg, int32_t CG,
                         int64_t ldw, int64_t E, int32_t F, int32_t C,
                         void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * Edge geometry with explicit derivatives (reference: get_edge_vectors_and_lengths,
+ * hydragnn/utils/model/operations.py:21-36 = two index_selects, sub, add, vector
+ * norm, division; and autograd through them, twice under the force loss,
+ * models/Base.py:614-620).
+ *   fwd : vec[e] = pos[dst[e]] - pos[src[e]] (+ shifts[e]);  len[e] = |vec[e]|;
+ *         unit[e] = vec[e] / (len[e] + eps)            (unit may be NULL)
+ *   bwd : t[e] = d loss / d vec[e] given g_vec, g_len, g_unit (each may be NULL)
+ *         = g_vec + g_len vec / len + g_unit / (len + eps)
+ *           - vec (g_unit . vec) / (len (len + eps)^2)
+ *         (terms in 1 / len are dropped where len == 0); the gradient of pos is
+ *         the segmented sum of +t at dst and -t at src (hgk_contract_node).
+ *   bwd2: the derivative of bwd, for h = d loss / d t:  d_glen[e] = h . vec / len,
+ *         d_gunit = J h (J = d unit / d vec, symmetric), d_vec = sum_j h_j d t_j / d vec
+ *         (d g_vec = h itself).  d_glen / d_gunit may be NULL.
+ * pos, vec, unit, shifts, t, h: rows of 3 floats, contiguous.
+ * ------------------------------------------------------------------------- */
+int hgk_edge_geom_fwd(float* vec, float* len, float* unit, const float* pos,
+                      const int32_t* src, const int32_t* dst, const float* shifts,
+                      float eps, int64_t E, void* stream);
+int hgk_edge_geom_bwd(float* t, const float* g_vec, const float* g_len,
+                      const float* g_unit, const float* vec, const float* len,
+                      float eps, int64_t E, void* stream);
+int hgk_edge_geom_bwd2(float* d_glen, float* d_gunit, float* d_vec, const float* h,
+                       const float* g_len, const float* g_unit, const float* vec,
+                       const float* len, float eps, int64_t E, void* stream);
+
 /* out[e, f] = P[pi[e], f] + Q[qi[e], f]   (Q may be NULL)
  * The per-edge input of E_GCL.edge_model / PNAConv.message in split-weight
  * form: Linear(cat[x_i, x_j, ...]) = x_i W_a + x_j W_b + ... computed on the

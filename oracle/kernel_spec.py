@@ -344,3 +344,51 @@ def wgrad_edges(a, scale_d, cutoff, b=None, gauss=None):
     if b is None:
         b = _filter_input_padded(*gauss)
     return a.t() @ b, a.sum(0)
+
+
+# ---- edge geometry with explicit derivatives (csrc/edge_geom.cu; reference utils/model/operations.py:21-36) ----
+def edge_geom_fwd(pos, src, dst, shifts, eps, want_unit):
+    vec = pos[dst.long()] - pos[src.long()]
+    if shifts is not None:
+        vec = vec + shifts
+    length = torch.linalg.norm(vec, dim=-1)
+    unit = vec / (length + eps).unsqueeze(-1) if want_unit else None
+    return vec, length, unit
+
+
+def _inv_len(length):
+    return torch.where(length > 0, 1.0 / length.clamp(min=1e-300 if length.dtype == torch.float64 else 1e-38),
+                       torch.zeros_like(length))
+
+
+def edge_geom_bwd(g_vec, g_len, g_unit, vec, length, eps):
+    """t = d loss / d vec given the gradients of (vec, len, unit)."""
+    inv = _inv_len(length).unsqueeze(-1)
+    t = torch.zeros_like(vec) if g_vec is None else g_vec.clone()
+    if g_len is not None:
+        t = t + g_len.unsqueeze(-1) * vec * inv
+    if g_unit is not None:
+        d = 1.0 / (length + eps).unsqueeze(-1)
+        t = t + g_unit * d - vec * (g_unit * vec).sum(-1, keepdim=True) * inv * d * d
+    return t
+
+
+def edge_geom_bwd2(h, g_len, g_unit, vec, length, eps):
+    """(d g_len, d g_unit, d vec) for h = d loss / d t (the derivative of edge_geom_bwd)."""
+    L = length.unsqueeze(-1)
+    inv = _inv_len(length).unsqueeze(-1)
+    d = 1.0 / (L + eps)
+    c = inv * d * d
+    hv = (h * vec).sum(-1, keepdim=True)
+    d_glen = (hv * inv).squeeze(-1)
+    d_gunit = h * d - c * hv * vec
+    dv = torch.zeros_like(vec)
+    if g_len is not None:
+        gl = g_len.unsqueeze(-1)
+        dv = dv + gl * inv * h - gl * hv * inv ** 3 * vec
+    if g_unit is not None:
+        hg = (h * g_unit).sum(-1, keepdim=True)
+        gv = (g_unit * vec).sum(-1, keepdim=True)
+        cp = -inv * inv * d * d - 2.0 * inv * d ** 3
+        dv = dv - ((hg * c + hv * gv * cp * inv) * vec + gv * c * h + hv * c * g_unit)
+    return d_glen, d_gunit, dv

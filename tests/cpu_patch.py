@@ -112,7 +112,7 @@ def _fused_filter_ok(dist, raw, num_filters, num_gaussians):
 
 @contextlib.contextmanager
 def cpu_kernels():
-    from hydragnn.ops import attention, contract, node, pna, topo
+    from hydragnn.ops import attention, contract, geometry, node, pna, topo
     from hydragnn.ops import filter as filt
     import importlib
 
@@ -131,6 +131,8 @@ def cpu_kernels():
         (node, "linear_tc", ks.linear_tc), (node, "wgrad_rows", ks.wgrad_rows), (node, "bn_stats", ks.bn_stats),
         (node, "bn_apply", ks.bn_apply), (node, "bn_bwd", ks.bn_bwd), (node, "mask_axpy", ks.mask_axpy),
         (node, "device_ok", lambda t: t.dtype == torch.float32),
+        (geometry, "_fwd_raw", ks.edge_geom_fwd), (geometry, "_bwd_raw", ks.edge_geom_bwd),
+        (geometry, "_bwd2_raw", ks.edge_geom_bwd2),
         (filt, "_filter_fwd_raw", _filter_fwd_raw), (filt, "_filter_bwd_raw", _filter_bwd_raw),
         (filt, "_wgrad_raw", _wgrad_raw), (filt, "_cfconv_filter_bwd_raw", _cfconv_filter_bwd_raw),
         (filt, "_cfconv_wgrad_raw", _cfconv_wgrad_raw), (filt, "fused_filter_ok", _fused_filter_ok),

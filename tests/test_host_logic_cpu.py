@@ -103,3 +103,44 @@ def test_attention_double_backward_in_row_blocks(monkeypatch):
         want = second_order(lambda q, k, v: ks.attn_varlen_fwd_autograd(q, k, v, cu, H, D ** -0.5)[0])
         for a, b in zip(got, want):
             torch.testing.assert_close(a, b, rtol=1e-9, atol=1e-11)
+
+
+def _geometry_case(dtype, device, normalize, eps, with_shifts, use_op):
+    """value, d/dpos and d/dpos of |d/dpos|^2 (second order) of a scalar function of the edge geometry."""
+    from hydragnn.graph import topo_of
+    from hydragnn.utils.model import get_edge_vectors_and_lengths
+    from oracle import hydragnn_ref as ora
+
+    gen = torch.Generator().manual_seed(3)
+    N, E = 9, 40
+    pos = (torch.randn(N, 3, generator=gen, dtype=torch.float64) * 1.5).to(dtype).to(device).requires_grad_(True)
+    ei = torch.stack([torch.randint(0, N, (E,), generator=gen), torch.randint(0, N, (E,), generator=gen)])
+    ei = ei[:, ei[0] != ei[1]].to(device)
+    shifts = (torch.randn(ei.size(1), 3, generator=gen, dtype=torch.float64) * 0.1).to(dtype).to(device) if with_shifts else None
+    w = torch.randn(ei.size(1), 3, generator=gen, dtype=torch.float64).to(dtype).to(device)
+    if use_op:
+        vec, length = get_edge_vectors_and_lengths(pos, ei, shifts, normalize=normalize, eps=eps)
+    else:           # the reference always adds a shift tensor (zeros without PBC)
+        vec, length = ora.get_edge_vectors_and_lengths(pos, ei, torch.zeros_like(w) if shifts is None else shifts,
+                                                       normalize=normalize, eps=eps)
+    value = (torch.sin(vec) * w).sum() + (length ** 2 * w[:, :1]).sum() + (vec * w).sum() ** 2 * 0.01
+    (g,) = torch.autograd.grad(value, pos, create_graph=True)
+    (gg,) = torch.autograd.grad((g ** 2).sum(), pos)
+    return value.detach(), g.detach(), gg.detach()
+
+
+@pytest.mark.parametrize("normalize,eps,with_shifts", [(False, 1e-9, False), (True, 1e-9, True), (True, 1.0, False)])
+def test_edge_geometry_operator_first_and_second_derivatives(normalize, eps, with_shifts):
+    """ops.geometry (forward, vector-Jacobian product and its hand-written derivative, over kernel_spec on the
+    CPU) against torch autograd through the reference's op chain, in fp64: value, forces-like first
+    derivative and the second-order term the force loss differentiates."""
+    from hydragnn.ops import geometry
+
+    want = _geometry_case(torch.float64, "cpu", normalize, eps, with_shifts, use_op=False)
+    with cpu_kernels():
+        got = _geometry_case(torch.float32, "cpu", normalize, eps, with_shifts, use_op=True)
+    # the operator runs in fp32 (kernel_spec's segmented sums are fp32): a wrong term in a derivative formula
+    # would show up at order one, rounding at 1e-6
+    for a, b, what in zip(got, want, ("value", "first derivative", "second-order term")):
+        scale = float(b.abs().max())
+        torch.testing.assert_close(a.double(), b, rtol=1e-4, atol=1e-5 * scale, msg=lambda m, what=what: f"{what}: {m}")

@@ -547,3 +547,44 @@ def test_cfconv_gathered_backward_kernels(ops, N, E):
     ref = ks.filter_bwd(gw_cpu, h.cpu(), dist.cpu(), cutoff, w1t.cpu())
     truth = ks.filter_bwd(gw_cpu.double(), h.cpu().double(), dist.cpu().double(), cutoff, w1t.cpu().double())
     pu.assert_close_to_truth(dz0, ref, truth, "dz0")
+
+
+# -------------------------------------------------------------------- edge geometry ---
+@pytest.mark.parametrize("normalize,eps,with_shifts", [(False, 1e-9, False), (True, 1e-9, True), (True, 1.0, False)])
+def test_edge_geometry_kernels(ops, normalize, eps, with_shifts):
+    """hgk_edge_geom_fwd / _bwd / _bwd2 vs their restatement, and the operator (value, first derivative and
+    the second-order term of the force loss) vs torch autograd through the reference's op chain in fp64."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(__file__))
+    from test_host_logic_cpu import _geometry_case
+    from hydragnn.ops import geometry
+
+    gen = torch.Generator().manual_seed(11)
+    N, E = 300, 5000
+    pos = torch.randn(N, 3, generator=gen) * 2
+    src = torch.randint(0, N, (E,), generator=gen, dtype=torch.int32)
+    dst = (src + 1 + torch.randint(0, N - 1, (E,), generator=gen, dtype=torch.int32)) % N      # no self pairs
+    shifts = torch.randn(E, 3, generator=gen) * 0.1 if with_shifts else None
+    d = lambda t: None if t is None else t.to(DEV)
+    vec, length, unit = geometry._fwd_raw(d(pos), d(src), d(dst), d(shifts), eps, normalize)
+    rv, rl, ru = ks.edge_geom_fwd(pos, src, dst, shifts, eps, normalize)
+    torch.testing.assert_close(vec.cpu(), rv, rtol=0, atol=0)             # sub / add with the reference's roundings
+    torch.testing.assert_close(length.cpu(), rl, rtol=1e-6, atol=1e-7)
+    if normalize:
+        torch.testing.assert_close(unit.cpu(), ru, rtol=1e-6, atol=1e-7)
+    g_vec, g_unit, h = (torch.randn(E, 3, generator=gen) for _ in range(3))
+    g_len = torch.randn(E, generator=gen)
+    gu = g_unit if normalize else None
+    t = geometry._bwd_raw(d(g_vec), d(g_len), d(gu), vec, length, eps)
+    torch.testing.assert_close(t.cpu(), ks.edge_geom_bwd(g_vec, g_len, gu, rv, rl, eps), rtol=1e-5, atol=1e-5)
+    got = geometry._bwd2_raw(d(h), d(g_len), d(gu), vec, length, eps)
+    want = ks.edge_geom_bwd2(h.double(), g_len.double(), None if gu is None else gu.double(), rv.double(), rl.double(), eps)
+    for a, b, what in zip(got, want, ("d g_len", "d g_unit", "d vec")):
+        scale = float(b.abs().max())
+        torch.testing.assert_close(a.cpu().double(), b, rtol=1e-4, atol=1e-5 * scale, msg=lambda m, what=what: f"{what}: {m}")
+    # the operator end to end, second order included
+    truth = _geometry_case(torch.float64, "cpu", normalize, eps, with_shifts, use_op=False)
+    gpu = _geometry_case(torch.float32, DEV, normalize, eps, with_shifts, use_op=True)
+    for a, b, what in zip(gpu, truth, ("value", "first derivative", "second-order term")):
+        scale = float(b.abs().max())
+        torch.testing.assert_close(a.cpu().double(), b, rtol=1e-4, atol=1e-5 * scale, msg=lambda m, what=what: f"{what}: {m}")
