@@ -244,16 +244,25 @@ k_linear_tc(const LinearArgs p) {
 // stable merge across slabs; the order is fixed by (N, C) alone.
 constexpr int kBnSlabRows = 256;
 
+// Rows that count: the first min(N, *n_valid) (n_valid: device scalar or NULL).  Padded mini-batches
+// (train/step_graph.py) keep their pad rows behind the real ones; statistics and gradients ignore them.
+__device__ __forceinline__ int64_t valid_rows(int64_t N, const long long* n_valid) {
+  if (n_valid == nullptr) return N;
+  const int64_t v = (int64_t)__ldg(n_valid);
+  return v < N ? (v > 0 ? v : 0) : N;
+}
+
 __global__ void __launch_bounds__(256)
 k_bn_stats_partial(float* __restrict__ part_mean, float* __restrict__ part_m2, const float* __restrict__ t,
-                   int64_t ldt, int64_t N, int C) {
+                   int64_t ldt, int64_t N_all, int C, const long long* __restrict__ n_valid) {
   __shared__ float red[8][32];
   __shared__ float mean_s[32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
+  const int64_t N = valid_rows(N_all, n_valid);
   const int64_t beg = (int64_t)blockIdx.y * kBnSlabRows;
-  const int64_t end = beg + kBnSlabRows < N ? beg + kBnSlabRows : N;
-  const float cnt = (float)(end - beg);
+  const int64_t end = beg + kBnSlabRows < N ? beg + kBnSlabRows : (N > beg ? N : beg);
+  const float cnt = end > beg ? (float)(end - beg) : 1.f;
   float acc = 0.f;
   if (c < C)
     for (int64_t n = beg + warp; n < end; n += 8) acc += __ldg(t + n * ldt + c);
@@ -288,10 +297,12 @@ k_bn_stats_partial(float* __restrict__ part_mean, float* __restrict__ part_m2, c
 __global__ void __launch_bounds__(128)
 k_bn_stats_final(float* __restrict__ mean_out, float* __restrict__ rstd_out, float* __restrict__ running_mean,
                  float* __restrict__ running_var, long long* __restrict__ num_batches, float momentum, float eps,
-                 const float* __restrict__ part_mean, const float* __restrict__ part_m2, int S, int64_t N, int C) {
+                 const float* __restrict__ part_mean, const float* __restrict__ part_m2, int S, int64_t N_all, int C,
+                 const long long* __restrict__ n_valid) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c == 0 && num_batches != nullptr) *num_batches += 1;
   if (c >= C) return;
+  const int64_t N = valid_rows(N_all, n_valid);
   float n_a = 0.f, mean = 0.f, m2 = 0.f;
   for (int s0 = 0; s0 < S; s0 += 8) {                   // the slabs' statistics are fetched eight at a time
     float mb[8], qb[8];
@@ -304,7 +315,7 @@ k_bn_stats_final(float* __restrict__ mean_out, float* __restrict__ rstd_out, flo
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int s = s0 + j;
-      if (s < S) {
+      if (s < S && (int64_t)s * kBnSlabRows < N) {
         const int64_t beg = (int64_t)s * kBnSlabRows;
         const float n_b = (float)((beg + kBnSlabRows < N ? beg + kBnSlabRows : N) - beg);
         const float n = n_a + n_b;
@@ -315,7 +326,7 @@ k_bn_stats_final(float* __restrict__ mean_out, float* __restrict__ rstd_out, flo
       }
     }
   }
-  const float var = m2 / (float)N;                      // biased: what normalises the batch
+  const float var = N > 0 ? m2 / (float)N : 0.f;        // biased: what normalises the batch
   mean_out[c] = mean;
   rstd_out[c] = rsqrtf(var + eps);
   if (running_mean != nullptr) {
@@ -359,10 +370,11 @@ k_bn_apply(float* __restrict__ out, int64_t ldo, const BnSide a, const BnSide b,
 // column sums of the backward: S0 = sum g, Sa = sum g * xhat_a, Sb = sum g * xhat_b (slab partials)
 __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(float* __restrict__ partial, const float* __restrict__ g, int64_t ldg, const BnSide a,
-                 const BnSide b, int64_t N, int C, int S) {
+                 const BnSide b, int64_t N_all, int C, int S, const long long* __restrict__ n_valid) {
   __shared__ float red[3][8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
+  const int64_t N = valid_rows(N_all, n_valid);
   const int64_t beg = (int64_t)blockIdx.y * kBnSlabRows;
   const int64_t end = beg + kBnSlabRows < N ? beg + kBnSlabRows : N;
   float s0 = 0.f, sa = 0.f, sb = 0.f;
@@ -417,12 +429,24 @@ struct BnBwdOut {
 // dt = gamma * rstd * (g - S0 / N - xhat * Sx / N)
 __global__ void __launch_bounds__(256)
 k_bn_bwd_apply(const float* __restrict__ g, int64_t ldg, const BnSide a, const BnSide b, const BnBwdOut oa,
-               const BnBwdOut ob, const float* __restrict__ sums, int64_t N, int C) {
+               const BnBwdOut ob, const float* __restrict__ sums, int64_t N_all, int C,
+               const long long* __restrict__ n_valid) {
   const int C4 = C / 4;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N * C4) return;
+  if (i >= N_all * C4) return;
   const int64_t n = i / C4;
   const int c = (int)(i % C4) * 4;
+  const int64_t N = valid_rows(N_all, n_valid);
+  if (n >= N) {                                          // pad rows: no gradient (they never reach the loss)
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(oa.dt + n * C + c) = z;
+    if (oa.dz != nullptr) *reinterpret_cast<float4*>(oa.dz + n * C + c) = z;
+    if (b.t != nullptr) {
+      *reinterpret_cast<float4*>(ob.dt + n * C + c) = z;
+      if (ob.dz != nullptr) *reinterpret_cast<float4*>(ob.dz + n * C + c) = z;
+    }
+    return;
+  }
   const float inv_n = 1.f / (float)N;
   const float4 gv = __ldg(reinterpret_cast<const float4*>(g + n * ldg + c));
   const float4 s0 = __ldg(reinterpret_cast<const float4*>(sums + c));
@@ -535,7 +559,8 @@ static int bn_check(const char* what, const float* t, int64_t ldt, int64_t N, in
 
 extern "C" int hgk_bn_stats(float* mean, float* rstd, float* running_mean, float* running_var,
                             int64_t* num_batches_tracked, float momentum, float eps, float* partial,
-                            const float* t, int64_t ldt, int64_t N, int32_t C, void* stream) {
+                            const float* t, int64_t ldt, int64_t N, int32_t C, const int64_t* n_valid,
+                            void* stream) {
   int rc = bn_check("bn_stats", t, ldt, N, C);
   if (rc) return rc;
   HGK_REQUIRE(mean && rstd && partial, "bn_stats: NULL output");
@@ -543,10 +568,11 @@ extern "C" int hgk_bn_stats(float* mean, float* rstd, float* running_mean, float
   const int S = (int)hgk_bn_slabs(N);
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((unsigned)ceil_div(C, 32), (unsigned)S);
-  k_bn_stats_partial<<<grid, 256, 0, st>>>(partial, partial + (int64_t)S * C, t, ldt, N, C);
+  k_bn_stats_partial<<<grid, 256, 0, st>>>(partial, partial + (int64_t)S * C, t, ldt, N, C, (const long long*)n_valid);
   k_bn_stats_final<<<(unsigned)ceil_div(C, 32), 32, 0, st>>>(mean, rstd, running_mean, running_var,
                                                                (long long*)num_batches_tracked, momentum, eps, partial,
-                                                               partial + (int64_t)S * C, S, N, C);
+                                                               partial + (int64_t)S * C, S, N, C,
+                                                               (const long long*)n_valid);
   return check_launch("bn_stats");
 }
 
@@ -570,7 +596,8 @@ extern "C" int hgk_bn_bwd(float* dta, float* dza, const uint8_t* mask_a, float s
                           float* dgamma_b, float* dbeta_b, float* workspace, const float* g, int64_t ldg,
                           const float* ta, int64_t ldta, const float* mean_a, const float* rstd_a,
                           const float* gamma_a, const float* tb, int64_t ldtb, const float* mean_b,
-                          const float* rstd_b, const float* gamma_b, int64_t N, int32_t C, void* stream) {
+                          const float* rstd_b, const float* gamma_b, int64_t N, int32_t C, const int64_t* n_valid,
+                          void* stream) {
   int rc = bn_check("bn_bwd", ta, ldta, N, C);
   if (rc) return rc;
   rc = bn_check("bn_bwd", g, ldg, N, C);
@@ -584,12 +611,13 @@ extern "C" int hgk_bn_bwd(float* dta, float* dza, const uint8_t* mask_a, float s
   float* partial = workspace;                       // [3, S, C]
   float* sums = workspace + 3 * (int64_t)S * C;     // [3, C]
   dim3 grid((unsigned)ceil_div(C, 32), (unsigned)S);
-  k_bn_bwd_partial<<<grid, 256, 0, st>>>(partial, g, ldg, a, b, N, C, S);
+  k_bn_bwd_partial<<<grid, 256, 0, st>>>(partial, g, ldg, a, b, N, C, S, (const long long*)n_valid);
   k_bn_bwd_final<<<(unsigned)ceil_div(C, 32), 32, 0, st>>>(sums, dgamma_a, dbeta_a, tb ? dgamma_b : nullptr,
                                                              tb ? dbeta_b : nullptr, partial, S, C);
   const BnBwdOut oa{dta, dza, mask_a, scale_a}, ob{dtb, dzb, mask_b, scale_b};
   const int64_t total = N * (C / 4);
-  k_bn_bwd_apply<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(g, ldg, a, b, oa, ob, sums, N, C);
+  k_bn_bwd_apply<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(g, ldg, a, b, oa, ob, sums, N, C,
+                                                                 (const long long*)n_valid);
   return check_launch("bn_bwd");
 }
 

@@ -73,7 +73,7 @@ _SIGNATURES = {
     "hgk_bn_slabs": (_c_i64, [_c_i64]),
     "hgk_bn_stats": (
         _c_i32,
-        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_f32, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr],
+        [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_f32, _c_ptr, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr, _c_ptr],
     ),
     "hgk_bn_apply": (
         _c_i32,
@@ -85,7 +85,7 @@ _SIGNATURES = {
         _c_i32,
         [_c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_ptr, _c_ptr, _c_ptr,
          _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_ptr,
-         _c_i64, _c_i32, _c_ptr],
+         _c_i64, _c_i32, _c_ptr, _c_ptr],
     ),
     "hgk_mask_axpy": (_c_i32, [_c_ptr, _c_ptr, _c_i64, _c_ptr, _c_f32, _c_ptr, _c_i64, _c_i64, _c_i32, _c_ptr]),
     "hgk_edge_geom_fwd": (_c_i32, [_c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_ptr, _c_f32, _c_i64, _c_ptr]),
@@ -168,7 +168,8 @@ KERNELS_PER_CALL = {
     "hgk_edge_gather_add": 1, "hgk_schnet_filter_fwd": 1, "hgk_schnet_filter_bwd": 1, "hgk_wgrad_tn": 1, "hgk_wgrad_reduce": 1, "hgk_colsum": 2, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
     "hgk_radius_graph_count": 8, "hgk_radius_graph_fill": 1, "hgk_attn_varlen_fwd": 1,
     "hgk_attn_varlen_bwd": 3, "hgk_wgrad_rows": 2, "hgk_linear_tc": 1, "hgk_bn_stats": 2, "hgk_bn_apply": 1,
-    "hgk_bn_bwd": 3, "hgk_mask_axpy": 1,
+    "hgk_bn_bwd": 3, "hgk_mask_axpy": 1, "hgk_edge_geom_fwd": 1, "hgk_edge_geom_bwd": 1, "hgk_edge_geom_bwd2": 1,
+    "hgk_collate_rows": 1, "hgk_collate_edges": 1, "hgk_cfconv_filter_bwd": 1, "hgk_cfconv_wgrad": 1,
 }
 
 
@@ -188,9 +189,10 @@ class Stats:
         self.calls = {}
         self.cost = {}
         self.events = []
+        self.replayed = 0           # libhgk kernels launched by CUDA-graph replays (train/step_graph.py)
 
     def launches(self):
-        return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in self.calls.items())
+        return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in self.calls.items()) + self.replayed
 
     def summary(self):
         """name -> dict(calls, ms, bytes, flops); call after torch.cuda.synchronize()."""

@@ -304,6 +304,9 @@ class Base(Module):
     def _attention_segments(self, data, num_nodes, device):
         """cu_seqlens for the GPS layers, built once per forward (with the host-side sum of
         squared segment lengths attached for the kernel's flop accounting -- no device sync)."""
+        static = getattr(data, "gps_cu_seqlens", None)
+        if static is not None:          # a batch padded to its size bucket (train/step_graph.py): [0, N, N_b]
+            return static
         bounds = None
         if self.gps_segments == "graph" and getattr(data, "ptr", None) is not None:
             cu = data.ptr.to(device=device, dtype=torch.int32)

@@ -49,6 +49,13 @@ class RadiusInteractionGraph(nn.Module):
         # cached on the tensor object itself (not on its address, which the allocator reuses)
         # ... and keyed on the tensor's version counter: an in-place update of the positions (an MD or
         # relaxation loop, noise augmentation) rebuilds the graph, as the reference does every call
+        static = getattr(pos, "_hgk_rgraph_static", None)
+        if static is not None:
+            # a step captured as a CUDA graph (train/step_graph.py): the neighbour search ran before the
+            # replay, its result sits in this buffer (padded to the bucket, grouped by centre)
+            topo_of(static, pos.size(0), sorted_side=1)
+            vec, length = get_edge_vectors_and_lengths(pos, static, None)
+            return static, length.squeeze(-1)
         key = (self.cutoff, self.max_num_neighbors, pos._version)
         cached = getattr(pos, "_hgk_rgraph", None)
         if cached is None or cached[0] != key:

@@ -84,7 +84,12 @@ class BnParams:
         self.mean, self.rstd, self.gamma, self.beta = mean, rstd, gamma, beta
 
 
-def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, momentum=0.1, eps=1e-5):
+# Rows of the node matrices that belong to the mini-batch proper: None (all) or a device int64 scalar set by
+# train/step_graph.py around the forward pass of a batch padded to its size bucket.
+valid_rows = None
+
+
+def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, momentum=0.1, eps=1e-5, n_valid=None):
     """Batch statistics of the columns of t [N, C] -> (mean, 1 / sqrt(var + eps)); updates the running
     buffers in place the way nn.BatchNorm1d does in training (unbiased variance, momentum)."""
     t, ldt = _rows(t)
@@ -96,7 +101,7 @@ def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, m
     partial = torch.empty(2 * S * C, dtype=torch.float32, device=t.device)
     _hgk.call("hgk_bn_stats", _hgk.ptr(mean), _hgk.ptr(rstd), _hgk.ptr(running_mean), _hgk.ptr(running_var),
               _hgk.ptr(num_batches_tracked), float(momentum), float(eps), _hgk.ptr(partial), _hgk.ptr(t), ldt, N, C,
-              cost=(4 * (2 * N * C + 4 * S * C), 0))
+              _hgk.ptr(n_valid), cost=(4 * (2 * N * C + 4 * S * C), 0))
     return mean, rstd
 
 
@@ -116,7 +121,7 @@ def bn_apply(ta, pa, tb=None, pb=None, relu=False):
     return out
 
 
-def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, scale_b=1.0):
+def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, scale_b=1.0, n_valid=None):
     """Backward of bn_apply (without the activation) for the gradient g of its output.
     -> dict(dta, dza, dgamma_a, dbeta_a[, dtb, dzb, dgamma_b, dbeta_b]); dz* = scale * mask * dt*
     (the gradient behind a dropout feeding the BatchNorm input) or dt* itself without a mask."""
@@ -143,7 +148,7 @@ def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, s
               _hgk.ptr(out.get("dtb")), _hgk.ptr(out.get("dzb")), _hgk.ptr(mask_b), float(scale_b),
               _hgk.ptr(out.get("dgamma_b")), _hgk.ptr(out.get("dbeta_b")), _hgk.ptr(ws), _hgk.ptr(g), ldg,
               _hgk.ptr(ta), lda, _hgk.ptr(pa.mean), _hgk.ptr(pa.rstd), _hgk.ptr(pa.gamma), *side_b, N, C,
-              cost=(4 * N * C * (3 + 2 * (1 + two) + (mask_a is not None) + (mask_b is not None)), 0))
+              _hgk.ptr(n_valid), cost=(4 * N * C * (3 + 2 * (1 + two) + (mask_a is not None) + (mask_b is not None)), 0))
     if out["dza"] is None:
         out["dza"] = out["dta"]
     if two and out["dzb"] is None:
@@ -250,11 +255,12 @@ class GpsTailPost(torch.autograd.Function):
     def forward(ctx, x, t1, o, out_w, out_b, w1, b1, w2, b2, g1, be1, g2, be2, g3, be3, bufs, p):
         dev = x.device
         N, C = x.shape
+        nv = valid_rows                     # device scalar for a padded batch (train/step_graph.py), else None
         m2, scale = dropout_mask((N, C), p, dev)
         t2 = linear_tc(o, out_w, out_b, mask=m2, scale=scale, residual=x)
-        p2 = BnParams(*bn_stats(t2, *bufs[1]), g2, be2)
+        p2 = BnParams(*bn_stats(t2, *bufs[1], n_valid=nv), g2, be2)
         if t1 is not None:
-            p1 = BnParams(*bn_stats(t1, *bufs[0]), g1, be1)
+            p1 = BnParams(*bn_stats(t1, *bufs[0], n_valid=nv), g1, be1)
             s = bn_apply(t1, p1, t2, p2)
         else:
             p1 = None
@@ -263,19 +269,19 @@ class GpsTailPost(torch.autograd.Function):
         u = linear_tc(s, w1, b1, relu=True, mask=m3, scale=scale)
         m4, _ = dropout_mask((N, C), p, dev)
         t3 = linear_tc(u, w2, b2, mask=m4, scale=scale, residual=s)
-        p3 = BnParams(*bn_stats(t3, *bufs[2]), g3, be3)
+        p3 = BnParams(*bn_stats(t3, *bufs[2], n_valid=nv), g3, be3)
         y = bn_apply(t3, p3)
         ctx.save_for_backward(o, t1, t2, t3, s, u, m2, m4, out_w, w1, w2, g1, g2, g3,
                               p1.mean if p1 else None, p1.rstd if p1 else None, p2.mean, p2.rstd, p3.mean, p3.rstd)
-        ctx.scale = scale
+        ctx.scale, ctx.nv = scale, nv
         return y
 
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, gy):
         (o, t1, t2, t3, s, u, m2, m4, out_w, w1, w2, g1, g2, g3, mean1, rstd1, mean2, rstd2, mean3, rstd3) = ctx.saved_tensors
-        scale = ctx.scale
-        r3 = bn_bwd(gy, t3, BnParams(mean3, rstd3, g3, None), mask_a=m4, scale_a=scale)
+        scale, nv = ctx.scale, ctx.nv
+        r3 = bn_bwd(gy, t3, BnParams(mean3, rstd3, g3, None), mask_a=m4, scale_a=scale, n_valid=nv)
         dt3, dz4 = r3["dta"], r3["dza"]                       # dz4: gradient at W2's output (behind its dropout)
         dw2, db2 = wgrad_rows(dz4, u)
         dzu = linear_tc(dz4, w2, trans_w=True, nz=u, scale=scale)      # through dropout and ReLU: where u != 0
@@ -283,11 +289,11 @@ class GpsTailPost(torch.autograd.Function):
         ds = linear_tc(dzu, w1, trans_w=True, residual=dt3)
         p2 = BnParams(mean2, rstd2, g2, None)
         if t1 is not None:
-            r = bn_bwd(ds, t1, BnParams(mean1, rstd1, g1, None), t2, p2, mask_b=m2, scale_b=scale)
+            r = bn_bwd(ds, t1, BnParams(mean1, rstd1, g1, None), t2, p2, mask_b=m2, scale_b=scale, n_valid=nv)
             dt1, dt2, dz2 = r["dta"], r["dtb"], r["dzb"]
             dg1, dbe1, dg2, dbe2 = r["dgamma_a"], r["dbeta_a"], r["dgamma_b"], r["dbeta_b"]
         else:
-            r = bn_bwd(ds, t2, p2, mask_a=m2, scale_a=scale)
+            r = bn_bwd(ds, t2, p2, mask_a=m2, scale_a=scale, n_valid=nv)
             dt1, dt2, dz2 = None, r["dta"], r["dza"]
             dg1 = dbe1 = None
             dg2, dbe2 = r["dgamma_a"], r["dbeta_a"]

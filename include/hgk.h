@@ -270,12 +270,16 @@ int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
  *   variance), and *num_batches_tracked (int64, may be NULL) is incremented --
  *   nn.BatchNorm1d in training.  Slabs of 256 rows are reduced with the
  *   two-pass formula and merged in slab order (Chan et al.): fixed order.
- *   partial: scratch of 2 * hgk_bn_slabs(N) * C floats. */
+ *   partial: scratch of 2 * hgk_bn_slabs(N) * C floats.
+ *   n_valid (device int64 scalar or NULL): only the first min(N, *n_valid) rows
+ *   count -- mini-batches padded to a size bucket keep their pad rows last; in
+ *   hgk_bn_bwd the rows beyond get a zero gradient. */
 int64_t hgk_bn_slabs(int64_t N);
 int hgk_bn_stats(float* mean, float* rstd, float* running_mean,
                  float* running_var, int64_t* num_batches_tracked,
                  float momentum, float eps, float* partial, const float* t,
-                 int64_t ldt, int64_t N, int32_t C, void* stream);
+                 int64_t ldt, int64_t N, int32_t C, const int64_t* n_valid,
+                 void* stream);
 /* out = act( BN_a(ta) [+ BN_b(tb)] ),  BN(t) = (t - mean) * rstd * gamma + beta
  * (gamma / beta may be NULL; tb NULL = one input; relu != 0: act = ReLU). */
 int hgk_bn_apply(float* out, int64_t ldo, const float* ta, int64_t ldta,
@@ -298,7 +302,8 @@ int hgk_bn_bwd(float* dta, float* dza, const uint8_t* mask_a, float scale_a,
                const float* ta, int64_t ldta, const float* mean_a,
                const float* rstd_a, const float* gamma_a, const float* tb,
                int64_t ldtb, const float* mean_b, const float* rstd_b,
-               const float* gamma_b, int64_t N, int32_t C, void* stream);
+               const float* gamma_b, int64_t N, int32_t C, const int64_t* n_valid,
+               void* stream);
 /* out[N,C] = residual + scale * mask * z  (F.dropout + residual add,
  * gps.py:116-117,134-135; mask / residual may be NULL). */
 int hgk_mask_axpy(float* out, const float* z, int64_t ldz, const uint8_t* mask,

@@ -253,9 +253,11 @@ def wgrad_rows(a, b, want_bias=True):
     return a.t() @ b, (a.sum(0) if want_bias else None)
 
 
-def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, momentum=0.1, eps=1e-5):
+def bn_stats(t, running_mean=None, running_var=None, num_batches_tracked=None, momentum=0.1, eps=1e-5, n_valid=None):
     """hgk_bn_stats: what nn.BatchNorm1d computes in training (biased variance normalises, the unbiased
-    one goes into running_var)."""
+    one goes into running_var); with n_valid, over the first n_valid rows only."""
+    if n_valid is not None:
+        t = t[:int(n_valid)]
     n = t.size(0)
     mean = t.mean(0)
     var = t.var(0, unbiased=False)
@@ -283,17 +285,19 @@ def bn_apply(ta, pa, tb=None, pb=None, relu=False):
     return torch.relu(y) if relu else y
 
 
-def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, scale_b=1.0):
+def bn_bwd(g, ta, pa, tb=None, pb=None, mask_a=None, scale_a=1.0, mask_b=None, scale_b=1.0, n_valid=None):
     """hgk_bn_bwd: the standard BatchNorm backward with batch statistics,
-    dt = gamma rstd (g - mean(g) - xhat mean(g xhat))."""
-    n = ta.size(0)
+    dt = gamma rstd (g - mean(g) - xhat mean(g xhat)); with n_valid the sums run over the first n_valid rows
+    and the rows beyond get zero."""
+    n = ta.size(0) if n_valid is None else int(n_valid)
+    rows = (torch.arange(ta.size(0)) < n).to(ta.dtype).unsqueeze(1)
     out = {}
     for key, t, p, mask, scale in (("a", ta, pa, mask_a, scale_a), ("b", tb, pb, mask_b, scale_b)):
         if t is None:
             continue
         xhat = (t - p.mean) * p.rstd
-        s0, sx = g.sum(0), (g * xhat).sum(0)
-        dt = p.rstd * (g - s0 / n - xhat * (sx / n))
+        s0, sx = (g * rows).sum(0), (g * xhat * rows).sum(0)
+        dt = p.rstd * (g - s0 / n - xhat * (sx / n)) * rows
         if p.gamma is not None:
             dt = dt * p.gamma
         out["dt" + key] = dt
