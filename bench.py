@@ -42,6 +42,9 @@ def parse_args():
                          "plus a `workloads` array with BASELINE configs 2-4 (N = 1 only; the default when "
                          "no --workload is given on one GPU)")
     ap.add_argument("--single", action="store_true", help="default workload only (no `workloads` array)")
+    ap.add_argument("--step-graph", default="auto", choices=["auto", "on", "off"],
+                    help="replay whole training steps as CUDA graphs over size buckets (train/step_graph.py); "
+                         "auto = for the small-molecule workloads of the `workloads` array (configs 2 and 3)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gps-segments", default="batch", choices=["batch", "graph"],
                     help="batch = the reference's whole-mini-batch attention (SURVEY F3); graph = per-graph varlen")
@@ -295,8 +298,17 @@ def measure(args, workload, ctx, headline):
     model = create_model(**spec["arch"])
     model = get_distributed_model(model)
     model.module.gps_segments = args.gps_segments      # "batch" = the reference's semantics
-    optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3, fused=True)
+    # whole-step CUDA graphs over size buckets: the small-molecule configs, whose step is 1-3 ms of kernels
+    # behind 5-13 ms of host work.  Single rank, no force loss (train/step_graph.py says what is eligible).
+    want_sg = args.step_graph == "on" or (args.step_graph == "auto" and not headline
+                                          and workload in ("schnet_qm9", "egnn_gps_zinc"))
+    want_sg = want_sg and world == 1 and not forces
+    optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3, fused=True, capturable=want_sg)
     model.train()
+    step_graph = None
+    if want_sg:
+        from hydragnn.train.step_graph import BucketedStepGraph
+        step_graph = BucketedStepGraph(model, optimizer)
 
     resident = to_data(host, device, Data)
     torch.cuda.synchronize()
@@ -309,11 +321,16 @@ def measure(args, workload, ctx, headline):
         return out
 
     def step_resident():
+        if step_graph is not None:
+            return step_graph.step(fresh(resident))[0]
         return train_step(model, optimizer, fresh(resident), compute_grad_energy=forces)[0]
 
     def step_e2e():
         data = to_data(pinned, device, Data, non_blocking=True)
-        loss = train_step(model, optimizer, data, compute_grad_energy=forces)[0]
+        if step_graph is not None:
+            loss = step_graph.step(data)[0]
+        else:
+            loss = train_step(model, optimizer, data, compute_grad_energy=forces)[0]
         return float(loss)          # device -> host read of the step's result
 
     # ---- parity of the benchmarked step itself: the first training step's loss with the initial
@@ -406,6 +423,10 @@ def measure(args, workload, ctx, headline):
                    "gps_segments": args.gps_segments if spec["arch"]["global_attn_engine"] else None,
                    "parallelism": f"dp{world}", "optimizer": "AdamW (fused)", "tf32": False,
                    "graphed_gps_tail": bool(graphed_tail.ENABLED and spec["arch"]["global_attn_engine"]),
+                   "step_graph": (None if step_graph is None else
+                                  f"whole step replayed as a CUDA graph per size bucket (nodes -> x64, edges -> x1024): "
+                                  f"{step_graph.captures} captured, {step_graph.replays} replays, "
+                                  f"{step_graph.eager_steps} eager"),
                    "l2": ("flushed between steps" if flush is not None
                           else f"per-step working set ~{working_set / 1e9:.1f} GB of [E,F] edge tensors exceeds the 126 MB L2")},
         "e2e": {"value": (graphs_total * e2e_steps / (e2e_ms * 1e-3)) if e2e_steps else None, "unit": "graphs/s",

@@ -21,7 +21,12 @@ def _batches(workload, sizes, seed=3):
     out = []
     for n_graphs in sizes:
         graphs = [spec["sample"](rng) for _ in range(n_graphs)]
-        batch = syn.finish_edges(syn.collate(graphs))
+        batch = syn.collate(graphs)
+        if spec["edges"] == "radius":
+            from hydragnn.ops import radius_graph
+            g = radius_graph(batch["pos"].cuda(), batch["ptr"], spec["radius"], spec["max_neighbours"], loop=False)
+            batch["edge_index"] = g["edge_index"].cpu()
+        batch = syn.finish_edges(batch)
         dev = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in batch.items() if k not in ("cell", "pbc")}
         out.append(lambda dev=dev: Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in dev.items()}))
     return spec, out
