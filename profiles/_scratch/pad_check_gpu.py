@@ -48,3 +48,25 @@ with graphed_tail.eager():
         a,b=v[0],v[1][:N]
         print(k, "max abs diff on real rows", float((a-b).abs().max()), "scale", float(a.abs().max()))
     print("pred diff", float((pred[0]-pred2[0][:pred[0].size(0)]).abs().max()))
+# finer: sub-module outputs of layer 0
+from hydragnn.ops import node as nd
+layer=model.graph_convs[0]
+d_a=mk(); d_b=static["data"]
+with graphed_tail.eager(), torch.no_grad():
+    xa,_,ca=model._embedding(d_a); ca["cu_seqlens"]=model._attention_segments(d_a, xa.size(0), xa.device)
+    xb,_,cb=model._embedding(d_b); cb["cu_seqlens"]=model._attention_segments(d_b, xb.size(0), xb.device)
+    print("embed diff", float((xa-xb[:N]).abs().max()))
+    ha,_=layer.conv(inv_node_feat=xa, equiv_node_feat=d_a.pos, **{k:v for k,v in ca.items() if k!="cu_seqlens"})
+    hb,_=layer.conv(inv_node_feat=xb, equiv_node_feat=d_b.pos, **{k:v for k,v in cb.items() if k!="cu_seqlens"})
+    print("local conv diff", float((ha-hb[:N]).abs().max()), float(ha.abs().max()))
+    t1a,qa=layer._tail_pre(xa,ha); 
+    nd.valid_rows=static["valid_rows"]; t1b,qb=layer._tail_pre(xb,hb)
+    print("t1 diff", float((t1a-t1b[:N]).abs().max()), "qkv diff", float((qa-qb[:N]).abs().max()))
+    from hydragnn.ops import attn_varlen
+    C=layer.channels
+    oa=attn_varlen(qa[:,:C],qa[:,C:2*C],qa[:,2*C:],ca["cu_seqlens"],layer.heads)
+    ob=attn_varlen(qb[:,:C],qb[:,C:2*C],qb[:,2*C:],cb["cu_seqlens"],layer.heads)
+    print("attn diff", float((oa-ob[:N]).abs().max()), "cu", cb["cu_seqlens"].tolist())
+    nd.valid_rows=None; ya=layer._tail_post(xa,t1a,oa)
+    nd.valid_rows=static["valid_rows"]; yb=layer._tail_post(xb,t1b,ob); nd.valid_rows=None
+    print("post diff", float((ya-yb[:N]).abs().max()))

@@ -269,3 +269,44 @@ def test_linear_fast_autograd(libhgk):
     (gxc,) = torch.autograd.grad(yc.pow(2).sum(), xc, create_graph=True)
     gxc.sum().backward()
     torch.testing.assert_close(xs.grad.cpu(), xc.grad, rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,nv,C", [(192, 187, 128), (512, 300, 128), (256, 256, 64), (1030, 5, 128)])
+def test_batchnorm_valid_rows(libhgk, N, nv, C):
+    """n_valid (device scalar): statistics and gradients over the first nv rows only; rows beyond get no
+    gradient -- the padded mini-batches of train/step_graph.py."""
+    from hydragnn.ops import node
+
+    gen = torch.Generator().manual_seed(N + nv)
+    t = torch.randn(N, C, generator=gen) * 2 + 0.5
+    t[nv:] = 1.0e3                                                  # pad rows must not leak into the statistics
+    g = torch.randn(N, C, generator=gen)
+    gam, bet = torch.rand(C, generator=gen) + 0.5, torch.randn(C, generator=gen)
+    nv_d = torch.tensor([nv], dtype=torch.int64, device="cuda")
+    mean, rstd = node.bn_stats(t.cuda(), n_valid=nv_d)
+    mean_r, rstd_r = ks.bn_stats(t, n_valid=nv)
+    torch.testing.assert_close(mean.cpu(), mean_r, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(rstd.cpu(), rstd_r, rtol=1e-5, atol=1e-6)
+    pa = node.BnParams(mean, rstd, gam.cuda(), bet.cuda())
+    pr = node.BnParams(mean_r, rstd_r, gam, bet)
+    got = node.bn_bwd(g.cuda(), t.cuda(), pa, n_valid=nv_d)
+    want = ks.bn_bwd(g, t, pr, n_valid=nv)
+    torch.testing.assert_close(got["dta"].cpu()[:nv], want["dta"][:nv], rtol=1e-4, atol=1e-5)
+    assert float(got["dta"][nv:].abs().max()) == 0.0 if nv < N else True
+    torch.testing.assert_close(got["dgamma_a"].cpu(), want["dgamma_a"], rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(got["dbeta_a"].cpu(), want["dbeta_a"], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.gpu
+def test_attention_pad_segment_is_invisible(libhgk):
+    """cu_seqlens = [0, N, N_b]: the rows of the first segment equal whole-batch attention over N rows."""
+    from hydragnn.ops import attn_varlen
+
+    gen = torch.Generator().manual_seed(1)
+    N, Nb, H, D = 187, 192, 4, 32
+    qkv = torch.randn(Nb, 3 * H * D, generator=gen).cuda()
+    c = H * D
+    whole = attn_varlen(qkv[:N, :c], qkv[:N, c:2 * c], qkv[:N, 2 * c:], torch.tensor([0, N], dtype=torch.int32).cuda(), H)
+    padded = attn_varlen(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], torch.tensor([0, N, Nb], dtype=torch.int32).cuda(), H)
+    torch.testing.assert_close(padded[:N], whole, rtol=1e-6, atol=1e-6)
