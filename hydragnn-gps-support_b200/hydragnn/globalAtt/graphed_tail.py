@@ -35,13 +35,29 @@ _eager_depth = 0
 
 @contextlib.contextmanager
 def eager():
-    """Run GPS layers eagerly inside this block (double backward, debugging)."""
+    """Run GPS layers eagerly inside this block AND on twice-differentiable torch ops (force loss: the
+    backward pass is itself differentiated; GPSConv._native reads this flag)."""
     global _eager_depth
     _eager_depth += 1
     try:
         yield
     finally:
         _eager_depth -= 1
+
+
+_no_capture_depth = 0
+
+
+@contextlib.contextmanager
+def no_capture():
+    """No CUDA graphs of the tail's own inside this block (the caller captures the whole step itself,
+    train/step_graph.py); the kernel-library tail stays selected."""
+    global _no_capture_depth
+    _no_capture_depth += 1
+    try:
+        yield
+    finally:
+        _no_capture_depth -= 1
 
 
 class _Piece(torch.nn.Module):
@@ -111,7 +127,7 @@ def run(layer, which, x, *rest):
     """`layer._tail_pre(x, h_local)` or `layer._tail_post(x, h1, o)`, replayed from a CUDA graph when
     this signature has been captured."""
     has_local = rest[0] is not None
-    usable = (ENABLED and _eager_depth == 0 and layer.training and torch.is_grad_enabled() and x.is_cuda
+    usable = (ENABLED and _eager_depth == 0 and _no_capture_depth == 0 and layer.training and torch.is_grad_enabled() and x.is_cuda
               and x.requires_grad and (which == "post" or has_local)
               and not torch.cuda.is_current_stream_capturing())
     if not usable:

@@ -164,7 +164,7 @@ class BucketedStepGraph:
         data = static["data"]
         node_ops.valid_rows = static["valid_rows"]
         try:
-            with graphed_tail.eager():            # no graphs of their own inside the step graph
+            with graphed_tail.no_capture():       # no graphs of their own inside the step graph
                 pred = self.model(data)
         finally:
             node_ops.valid_rows = None

@@ -23,7 +23,7 @@ for m in model.modules():
 model.train()
 dev={k:(v.cuda() if torch.is_tensor(v) else v) for k,v in batch.items() if k not in ("cell","pbc")}
 mk=lambda: Data(**{k:(v.clone() if torch.is_tensor(v) else v) for k,v in dev.items()})
-with graphed_tail.eager():
+with graphed_tail.no_capture():
     d=mk(); pred=model(d); loss=model.loss(pred, d.y, get_head_indices(model,d))[0]
     print("eager loss", float(loss.detach()))
     class Opt: param_groups=[{"capturable":True}]; state={}
@@ -52,7 +52,7 @@ with graphed_tail.eager():
 from hydragnn.ops import node as nd
 layer=model.graph_convs[0]
 d_a=mk(); d_b=static["data"]
-with graphed_tail.eager(), torch.no_grad():
+with graphed_tail.no_capture(), torch.no_grad():
     xa,_,ca=model._embedding(d_a); ca["cu_seqlens"]=model._attention_segments(d_a, xa.size(0), xa.device)
     xb,_,cb=model._embedding(d_b); cb["cu_seqlens"]=model._attention_segments(d_b, xb.size(0), xb.device)
     print("embed diff", float((xa-xb[:N]).abs().max()))
