@@ -40,12 +40,8 @@ def _no_dropout(model):
             m.dropout = 0.0
 
 
-@pytest.mark.parametrize("workload", ["schnet_qm9", "egnn_gps_zinc"])
-def test_step_graph_matches_eager_training(libhgk, workload):
+def _setup(workload):
     from hydragnn.models import create_model
-    from hydragnn.train import train_step
-    from hydragnn.train.step_graph import BucketedStepGraph
-    from hydragnn.utils.distributed import get_distributed_model
 
     torch.backends.cuda.matmul.allow_tf32 = False
     # eight graphs per batch, every batch a different draw: N and E vary inside and across buckets
@@ -55,34 +51,61 @@ def test_step_graph_matches_eager_training(libhgk, workload):
     base = create_model(**arch).cuda()
     _no_dropout(base)
     base.train()
+    return base, batches
 
-    def run(use_graph):
-        model = get_distributed_model(copy.deepcopy(base))
-        opt = torch.optim.AdamW(model.module.parameters(), lr=1e-3, fused=True, capturable=True)
-        sg = BucketedStepGraph(model, opt, node_bucket=32, edge_bucket=256) if use_graph else None
-        losses = []
-        for rep in range(2):
-            for make in batches:
-                data = make()
-                if use_graph:
-                    assert sg.eligible(data), "step graph not eligible"
-                    loss, _ = sg.step(data)
-                else:
-                    loss, _ = train_step(model, opt, data)
-                losses.append(float(loss))
-        return losses, {k: v.detach().cpu() for k, v in model.module.state_dict().items()}, sg
 
-    eager_losses, eager_state, _ = run(False)
-    graph_losses, graph_state, sg = run(True)
-    assert sg.replays == len(graph_losses) and sg.eager_steps == 0
+def _runner(base, use_graph, lr):
+    from hydragnn.train import train_step
+    from hydragnn.train.step_graph import BucketedStepGraph
+    from hydragnn.utils.distributed import get_distributed_model
+
+    model = get_distributed_model(copy.deepcopy(base))
+    opt = torch.optim.AdamW(model.module.parameters(), lr=lr, fused=True, capturable=True)
+    sg = BucketedStepGraph(model, opt, node_bucket=32, edge_bucket=256) if use_graph else None
+
+    def step(data):
+        if use_graph:
+            assert sg.eligible(data), "step graph not eligible"
+            return sg.step(data)[0]
+        return train_step(model, opt, data)[0]
+    return model, sg, step
+
+
+@pytest.mark.parametrize("workload", ["schnet_qm9", "egnn_gps_zinc"])
+def test_step_graph_gradients_match_eager(libhgk, workload):
+    """Learning rate 0 (the weights stay put): every batch, first through a freshly captured graph and again
+    through its replay, must give the eager step's loss (rel 1e-5) and gradients."""
+    base, batches = _setup(workload)
+    model_e, _, step_e = _runner(base, False, 0.0)
+    model_g, sg, step_g = _runner(base, True, 0.0)
+    for rep in range(2):
+        for make in batches:
+            le, lg = float(step_e(make())), float(step_g(make()))
+            assert abs(lg - le) <= 1e-5 * abs(le) + 1e-7, (rep, le, lg)
+            ge = {n: p.grad.detach().clone() for n, p in model_e.module.named_parameters() if p.grad is not None}
+            gg = {n: p.grad.detach().clone() for n, p in model_g.module.named_parameters() if p.grad is not None}
+            assert set(ge) == set(gg)
+            floor = 1e-6 * max(float(g.abs().max()) for g in ge.values())
+            for n, g in ge.items():
+                scale = float(g.abs().max())
+                torch.testing.assert_close(gg[n], g, rtol=1e-4, atol=max(1e-4 * scale, floor), msg=lambda m, n=n: f"{n}: {m}")
+    assert sg.replays == 12 and sg.eager_steps == 0
     assert 1 <= sg.captures < len(batches) + 1                      # buckets are shared between batches
-    # the first step starts from identical weights: fp32 rel 1e-5; later steps compound rounding
-    # differences through AdamW (g / sqrt(v) amplifies them for small gradients)
-    assert abs(graph_losses[0] - eager_losses[0]) <= 1e-5 * abs(eager_losses[0]) + 1e-7
-    np.testing.assert_allclose(graph_losses, eager_losses, rtol=2e-4, atol=1e-6)
-    for k, v in eager_state.items():
-        if v.is_floating_point():
-            scale = float(v.abs().max())
-            torch.testing.assert_close(graph_state[k], v, rtol=1e-3, atol=2e-4 * max(scale, 1e-3), msg=lambda m, k=k: f"{k}: {m}")
-        else:
-            assert torch.equal(graph_state[k], v), k
+
+
+@pytest.mark.parametrize("workload", ["schnet_qm9", "egnn_gps_zinc"])
+def test_step_graph_training_tracks_eager(libhgk, workload):
+    """Real optimisation steps: the two trajectories start together (first losses rel 1e-5) and stay close;
+    they may drift apart slowly -- AdamW turns rounding-level differences of near-zero gradients into
+    full-size updates -- so the later steps are held to 1 % only."""
+    base, batches = _setup(workload)
+    _, _, step_e = _runner(base, False, 1e-3)
+    _, sg, step_g = _runner(base, True, 1e-3)
+    eager, graph = [], []
+    for rep in range(2):
+        for make in batches:
+            eager.append(float(step_e(make())))
+            graph.append(float(step_g(make())))
+    assert abs(graph[0] - eager[0]) <= 1e-5 * abs(eager[0]) + 1e-7
+    np.testing.assert_allclose(graph[:3], eager[:3], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(graph, eager, rtol=1e-2, atol=1e-5)
