@@ -41,7 +41,7 @@ def _roundup(n, m):
 
 
 class _Entry:
-    __slots__ = ("static", "graph", "loss", "tasks", "uses", "launches")
+    __slots__ = ("static", "graph", "loss", "tasks", "uses", "launches", "grads")
 
 
 class BucketedStepGraph:
@@ -276,6 +276,9 @@ class BucketedStepGraph:
             entry.loss, entry.tasks = self._body(entry.static)
         entry.launches = _hgk.stats.launches() - before      # libhgk kernels inside one replay
         entry.graph = graph
+        # the gradient buffers this graph writes (allocated inside its capture); after a replay the
+        # parameters' .grad are pointed back at them, so that `.grad` is what the step just computed
+        entry.grads = [(p, p.grad) for p in self.core.parameters() if p.grad is not None]
         self.captures += 1
         return entry
 
@@ -296,6 +299,8 @@ class BucketedStepGraph:
             entry = self.entries[key] = self._capture(data, padded, key)
         self._fill(entry.static, data, padded, key)
         entry.graph.replay()
+        for p, g in entry.grads:
+            p.grad = g
         entry.uses += 1
         self.replays += 1
         _hgk.stats.replayed += entry.launches
