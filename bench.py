@@ -301,8 +301,8 @@ def measure(args, workload, ctx, headline):
     # whole-step CUDA graphs over size buckets: the small-molecule configs, whose step is 1-3 ms of kernels
     # behind 5-13 ms of host work.  Single rank, no force loss (train/step_graph.py says what is eligible).
     want_sg = args.step_graph == "on" or (args.step_graph == "auto" and not headline
-                                          and workload in ("schnet_qm9", "egnn_gps_zinc"))
-    want_sg = want_sg and world == 1 and not forces
+                                          and workload in ("schnet_qm9", "egnn_gps_zinc", "painn_oc20_forces"))
+    want_sg = want_sg and world == 1
     optimizer = torch.optim.AdamW(model.module.parameters(), lr=1e-3, fused=True, capturable=want_sg)
     model.train()
     step_graph = None
@@ -322,13 +322,13 @@ def measure(args, workload, ctx, headline):
 
     def step_resident():
         if step_graph is not None:
-            return step_graph.step(fresh(resident))[0]
+            return step_graph.step(fresh(resident), compute_grad_energy=forces)[0]
         return train_step(model, optimizer, fresh(resident), compute_grad_energy=forces)[0]
 
     def step_e2e():
         data = to_data(pinned, device, Data, non_blocking=True)
         if step_graph is not None:
-            loss = step_graph.step(data)[0]
+            loss = step_graph.step(data, compute_grad_energy=forces)[0]
         else:
             loss = train_step(model, optimizer, data, compute_grad_energy=forces)[0]
         return float(loss)          # device -> host read of the step's result

@@ -18,9 +18,10 @@ whole step -- forward, loss, backward, optimizer -- is captured once per SIZE BU
     Shapes are static per bucket, batch-dependent values (sizes, offsets, scale) are device tensors.
 
 A stream of random mini-batches of a molecular dataset hits a handful of buckets (sum of 64 molecule
-sizes: +-2 %), each captured on first use.  Eligible: single-rank training without the force loss,
-mse / mae losses, SchNet / EGNN / PAINN stacks (their per-node normalisation, if any, is the GPS
-block's, which honours `valid_rows`); everything else runs the eager `train_step`.
+sizes: +-2 %), each captured on first use.  Eligible: single-rank training, mse / mae losses, SchNet /
+EGNN / PAINN stacks (their per-node normalisation, if any, is the GPS block's, which honours
+`valid_rows`), with or without the energy + force loss (the double backward is captured like
+everything else; not through a GPS layer); everything else runs the eager `train_step`.
 
 Opt in with `HYDRAGNN_STEP_GRAPH=1` (train loop) or `BucketedStepGraph(model, optimizer)` directly.
 """
@@ -56,8 +57,11 @@ class BucketedStepGraph:
     # ----------------------------------------------------------------------------- eligibility ---
     def eligible(self, data, compute_grad_energy=False):
         core = self.core
-        if compute_grad_energy or not torch.cuda.is_available():
+        if not torch.cuda.is_available():
             return False
+        if compute_grad_energy and (core.use_global_attn or core.num_heads != 1 or core.head_type[0] != "node"
+                                    or getattr(data, "energy", None) is None or getattr(data, "forces", None) is None):
+            return False            # the force loss through a GPS layer differentiates attention twice: eager
         if getattr(self.model, "averager", None) is not None and self.model.averager.enabled:
             return False                                    # gradient all-reduce: eager path
         if core.loss_function_type not in ("mse", "mae") or core.var_output or core.num_branches > 1:
@@ -79,7 +83,7 @@ class BucketedStepGraph:
                 return False
         if not data.pos.is_cuda:
             return False
-        return len(self.entries) < self.max_entries or self._key_of(data) in self.entries
+        return len(self.entries) < self.max_entries or self._key_of(data, compute_grad_energy) in self.entries
 
     # ------------------------------------------------------------------------------- padding ---
     def _own_graph(self):
@@ -96,14 +100,14 @@ class BucketedStepGraph:
             cached = data._step_graph_edges = g["edge_index"]
         return cached
 
-    def _key_of(self, data):
+    def _key_of(self, data, forces=False):
         N, B = data.pos.size(0), int(data.num_graphs)
         E = self._edges_of(data).size(1)
-        return (_roundup(N + 2, self.node_bucket), _roundup(max(E, 1), self.edge_bucket), B)
+        return (_roundup(N + 2, self.node_bucket), _roundup(max(E, 1), self.edge_bucket), B, bool(forces))
 
     def _pad(self, data, key):
         """-> dict of padded tensors (+ masks, scale) for bucket `key`; all on the device."""
-        N_b, E_b, B = key
+        N_b, E_b, B, forces = key
         dev = data.pos.device
         N = data.pos.size(0)
         ei = self._edges_of(data)
@@ -134,10 +138,9 @@ class BucketedStepGraph:
         out["ptr"] = torch.cat([ptr, torch.full((1,), N_b, dtype=ptr.dtype, device=dev)])
         out["cu_seqlens"] = torch.tensor([0, N, N_b], dtype=torch.int32).to(dev, non_blocking=True)
         out["valid_rows"] = torch.tensor([N], dtype=torch.int64).to(dev, non_blocking=True)
-        # targets: the real ones; pad entries are filled inside the graph
-        out["y"] = data.y
-        if getattr(data, "y_loc", None) is not None:
-            out["y_loc"] = data.y_loc
+        if forces:      # energy per graph / force per node, pad entries zero (replaced inside the graph)
+            out["energy"] = torch.cat([data.energy.reshape(-1).float(), torch.zeros(1, device=dev)])
+            out["forces"] = torch.cat([data.forces.float(), torch.zeros((P, 3), device=dev)])
         return out
 
     # -------------------------------------------------------------------------- the step body ---
@@ -159,6 +162,30 @@ class BucketedStepGraph:
             tasks.append(term)
         return total, tasks
 
+    def _masked_force_loss(self, pred, static):
+        """Base.energy_force_loss (Base.py:582-636 of the reference) over the padded batch: the pad graph's
+        energy and the pad nodes' forces are replaced by their own detached predictions, means rescaled."""
+        from ..graph import pool_topo
+        from ..ops import segment_sum
+
+        core, data = self.core, static["data"]
+        fn = core.loss_function
+        n_graphs, n_nodes = static["B"].to(torch.float32), static["valid_rows"].to(torch.float32)
+        e_pred = segment_sum(pred[0], pool_topo(data, pred[0].size(0)), 0).squeeze(-1).float()       # [B + 1]
+        rows_g, rows_n = e_pred.size(0), data.pos.size(0)
+        keep_g = torch.arange(rows_g, device=e_pred.device) < static["B"]
+        e_true = static["energy"]
+        w_e = core.loss_weights[0]
+        energy_loss = fn(e_pred, torch.where(keep_g, e_true, e_pred.detach())) * (rows_g / n_graphs).squeeze()
+        f_pred = -torch.autograd.grad(e_pred, data.pos, grad_outputs=torch.ones_like(e_pred), retain_graph=True,
+                                      create_graph=True)[0].float()
+        keep_n = (torch.arange(rows_n, device=e_pred.device) < static["valid_rows"]).unsqueeze(1)
+        f_true = static["forces"]
+        force_loss = fn(f_pred, torch.where(keep_n, f_true, f_pred.detach())) * (rows_n / n_nodes).squeeze()
+        # weight: mean |E_true| / (mean |F_true| + 1e-8) over the real entries (pad entries are zero)
+        w_f = w_e * (e_true.abs().sum() / n_graphs.squeeze()) / (f_true.abs().sum() / (3.0 * n_nodes.squeeze()) + 1e-8)
+        return energy_loss * w_e + force_loss * w_f, [energy_loss]
+
     def _body(self, static):
         from ..globalAtt import graphed_tail
         data = static["data"]
@@ -168,7 +195,10 @@ class BucketedStepGraph:
                 pred = self.model(data)
         finally:
             node_ops.valid_rows = None
-        loss, tasks = self._masked_loss(pred, static)
+        if static["forces"] is not None:
+            loss, tasks = self._masked_force_loss(pred, static)
+        else:
+            loss, tasks = self._masked_loss(pred, static)
         loss.backward()
         self.optimizer.step()
         return loss.detach(), [t.detach() for t in tasks]
@@ -178,7 +208,9 @@ class BucketedStepGraph:
         """Per head, the target rows in the padded layout ([B + 1, d] for graph heads, [N_b, d] for node
         heads), real rows first; pad rows zero (they are replaced inside the graph)."""
         core = self.core
-        N_b, _, B = key
+        N_b, _, B, forces = key
+        if forces:
+            return []
         head_index = get_head_indices(self.model, data)
         out = []
         for ihead, kind in enumerate(core.head_type):
@@ -192,7 +224,7 @@ class BucketedStepGraph:
 
     # ------------------------------------------------------------------------------- capture ---
     def _make_static(self, data, padded, key):
-        N_b, E_b, B = key
+        N_b, E_b, B, forces = key
         fields = {k: v.clone() for k, v in padded.items() if k in _NODE + _EDGE + ("edge_index", "batch", "ptr")}
         fields["num_graphs"] = B + 1
         sd = Data(**fields)
@@ -201,7 +233,11 @@ class BucketedStepGraph:
         sd.gps_cu_seqlens._hgk_bounds = None
         static = {"data": sd, "valid_rows": padded["valid_rows"].clone(),
                   "B": torch.tensor([B], dtype=torch.int64, device=sd.pos.device),
-                  "targets": [t.clone() for t in self._targets(data, padded, key)]}
+                  "targets": [t.clone() for t in self._targets(data, padded, key)],
+                  "energy": padded["energy"].clone() if forces else None,
+                  "forces": padded["forces"].clone() if forces else None}
+        if forces:
+            sd.pos.requires_grad_(True)        # the static position buffer is the leaf the forces are taken at
         if self._own_graph():
             # the in-model RadiusInteractionGraph takes the graph from this cache instead of searching
             sd.pos._hgk_rgraph_static = sd.edge_index
@@ -209,9 +245,13 @@ class BucketedStepGraph:
 
     def _fill(self, static, data, padded, key):
         sd = static["data"]
-        for k in _NODE + _EDGE + ("edge_index", "batch", "ptr"):
-            if k in padded and getattr(sd, k, None) is not None:
-                getattr(sd, k).copy_(padded[k], non_blocking=True)
+        with torch.no_grad():
+            for k in _NODE + _EDGE + ("edge_index", "batch", "ptr"):
+                if k in padded and getattr(sd, k, None) is not None:
+                    getattr(sd, k).copy_(padded[k], non_blocking=True)
+            if static["forces"] is not None:
+                static["energy"].copy_(padded["energy"], non_blocking=True)
+                static["forces"].copy_(padded["forces"], non_blocking=True)
         sd.gps_cu_seqlens.copy_(padded["cu_seqlens"], non_blocking=True)
         static["valid_rows"].copy_(padded["valid_rows"], non_blocking=True)
         for dst, src in zip(static["targets"], self._targets(data, padded, key)):
@@ -264,12 +304,12 @@ class BucketedStepGraph:
         with torch.cuda.stream(side):
             for _ in range(self.warmup):                 # eager runs: allocator / lazy-init warm-up
                 self._clear_caches(entry.static)
-                self._zero_grad()
+                self._zero_grad(entry.static)
                 self._body(entry.static)
         torch.cuda.current_stream().wait_stream(side)
         self._restore(snap)
         self._clear_caches(entry.static)
-        self._zero_grad()
+        self._zero_grad(entry.static)
         graph = torch.cuda.CUDAGraph()
         before = _hgk.stats.launches()
         with torch.cuda.graph(graph):
@@ -282,9 +322,11 @@ class BucketedStepGraph:
         self.captures += 1
         return entry
 
-    def _zero_grad(self):
+    def _zero_grad(self, static=None):
         for p in self.core.parameters():
             p.grad = None
+        if static is not None and static["data"].pos.requires_grad:
+            static["data"].pos.grad = None
 
     # ---------------------------------------------------------------------------------- step ---
     def step(self, data, compute_grad_energy=False):
@@ -292,7 +334,7 @@ class BucketedStepGraph:
         if not self.eligible(data, compute_grad_energy):
             self.eager_steps += 1
             return train_step(self.model, self.optimizer, data, compute_grad_energy)
-        key = self._key_of(data)
+        key = self._key_of(data, compute_grad_energy)
         padded = self._pad(data, key)
         entry = self.entries.get(key)
         if entry is None:

@@ -24,8 +24,11 @@ def _batches(workload, sizes, seed=3):
         batch = syn.collate(graphs)
         if spec["edges"] == "radius":
             from hydragnn.ops import radius_graph
-            g = radius_graph(batch["pos"].cuda(), batch["ptr"], spec["radius"], spec["max_neighbours"], loop=False)
+            g = radius_graph(batch["pos"].cuda(), batch["ptr"], spec["radius"], spec["max_neighbours"], loop=False,
+                             cell=batch.get("cell") if spec["pbc"] else None, pbc=batch.get("pbc") if spec["pbc"] else None)
             batch["edge_index"] = g["edge_index"].cpu()
+            if spec["pbc"]:
+                batch["edge_shifts"] = g["edge_shifts"].cpu()
         batch = syn.finish_edges(batch)
         dev = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in batch.items() if k not in ("cell", "pbc")}
         out.append(lambda dev=dev: Data(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in dev.items()}))
@@ -44,8 +47,9 @@ def _setup(workload):
     from hydragnn.models import create_model
 
     torch.backends.cuda.matmul.allow_tf32 = False
-    # eight graphs per batch, every batch a different draw: N and E vary inside and across buckets
-    spec, batches = _batches(workload, [8, 8, 8, 8, 8, 8])
+    # eight (force workload: three) graphs per batch, every batch a different draw: N and E vary inside and
+    # across buckets
+    spec, batches = _batches(workload, [3] * 6 if workload == "painn_oc20_forces" else [8] * 6)
     arch = dict(spec["arch"], num_conv_layers=2)
     torch.manual_seed(0)
     base = create_model(**arch).cuda()
@@ -54,7 +58,7 @@ def _setup(workload):
     return base, batches
 
 
-def _runner(base, use_graph, lr):
+def _runner(base, use_graph, lr, forces=False):
     from hydragnn.train import train_step
     from hydragnn.train.step_graph import BucketedStepGraph
     from hydragnn.utils.distributed import get_distributed_model
@@ -65,19 +69,21 @@ def _runner(base, use_graph, lr):
 
     def step(data):
         if use_graph:
-            assert sg.eligible(data), "step graph not eligible"
-            return sg.step(data)[0]
-        return train_step(model, opt, data)[0]
+            assert sg.eligible(data, forces), "step graph not eligible"
+            return sg.step(data, compute_grad_energy=forces)[0]
+        return train_step(model, opt, data, compute_grad_energy=forces)[0]
     return model, sg, step
 
 
-@pytest.mark.parametrize("workload", ["schnet_qm9", "egnn_gps_zinc"])
+@pytest.mark.parametrize("workload", ["schnet_qm9", "egnn_gps_zinc", "painn_oc20_forces"])
 def test_step_graph_gradients_match_eager(libhgk, workload):
     """Learning rate 0 (the weights stay put): every batch, first through a freshly captured graph and again
-    through its replay, must give the eager step's loss (rel 1e-5) and gradients."""
+    through its replay, must give the eager step's loss (rel 1e-5) and gradients.  The PaiNN case runs the
+    energy + force loss: the captured step contains the double backward."""
+    forces = workload == "painn_oc20_forces"
     base, batches = _setup(workload)
-    model_e, _, step_e = _runner(base, False, 0.0)
-    model_g, sg, step_g = _runner(base, True, 0.0)
+    model_e, _, step_e = _runner(base, False, 0.0, forces)
+    model_g, sg, step_g = _runner(base, True, 0.0, forces)
     for rep in range(2):
         for make in batches:
             le, lg = float(step_e(make())), float(step_g(make()))
