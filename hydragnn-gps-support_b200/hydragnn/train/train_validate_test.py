@@ -84,6 +84,27 @@ def train_step(model, optimizer, data, compute_grad_energy=False, head_index=Non
     return loss.detach(), tasks_loss
 
 
+def _step_graph_for(model, opt):
+    """One BucketedStepGraph per (model, optimizer), kept on the model object.  The optimizer is switched
+    to its capturable form (device-side step counter) before its first step."""
+    from .step_graph import BucketedStepGraph
+
+    sg = getattr(model, "_hgk_step_graph", None)
+    if sg is None or sg.optimizer is not opt:
+        if not opt.state:
+            for group in opt.param_groups:
+                if "capturable" in group:
+                    group["capturable"] = True
+        sg = BucketedStepGraph(model, opt, node_bucket=int(os.getenv("HYDRAGNN_STEP_GRAPH_NODES", "64")),
+                               edge_bucket=int(os.getenv("HYDRAGNN_STEP_GRAPH_EDGES", "1024")),
+                               max_entries=int(os.getenv("HYDRAGNN_STEP_GRAPH_MAX", "64")))
+        try:
+            model._hgk_step_graph = sg
+        except Exception:
+            pass
+    return sg
+
+
 def _reduce_mean(values):
     size, _ = get_comm_size_and_rank()
     if size > 1:
@@ -100,11 +121,15 @@ def train(loader, model, opt, verbosity=0, profiler=None, use_deepspeed=False, c
     tasks = torch.zeros(core.num_heads, device=device)
     seen = 0
     max_batches = int(os.getenv("HYDRAGNN_MAX_NUM_BATCH", "0")) or None
+    step_graph = _step_graph_for(model, opt) if os.getenv("HYDRAGNN_STEP_GRAPH", "0") == "1" else None
     for ibatch, data in enumerate(loader):
         if max_batches is not None and ibatch >= max_batches:
             break
         data = data.to(device)
-        loss, tasks_loss = train_step(model, opt, data, compute_grad_energy)
+        if step_graph is not None:      # whole steps replayed as CUDA graphs over size buckets (step_graph.py)
+            loss, tasks_loss = step_graph.step(data, compute_grad_energy)
+        else:
+            loss, tasks_loss = train_step(model, opt, data, compute_grad_energy)
         n = _num_graphs(data)
         total += loss * n
         for k, t in enumerate(tasks_loss):

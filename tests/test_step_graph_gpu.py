@@ -115,3 +115,26 @@ def test_step_graph_training_tracks_eager(libhgk, workload):
     assert abs(graph[0] - eager[0]) <= 1e-5 * abs(eager[0]) + 1e-7
     np.testing.assert_allclose(graph[:3], eager[:3], rtol=1e-4, atol=1e-6)
     np.testing.assert_allclose(graph, eager, rtol=1e-2, atol=1e-5)
+
+
+def test_run_training_with_step_graphs(libhgk, tmp_path, monkeypatch):
+    """hydragnn.run_training / run_prediction on the CI toy with HYDRAGNN_STEP_GRAPH=1 (tiny graphs of 2-8 atoms,
+    batch 32: many size buckets, a ragged last batch) reaches the reference's accuracy gate."""
+    import os
+
+    import hydragnn
+    import toy_data
+    from test_run_training_gpu import CI_CONFIG
+
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.setenv("SERIALIZED_DATA_PATH", str(tmp_path))
+    monkeypatch.setenv("HYDRAGNN_STEP_GRAPH", "1")
+    monkeypatch.setenv("HYDRAGNN_STEP_GRAPH_NODES", "32")
+    monkeypatch.setenv("HYDRAGNN_STEP_GRAPH_EDGES", "128")
+    for split, count, seed in (("train", 350, 1), ("test", 75, 2), ("validate", 75, 3)):
+        toy_data.generate(os.path.join(tmp_path, "dataset", f"unit_test_singlehead_{split}"), count, seed)
+    config = copy.deepcopy(CI_CONFIG)
+    config["NeuralNetwork"]["Architecture"]["mpnn_type"] = "SchNet"
+    hydragnn.run_training(copy.deepcopy(config))
+    error, task_errors, true_values, predicted = hydragnn.run_prediction(copy.deepcopy(config))
+    assert torch.sqrt(torch.mean((true_values[0] - predicted[0]) ** 2)).item() < 0.20
