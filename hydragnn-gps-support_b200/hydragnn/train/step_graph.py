@@ -53,6 +53,10 @@ class BucketedStepGraph:
         self.max_entries, self.warmup = max_entries, warmup
         self.entries = {}
         self.replays = self.captures = self.eager_steps = 0
+        # The captured optimizer step must not bake the learning rate in as a constant (schedulers change
+        # it): while capturing, the param groups carry the rate as a device tensor; before a replay the
+        # tensor is refreshed from the (host) value the scheduler left in the group.
+        self._lr_dev, self._lr_host = None, None
 
     # ----------------------------------------------------------------------------- eligibility ---
     def eligible(self, data, compute_grad_energy=False):
@@ -298,6 +302,18 @@ class BucketedStepGraph:
         entry = _Entry()
         entry.static = self._make_static(data, padded, key)
         entry.uses = 0
+        lr_dev = self._lr_tensors(data.pos.device)
+        self._sync_lr()
+        host_lr = [g["lr"] for g in self.optimizer.param_groups]
+        for g, t in zip(self.optimizer.param_groups, lr_dev):
+            g["lr"] = t
+        try:
+            return self._capture_with_tensor_lr(entry, data, padded, key)
+        finally:
+            for g, v in zip(self.optimizer.param_groups, host_lr):
+                g["lr"] = v
+
+    def _capture_with_tensor_lr(self, entry, data, padded, key):
         snap = self._snapshot()
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
@@ -322,6 +338,21 @@ class BucketedStepGraph:
         self.captures += 1
         return entry
 
+    def _lr_tensors(self, device):
+        if self._lr_dev is None:
+            self._lr_host = [float(g["lr"]) for g in self.optimizer.param_groups]
+            self._lr_dev = [torch.tensor(v, dtype=torch.float32, device=device) for v in self._lr_host]
+        return self._lr_dev
+
+    def _sync_lr(self):
+        if self._lr_dev is None:
+            return
+        for k, g in enumerate(self.optimizer.param_groups):
+            v = float(g["lr"])
+            if v != self._lr_host[k]:
+                self._lr_dev[k].fill_(v)
+                self._lr_host[k] = v
+
     def _zero_grad(self, static=None):
         for p in self.core.parameters():
             p.grad = None
@@ -340,6 +371,7 @@ class BucketedStepGraph:
         if entry is None:
             entry = self.entries[key] = self._capture(data, padded, key)
         self._fill(entry.static, data, padded, key)
+        self._sync_lr()
         entry.graph.replay()
         for p, g in entry.grads:
             p.grad = g
