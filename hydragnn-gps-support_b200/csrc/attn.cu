@@ -235,6 +235,7 @@ k_attn_delta(const float* __restrict__ dout, int64_t lddo, const float* __restri
 struct AttnBwdArgs {
   const float* dout; int64_t lddo;
   const float* lse; const float* delta;
+  int64_t ldg;                       // row stride of dq / dk / dv (floats)
 };
 
 // ---------------------------------------------------- backward: dK, dV --
@@ -299,7 +300,7 @@ k_attn_bwd_kv(const AttnArgs p, const AttnBwdArgs b, float* __restrict__ dk, flo
       for (int jj = 0; jj < JJ; ++jj) {
         const int col = tx + 16 * jj;
         if (col < p.D) {
-          const int64_t off = ((int64_t)row * p.H + h) * p.D + col;
+          const int64_t off = (int64_t)row * b.ldg + h * p.D + col;
           dk[off] = adk[i][jj] * p.scale;
           dv[off] = adv[i][jj];
         }
@@ -367,7 +368,7 @@ k_attn_bwd_q(const AttnArgs p, const AttnBwdArgs b, float* __restrict__ dq) {
 #pragma unroll
       for (int jj = 0; jj < JJ; ++jj) {
         const int col = tx + 16 * jj;
-        if (col < p.D) dq[((int64_t)row * p.H + h) * p.D + col] = adq[i][jj] * p.scale;
+        if (col < p.D) dq[(int64_t)row * b.ldg + h * p.D + col] = adq[i][jj] * p.scale;
       }
     }
   }
@@ -398,7 +399,7 @@ namespace hgk {
 int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, const float* k,
                 int64_t ldk, const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N,
                 int32_t H, int32_t D, float scale, cudaStream_t st);
-int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float* dout, int64_t lddo,
+int attn_bwd_tc(float* dq, float* dk, float* dv, int64_t ldg, const float* delta, const float* dout, int64_t lddo,
                 const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
                 const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
                 int32_t D, float scale, cudaStream_t st);
@@ -446,8 +447,8 @@ extern "C" int hgk_attn_varlen_fwd(float* o, int64_t ldo, float* lse, const floa
   return check_launch("attn_varlen_fwd");
 }
 
-extern "C" int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta,
-                                   const float* dout, int64_t lddo, const float* o, int64_t ldo,
+extern "C" int hgk_attn_varlen_bwd_ld(float* dq, float* dk, float* dv, int64_t ldg, float* delta,
+                                      const float* dout, int64_t lddo, const float* o, int64_t ldo,
                                    const float* lse, const float* q, int64_t ldq, const float* k,
                                    int64_t ldk, const float* v, int64_t ldv,
                                    const int32_t* cu_seqlens, int64_t S, int64_t N, int32_t H,
@@ -456,13 +457,14 @@ extern "C" int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta
   if (rc) return rc;
   if (N == 0) return HGK_OK;
   HGK_REQUIRE(dq && dk && dv && delta && dout && o && lse, "attn_varlen_bwd: NULL operand");
+  HGK_REQUIRE(ldg >= (int64_t)H * D, "attn_varlen_bwd: gradient row stride %lld < H*D", (long long)ldg);
   const int Dp = (D + 3) / 4 * 4;
   AttnArgs a{q, ldq, k, ldk, v, ldv, cu_seqlens, (int32_t)S, N, H, D, Dp, scale};
-  AttnBwdArgs b{dout, lddo, lse, delta};
+  AttnBwdArgs b{dout, lddo, lse, delta, ldg};
   cudaStream_t st = (cudaStream_t)stream;
   k_attn_delta<<<(unsigned)ceil_div(N * H, 256), 256, 0, st>>>(dout, lddo, o, ldo, delta, N, H, D);
   if (!attn_force_simt()) {
-    rc = attn_bwd_tc(dq, dk, dv, delta, dout, lddo, lse, q, ldq, k, ldk, v, ldv, cu_seqlens, S, N, H, D, scale, st);
+    rc = attn_bwd_tc(dq, dk, dv, ldg, delta, dout, lddo, lse, q, ldq, k, ldk, v, ldv, cu_seqlens, S, N, H, D, scale, st);
     if (rc <= 0) return rc;
   }
   dim3 grid((unsigned)(ceil_div(N, kTile) + S), (unsigned)H);
@@ -477,4 +479,14 @@ extern "C" int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta
     k_attn_bwd_q<JJ><<<grid, kAttnThreads, smem_q, st>>>(a, b, dq);
   });
   return check_launch("attn_varlen_bwd");
+}
+
+extern "C" int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta,
+                                   const float* dout, int64_t lddo, const float* o, int64_t ldo,
+                                   const float* lse, const float* q, int64_t ldq, const float* k,
+                                   int64_t ldk, const float* v, int64_t ldv,
+                                   const int32_t* cu_seqlens, int64_t S, int64_t N, int32_t H,
+                                   int32_t D, float scale, void* stream) {
+  return hgk_attn_varlen_bwd_ld(dq, dk, dv, (int64_t)H * D, delta, dout, lddo, o, ldo, lse, q, ldq, k, ldk, v, ldv,
+                                cu_seqlens, S, N, H, D, scale, stream);
 }

@@ -215,7 +215,9 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   constexpr int G = kFwdGroups;
   constexpr int BK = 32;                               // keys per pipeline step
   constexpr int NST = 2 * G;                           // shared-memory stages
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(1024) float smem_raw[];
+  // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar[G + 1];         // [g]: scores of group g are ready; [G]: everything done
   __shared__ uint32_t tmem_slot;
   int32_t seg_beg, seg_end, row0;
@@ -225,7 +227,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   const bool issuer = warp_u == G * kFwdGroup / 32;    // the last warp
 
   constexpr int kTile = BK * D;
-  constexpr int kStage = 4 * kTile;                    // K rows hi/lo, V^T hi/lo
+  constexpr int kStage = 4 * kTile;                    // K rows hi/lo (K-major), V rows hi/lo (MN-major: B = V^T)
   constexpr int oKhi = 0, oKlo = kTile, oVThi = 2 * kTile, oVTlo = 3 * kTile;
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColS = 0, kColPlo = G * BK, kColO = 2 * G * BK, kColQhi = 2 * G * BK + G * D,
@@ -240,11 +242,11 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BK - 1) / BK;
   constexpr uint32_t kIdescS = idesc_tf32(BM, BK);
-  constexpr uint32_t kIdescO = idesc_tf32(BM, D);
+  constexpr uint32_t kIdescO = idesc_tf32(BM, D) | kIdescBMajorMN;
 
   if (issuer) {
     const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo);
-    const OperandDesc dVt = operand_desc<BK>(smem + oVThi, smem + oVTlo);
+    const OperandDesc dVt = operand_desc_mn(smem + oVThi, smem + oVTlo);
     auto at_stage = [](const OperandDesc& d, int st) {
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
@@ -264,8 +266,8 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
       named_bar_sync(2 + g, kFwdGroup + 32);           // P_s is in TMEM, stage of step s+G is written
       fence_after_sync();
       if (elect_one_sync()) {
-        mma3_ts<BK>(tmem + kColO + (uint32_t)g * D, tmem + kColS + (uint32_t)g * BK, tmem + kColPlo + (uint32_t)g * BK,
-                    at_stage(dVt, s % NST), kIdescO, ((s / G) % kPromote) != 0);   // O_g (+)= P_s V_s
+        mma3_ts_mn<BK>(tmem + kColO + (uint32_t)g * D, tmem + kColS + (uint32_t)g * BK, tmem + kColPlo + (uint32_t)g * BK,
+                       at_stage(dVt, s % NST), kIdescO, ((s / G) % kPromote) != 0);   // O_g (+)= P_s V_s
         if (s + G < nsub) issue_scores(s + G);
         mma_commit(&bar[g]);
         if (s == nsub - 1) mma_commit(&bar[G]);
@@ -290,7 +292,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
     auto stage = [&](int st) {
       float* base = smem + st * kStage;
       tk.store_rows_as(tl, base + oKhi, base + oKlo);
-      tv.store_transposed_as(tl, base + oVThi, base + oVTlo);
+      tv.store_mn_as(tl, base + oVThi, base + oVTlo);
     };
     if (g < nsub) { load(seg_beg + g * BK); stage(g); }
     fence_smem_to_async();
@@ -444,6 +446,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
 struct AttnTcBwdArgs {
   const float* dout; int64_t lddo;
   const float* lse; const float* delta;
+  int64_t ldg;                       // row stride of dq / dk / dv (floats)
 };
 
 // ---- dQ: CTA owns 128 queries, loops over 64-key tiles ---------------------------------------
@@ -548,7 +551,7 @@ k_attn_bwd_q_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ d
 
   // tcgen05.ld is warp-collective (.sync.aligned): every thread loads, valid rows store
   constexpr int DH = D / 2;
-  float* drow = dq + ((int64_t)row * p.H + h) * D + cs.half * DH;
+  float* drow = dq + (int64_t)row * b.ldg + h * D + cs.half * DH;
   uint32_t t[16];
 #pragma unroll
   for (int c0 = 0; c0 < DH; c0 += 16) {
@@ -712,7 +715,7 @@ k_attn_bwd_kv_tc(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ 
   if (ok) {
     // Q was staged as q * scale * log2(e):  dK = scale * dS^T Q = (dS^T Q_staged) * ln 2
     const float mul = is_k ? kLn2 : 1.f;
-    float* orow = (is_k ? dk : dv) + ((int64_t)krow * p.H + h) * D + chalf * EC;
+    float* orow = (is_k ? dk : dv) + (int64_t)krow * b.ldg + h * D + chalf * EC;
 #pragma unroll
     for (int j = 0; j < EC; j += 4)
       *reinterpret_cast<float4*>(orow + j) =
@@ -767,10 +770,12 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   constexpr int BQ = 32;                               // queries per pipeline step
   constexpr int QC = BQ / 2;                           // query columns per thread
   constexpr int NST = 4;                               // shared-memory stages
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(1024) float smem_raw[];
+  // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
   __shared__ uint32_t tmem_slot;
-  __shared__ float lse2_s[NST][BQ], delta_s[NST][BQ];
+  __shared__ __align__(16) float lse2_s[NST][BQ], delta_s[NST][BQ];
   int32_t seg_beg, seg_end, key0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &key0)) return;
   const int h = blockIdx.y;
@@ -781,8 +786,8 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   constexpr int kStage = 8 * kTile;                    // floats per stage
   constexpr int oQhi = 0, oQlo = kTile;                // rows = queries (B of S^T)
   constexpr int oGhi = 2 * kTile, oGlo = 3 * kTile;    // dO rows        (B of dP^T)
-  constexpr int oQThi = 4 * kTile, oQTlo = 5 * kTile;  // Q^T [D x BQ]   (B of dK)
-  constexpr int oGThi = 6 * kTile, oGTlo = 7 * kTile;  // dO^T [D x BQ]  (B of dV)
+  constexpr int oQThi = 4 * kTile, oQTlo = 5 * kTile;  // Q rows, MN-major  (B = Q^T of dK)
+  constexpr int oGThi = 6 * kTile, oGTlo = 7 * kTile;  // dO rows, MN-major (B = dO^T of dV)
 
   constexpr uint32_t kCols = 512;
   // one (dV, dK) accumulator pair per compute group: columns kColAcc + g * 2D (dV) and + D (dK); a group's
@@ -796,12 +801,12 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BQ - 1) / BQ;
   constexpr uint32_t kIdescS = idesc_tf32(BM, BQ);
-  constexpr uint32_t kIdescD = idesc_tf32(BM, D);
+  constexpr uint32_t kIdescD = idesc_tf32(BM, D) | kIdescBMajorMN;
 
   if (issuer) {
     // ------------------------------------------------------------------ MMA-issuing warp ---
     const OperandDesc dQ = operand_desc<D>(smem + oQhi, smem + oQlo), dG = operand_desc<D>(smem + oGhi, smem + oGlo);
-    const OperandDesc dQt = operand_desc<BQ>(smem + oQThi, smem + oQTlo), dGt = operand_desc<BQ>(smem + oGThi, smem + oGTlo);
+    const OperandDesc dQt = operand_desc_mn(smem + oQThi, smem + oQTlo), dGt = operand_desc_mn(smem + oGThi, smem + oGTlo);
     auto at_stage = [](const OperandDesc& d, int st) {   // start-address field is in 16-byte units
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
@@ -815,8 +820,8 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       const uint32_t set = (uint32_t)(s & 1) * BQ;
       const bool accumulate = ((s >> 1) % kPromote) != 0;
       const uint32_t acc = tmem + kColAcc + (uint32_t)(s & 1) * 2 * D;
-      mma3_ts<BQ>(acc, tmem + kColST + set, tmem + kColPlo + set, at_stage(dGt, s & (NST - 1)), kIdescD, accumulate);
-      mma3_ts<BQ>(acc + D, tmem + kColDPT + set, tmem + kColDSlo + set, at_stage(dQt, s & (NST - 1)), kIdescD, accumulate);
+      mma3_ts_mn<BQ>(acc, tmem + kColST + set, tmem + kColPlo + set, at_stage(dGt, s & (NST - 1)), kIdescD, accumulate);
+      mma3_ts_mn<BQ>(acc + D, tmem + kColDPT + set, tmem + kColDSlo + set, at_stage(dQt, s & (NST - 1)), kIdescD, accumulate);
     };
     named_bar_sync(1, kKvPipeThreads);                 // K / V rows are in TMEM, stages 0 and 1 are written
     fence_after_sync();
@@ -873,12 +878,12 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       float* base = smem + st * kStage;
       if (g == 0) {
         tq0.scale(qmul);
-        tq0.store_rows(base + oQhi, base + oQlo);  tq0.store_transposed(base + oQThi, base + oQTlo);
-        tg0.store_rows(base + oGhi, base + oGlo);  tg0.store_transposed(base + oGThi, base + oGTlo);
+        tq0.store_rows_and_mn_as(tl, base + oQhi, base + oQlo, base + oQThi, base + oQTlo);
+        tg0.store_rows_and_mn_as(tl, base + oGhi, base + oGlo, base + oGThi, base + oGTlo);
       } else {
         tq1.scale(qmul);
-        tq1.store_rows(base + oQhi, base + oQlo);  tq1.store_transposed(base + oQThi, base + oQTlo);
-        tg1.store_rows(base + oGhi, base + oGlo);  tg1.store_transposed(base + oGThi, base + oGTlo);
+        tq1.store_rows_and_mn_as(tl, base + oQhi, base + oQlo, base + oQThi, base + oQTlo);
+        tg1.store_rows_and_mn_as(tl, base + oGhi, base + oGlo, base + oGThi, base + oGTlo);
       }
       if (tl < BQ) {
         lse2_s[st][tl] = lse_r * kLog2e;
@@ -927,16 +932,28 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       tmem_ld16(tmem + cs.lane_base + kColDPT + set + col0, dp);
       tmem_ld_wait();
       KV_PROF(1)
+      if (nvalid < QC) {                               // the segment ends inside my columns: queries past the end
+#pragma unroll                                         // get score -inf, i.e. P = 0 and dS = 0
+        for (int j = 0; j < QC; ++j)
+          if (j >= nvalid) sv[j] = 0xff800000u;
+      }
+      // P and dS (hi, lo) of my 16 query columns; their lse / delta come from shared memory as 16-byte loads
 #pragma unroll
-      for (int j = 0; j < QC; ++j) {
-        float pj = fast_exp2(__uint_as_float(sv[j]) - lse2_s[st][col0 + j]);
-        if (j >= nvalid) pj = 0.f;
-        const float ds = pj * (__uint_as_float(dp[j]) - delta_s[st][col0 + j]);
-        float hi_, lo_;
-        split_tf32(pj, hi_, lo_);
-        sv[j] = __float_as_uint(hi_); plo[j] = __float_as_uint(lo_);
-        split_tf32(ds, hi_, lo_);
-        dp[j] = __float_as_uint(hi_); dslo[j] = __float_as_uint(lo_);
+      for (int j4 = 0; j4 < QC; j4 += 4) {
+        const float4 l4 = *reinterpret_cast<const float4*>(&lse2_s[st][col0 + j4]);
+        const float4 d4 = *reinterpret_cast<const float4*>(&delta_s[st][col0 + j4]);
+        const float lq[4] = {l4.x, l4.y, l4.z, l4.w}, dq_[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int j = j4 + jj;
+          const float pj = fast_exp2(__uint_as_float(sv[j]) - lq[jj]);
+          const float ds = pj * (__uint_as_float(dp[j]) - dq_[jj]);
+          float hi_, lo_;
+          split_tf32(pj, hi_, lo_);
+          sv[j] = __float_as_uint(hi_); plo[j] = __float_as_uint(lo_);
+          split_tf32(ds, hi_, lo_);
+          dp[j] = __float_as_uint(hi_); dslo[j] = __float_as_uint(lo_);
+        }
       }
       KV_PROF(2)
       tmem_st16(tmem + cs.lane_base + kColST + set + col0, sv);
@@ -983,7 +1000,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     }
     if (ok) {
       const float mul = is_k ? kLn2 : 1.f;             // Q was staged as q * scale * log2(e)
-      float* orow = (is_k ? dk : dv) + ((int64_t)krow * p.H + h) * D + chalf * EC;
+      float* orow = (is_k ? dk : dv) + (int64_t)krow * b.ldg + h * D + chalf * EC;
 #pragma unroll
       for (int j = 0; j < EC; j += 4)
         *reinterpret_cast<float4*>(orow + j) = make_float4(accv[j] * mul, accv[j + 1] * mul, accv[j + 2] * mul, accv[j + 3] * mul);
@@ -1001,7 +1018,9 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr int BK = 32;                               // keys per pipeline step
   constexpr int KC = BK / 2;                           // key columns per thread
   constexpr int NST = 4;                               // shared-memory stages
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(1024) float smem_raw[];
+  // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
   __shared__ uint32_t tmem_slot;
   int32_t seg_beg, seg_end, row0;
@@ -1014,7 +1033,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr int kStage = 6 * kTile;                    // floats per stage
   constexpr int oKhi = 0, oKlo = kTile;                // rows = keys    (B of S)
   constexpr int oVhi = 2 * kTile, oVlo = 3 * kTile;    // V rows         (B of dP)
-  constexpr int oKThi = 4 * kTile, oKTlo = 5 * kTile;  // K^T [D x BK]   (B of dQ)
+  constexpr int oKThi = 4 * kTile, oKTlo = 5 * kTile;  // K rows, MN-major (B = K^T of dQ)
 
   constexpr uint32_t kCols = 512;
   // one dQ accumulator per compute group (columns kColDQ + g * D): a group's chain of updates is then
@@ -1027,11 +1046,11 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BK - 1) / BK;
   constexpr uint32_t kIdescS = idesc_tf32(BM, BK);
-  constexpr uint32_t kIdescQ = idesc_tf32(BM, D);
+  constexpr uint32_t kIdescQ = idesc_tf32(BM, D) | kIdescBMajorMN;
 
   if (issuer) {
     const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo), dV = operand_desc<D>(smem + oVhi, smem + oVlo);
-    const OperandDesc dKt = operand_desc<BK>(smem + oKThi, smem + oKTlo);
+    const OperandDesc dKt = operand_desc_mn(smem + oKThi, smem + oKTlo);
     auto at_stage = [](const OperandDesc& d, int st) {
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
@@ -1055,8 +1074,8 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       fence_after_sync();
       if (elect_one_sync()) {
         const uint32_t set = (uint32_t)g * BK;
-        mma3_ts<BK>(tmem + kColDQ + (uint32_t)g * D, tmem + kColS + set, tmem + kColDP + set,
-                    at_stage(dKt, s & (NST - 1)), kIdescQ, ((s >> 1) % kPromote) != 0);
+        mma3_ts_mn<BK>(tmem + kColDQ + (uint32_t)g * D, tmem + kColS + set, tmem + kColDP + set,
+                       at_stage(dKt, s & (NST - 1)), kIdescQ, ((s >> 1) % kPromote) != 0);
         if (s + 2 < nsub) issue_scores(s + 2);
         mma_commit(&bar[g]);
         if (s == nsub - 1) mma_commit(&bar[2]);
@@ -1087,10 +1106,10 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     auto stage = [&](int st) {
       float* base = smem + st * kStage;
       if (g == 0) {
-        tk0.store_rows(base + oKhi, base + oKlo);  tk0.store_transposed(base + oKThi, base + oKTlo);
+        tk0.store_rows_and_mn_as((int)threadIdx.x, base + oKhi, base + oKlo, base + oKThi, base + oKTlo);
         tv0.store_rows(base + oVhi, base + oVlo);
       } else {
-        tk1.store_rows(base + oKhi, base + oKlo);  tk1.store_transposed(base + oKThi, base + oKTlo);
+        tk1.store_rows_and_mn_as((int)threadIdx.x - kKvGroup, base + oKhi, base + oKlo, base + oKThi, base + oKTlo);
         tv1.store_rows(base + oVhi, base + oVlo);
       }
     };
@@ -1125,11 +1144,15 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       tmem_ld16(tmem + cs.lane_base + kColS + set + col0, sv);
       tmem_ld16(tmem + cs.lane_base + kColDP + set + col0, dv);
       tmem_ld_wait();
+      if (nvalid < KC) {                               // the segment ends inside my columns: keys past the end
+#pragma unroll                                         // get score -inf, i.e. P = 0 and dS = 0
+        for (int j = 0; j < KC; ++j)
+          if (j >= nvalid) sv[j] = 0xff800000u;
+      }
 #pragma unroll
       for (int j = 0; j < KC; ++j) {
         const float pj = fast_exp2(__uint_as_float(sv[j]) - lse2);
-        float ds = pj * (__uint_as_float(dv[j]) - delta);
-        if (j >= nvalid) ds = 0.f;                     // keys past the segment end contribute nothing
+        const float ds = pj * (__uint_as_float(dv[j]) - delta);
         float hi_, lo_;
         split_tf32(ds, hi_, lo_);
         sv[j] = __float_as_uint(hi_);
@@ -1168,7 +1191,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       for (int j = 0; j < EC; ++j) acc[j] += __uint_as_float(t[j]) + (steps > kPromote ? tg[j * BM] : 0.f);
     }
     if (row_ok) {
-      float* drow = dq + ((int64_t)row * p.H + h) * D + part * EC;
+      float* drow = dq + (int64_t)row * b.ldg + h * D + part * EC;
       *reinterpret_cast<float4*>(drow) = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
       *reinterpret_cast<float4*>(drow + 4) = make_float4(acc[4] * p.scale, acc[5] * p.scale, acc[6] * p.scale, acc[7] * p.scale);
     }
@@ -1201,7 +1224,7 @@ int opt_in_smem(K kernel, size_t bytes, const char* what) {
 template <int D>
 int launch_fwd_pipe(const AttnTcArgs& a, float* o, int64_t ldo, float* lse, int64_t N, cudaStream_t st) {
   // one CTA per SM (512 TMEM columns): 8 operand stages of 16 KB + the groups' fp32 totals [G][D][128]
-  size_t smem = sizeof(float) * (2 * kFwdGroups * 4 * 32 * D + kFwdGroups * D * BM);
+  size_t smem = sizeof(float) * (2 * kFwdGroups * 4 * 32 * D + kFwdGroups * D * BM) + 1024;   // + alignment slack
   if (smem < 120 * 1024) smem = 120 * 1024;
   int rc = opt_in_smem(k_attn_fwd_pipe<D>, smem, "attn_fwd_pipe");
   if (rc) return rc;
@@ -1266,10 +1289,12 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
     return check_launch("attn_varlen_bwd(tcgen05)");
   }
+  smem_kv += 1024;                                                     // alignment slack of the pipelined kernels
   rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
   if (rc) return rc;
   size_t smem_q = sizeof(float) * (4 * 6 * 32 * D + 2 * D * BM);       // 4 stages + the groups' fp32 totals
   if (smem_q < 120 * 1024) smem_q = 120 * 1024;
+  smem_q += 1024;
   rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
   if (rc) return rc;
   // The dK/dV and dQ kernels are independent and each runs one CTA per SM: 256 + 256 CTAs on 148 SMs are
@@ -1322,17 +1347,17 @@ int attn_fwd_tc(float* o, int64_t ldo, float* lse, const float* q, int64_t ldq, 
 }
 
 // Called by hgk_attn_varlen_bwd after delta = rowsum(dO * O) has been enqueued.  Same return
-// convention as attn_fwd_tc.  dq, dk, dv are contiguous [N, H, D].
-int attn_bwd_tc(float* dq, float* dk, float* dv, const float* delta, const float* dout, int64_t lddo,
+// convention as attn_fwd_tc.  dq, dk, dv are [N, H, D] with row stride ldg.
+int attn_bwd_tc(float* dq, float* dk, float* dv, int64_t ldg, const float* delta, const float* dout, int64_t lddo,
                 const float* lse, const float* q, int64_t ldq, const float* k, int64_t ldk,
                 const float* v, int64_t ldv, const int32_t* cu, int64_t S, int64_t N, int32_t H,
                 int32_t D, float scale, cudaStream_t st) {
   if (D != 32) return 1;    // the 512-thread dK/dV kernel is laid out for 32-wide heads
   if (!tc_aligned(q, ldq) || !tc_aligned(k, ldk) || !tc_aligned(v, ldv) || !tc_aligned(dout, lddo) ||
-      !tc_aligned(dq, 4) || !tc_aligned(dk, 4) || !tc_aligned(dv, 4))
+      !tc_aligned(dq, ldg) || !tc_aligned(dk, ldg) || !tc_aligned(dv, ldg))
     return 1;
   AttnTcArgs a{q, ldq, k, ldk, v, ldv, cu, (int32_t)S, H, scale};
-  tc::AttnTcBwdArgs b{dout, lddo, lse, delta};
+  tc::AttnTcBwdArgs b{dout, lddo, lse, delta, ldg};
   return tc::launch_bwd<32>(a, b, dq, dk, dv, N, st);
 }
 

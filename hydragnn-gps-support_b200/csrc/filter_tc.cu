@@ -386,13 +386,16 @@ __global__ void __launch_bounds__(kThreads, 2)
 k_wgrad_tn(const WgradArgs p) {
   constexpr int BE = 32;                               // edges per iteration (the MMA K extent)
   constexpr int GP = (G + 3) / 4 * 4;
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(1024) float smem_raw[];
+  // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float off_s[64];
   __shared__ __align__(16) float cs_s[2][kFilt];
   // Two CTAs share an SM (64 KB of shared memory and <= 128 TMEM columns each): while one waits
-  // for its global loads or its MMAs, the other transposes its tile.
+  // for its global loads or its MMAs, the other stages its tile.  Both operands are MN-major tiles (rows =
+  // edges = the K index, as they lie in global memory): dW = A^T B needs no transposed staging.
   float* AThi = smem;                float* ATlo = AThi + kFilt * BE;
   float* BThi = ATlo + kFilt * BE;   float* BTlo = BThi + KB * BE;
   // Columns [0, KB): the running accumulator of the tensor cores; [KB, 2 KB): fp32 totals.  A tcgen05
@@ -425,8 +428,8 @@ k_wgrad_tn(const WgradArgs p) {
   if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
   __syncthreads();
 
-  const OperandDesc dA = operand_desc<BE>(AThi, ATlo), dB = operand_desc<BE>(BThi, BTlo);
-  constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB);
+  const OperandDesc dA = operand_desc_mn<BE>(AThi, ATlo), dB = operand_desc_mn<BE>(BThi, BTlo);
+  constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB) | kIdescAMajorMN | kIdescBMajorMN;
   const int a_slice = gridDim.y > 1 ? (int)blockIdx.y % p.num_a_slices : 0;
   const int b_slice = gridDim.y > 1 ? (int)blockIdx.y / p.num_a_slices : 0;
   const float* a_base = p.a + a_slice * kFilt;
@@ -496,7 +499,7 @@ k_wgrad_tn(const WgradArgs p) {
       }
     }
   };
-  // registers -> shared memory (transposed, hi / lo) and the bias-gradient partial sums of A
+  // registers -> shared memory (hi / lo) and the bias-gradient partial sums of A
   auto stage = [&]() {
     if (p.scale_d != nullptr) {
 #pragma unroll
@@ -509,8 +512,8 @@ k_wgrad_tn(const WgradArgs p) {
     for (int it = 0; it < Tile<BE, kFilt>::PER; ++it) {
       colsum.x += ta.v[it].x; colsum.y += ta.v[it].y; colsum.z += ta.v[it].z; colsum.w += ta.v[it].w;
     }
-    ta.store_transposed(AThi, ATlo);
-    tb.store_transposed(BThi, BTlo);
+    ta.store_mn(AThi, ATlo);
+    tb.store_mn(BThi, BTlo);
   };
 
   const int64_t num_tiles = (p.E + BE - 1) / BE;
@@ -524,7 +527,7 @@ k_wgrad_tn(const WgradArgs p) {
     publish_operands();        // also orders the promotion's TMEM reads before the restarting MMA
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ss<BE>(tmem, dA, dB, kIdesc, in_chain > 0);
+      mma3_ss_mn<BE>(tmem, dA, dB, kIdesc, in_chain > 0);
       mma_commit(&bar);
     }
     if (tile + stride < num_tiles) fetch(tile + stride);       // in flight during the MMAs
@@ -759,7 +762,7 @@ static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, i
   cudaStream_t st = (cudaStream_t)stream;
   static bool configured[3] = {false, false, false};      // the smem opt-in is per function: once is enough
   auto launch = [&](auto kernel, int kb, int slot) -> int {
-    size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + kb);
+    size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + kb) + 1024;     // + alignment slack of the MN-major tiles
     if (smem < 80 * 1024) smem = 80 * 1024;    // caps the occupancy at 2 CTAs per SM (register budget)
     if (!configured[slot]) {
       cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -805,7 +808,7 @@ extern "C" int hgk_wgrad_rows(float* dw, int64_t lddw, float* db, float* workspa
   float* db_partial = workspace + P * nA * nB * tc::kFilt * tc::kFilt;
   tc::WgradArgs args{a, lda, nullptr, 0.f, b, ldb, nullptr, nullptr, 0, nullptr, 0.f, dw_partial, db_partial, M, nA,
                      nullptr, nullptr, 0, nullptr};
-  size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + 128);
+  size_t smem = sizeof(float) * 2 * 32 * (tc::kFilt + 128) + 1024;      // + alignment slack of the MN-major tiles
   if (smem < 80 * 1024) smem = 80 * 1024;
   static bool configured = false;
   if (!configured) {

@@ -54,7 +54,9 @@ constexpr int kLinDepth = 4;                             // K chunks in flight (
 template <bool TRANS_B>
 __global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc(const LinearArgs p) {
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(1024) float smem_raw[];
+  // the MN-major B tile (TRANS_B) needs 1024-byte alignment; the launcher requests 1024 bytes more than the layout
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   // shared memory: operand tiles (A hi, A lo, B hi, B lo: 64 KB), then kLinDepth raw chunk slots of
@@ -70,8 +72,10 @@ k_linear_tc(const LinearArgs p) {
 
   const int32_t row0 = (int32_t)blockIdx.x * 128;
   const int32_t col0 = (int32_t)blockIdx.y * 128;
-  const OperandDesc dA = operand_desc<kBK>(Ahi, Alo), dB = operand_desc<kBK>(Bhi, Blo);
-  constexpr uint32_t kIdesc = idesc_tf32(128, 128);
+  // TRANS_B: w is [K, N] row-major, i.e. its rows are the k index: an MN-major B tile, nothing to transpose
+  const OperandDesc dA = operand_desc<kBK>(Ahi, Alo);
+  const OperandDesc dB = TRANS_B ? operand_desc_mn<kBK>(Bhi, Blo) : operand_desc<kBK>(Bhi, Blo);
+  constexpr uint32_t kIdesc = idesc_tf32(128, 128) | (TRANS_B ? kIdescBMajorMN : 0u);
 
   // The global-load latency used to be paid in every K iteration (ncu: long-scoreboard stalls dominate,
   // 16 us for [8192 x 128] x [128 x 128]).  Now the first kLinDepth chunks are requested at once with
@@ -151,7 +155,7 @@ k_linear_tc(const LinearArgs p) {
     }
     ta.store_rows(Ahi, Alo);
     if (!TRANS_B) tb.store_rows(Bhi, Blo);
-    else tbt.store_transposed(Bhi, Blo);
+    else tbt.store_mn(Bhi, Blo);
     // the slot is free again: its only reader has consumed the values (the stores above depend on them)
     request(chunk + kLinDepth);
     publish_operands();
@@ -159,7 +163,8 @@ k_linear_tc(const LinearArgs p) {
       fence_after_sync();
       const int k0 = chunk * kBK;
       const int acc = k0 / p.chunk_k;
-      mma3_ss<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, k0 > acc * p.chunk_k);
+      if (TRANS_B) mma3_ss_bmn<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, k0 > acc * p.chunk_k);
+      else mma3_ss<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, k0 > acc * p.chunk_k);
       mma_commit(&bar);
     }
   }
@@ -533,7 +538,7 @@ extern "C" int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
   tc::LinearArgs a{x, ldx, w, ldw, bias, mask, nz, ldnz, residual, ldr, scale, relu, y, ldy, M, N, K,
                    chunk_k, chunks, tmem_cols};
   // 64 KB of operand tiles + kLinDepth raw chunk slots of 32 KB: one CTA per SM
-  const size_t smem_max = sizeof(float) * (4 * 128 * tc::kBK + tc::kLinDepth * 2 * 128 * tc::kBK);
+  const size_t smem_max = sizeof(float) * (4 * 128 * tc::kBK + tc::kLinDepth * 2 * 128 * tc::kBK) + 1024;   // + alignment slack
   const size_t smem = smem_max;
   static bool configured[2] = {false, false};                   // the attribute is per function, set once
   cudaError_t err = cudaSuccess;

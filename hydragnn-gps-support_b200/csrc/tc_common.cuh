@@ -40,9 +40,21 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= static_cast<uint64_t>(1) << 46;
   return d;
 }
+// MN-major operands.  For 32-bit elements the hardware reads an MN-major operand only in the
+// SWIZZLE_128B_BASE32B layout (layout type 1; measured with profiles/_scratch/mn_major_probe*.cu -- with
+// any other layout type and the MN-major bit set the MMA reads zeros): rows of 128 bytes = 32 consecutive
+// MN elements of ONE k, consecutive k rows 128 bytes apart, and the four 32-byte chunks of a row stored at
+// chunk index c ^ (k & 3):
+//     offset(mn, k) = (mn / 32) * LBO + k * 128 + ((((mn % 32) / 8) ^ (k % 4)) * 32) + (mn % 8) * 4   [bytes]
+// SBO = 512 (distance between the 4-row atoms), one MMA (K = 8) covers 1024 bytes of rows.  This is the
+// natural row-major tile of a [rows x 32] fp32 matrix, so "B = X^T" needs no transposed staging: the rows
+// of X are the k index.  Tiles must start on a 1024-byte boundary (the swizzle is a function of the address).
+__device__ __forceinline__ uint64_t smem_desc_mn(uint32_t saddr, uint32_t lbo_bytes) {
+  return smem_desc(saddr, lbo_bytes, 512) | (static_cast<uint64_t>(1) << 61);
+}
+constexpr uint32_t kIdescBMajorMN = 1u << 16;   // OR into idesc_tf32: B is MN-major
+constexpr uint32_t kIdescAMajorMN = 1u << 15;   // OR into idesc_tf32: A (shared memory) is MN-major
 // 32-bit instruction descriptor: tf32 x tf32 -> f32, dense, A and B K-major.
-// (An MN-major B view of a K-major staged tile was tried for the transposed operands and did not
-// reproduce the reference with SWIZZLE_NONE; transposed operands are staged explicitly instead.)
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
   return (1u << 4)            // D format  = F32
        | (2u << 7)            // A format  = TF32
@@ -282,6 +294,48 @@ struct Tile {
       *reinterpret_cast<float4*>(lo + off) = l;
     }
   }
+  // float offset of 16-byte chunk c of row r in the MN-major (SWIZZLE_128B_BASE32B) tile of the matrix: one
+  // [ROWS x 32] block per 32 columns (LBO = ROWS * 128 bytes), 32-byte chunks of a row XOR-swizzled with r & 3
+  __device__ __forceinline__ static int mn_off(int r, int c) {
+    return (c >> 3) * (ROWS * 32) + r * 32 + (((((c & 7) >> 1) ^ (r & 3)) << 3) | ((c & 1) << 2));
+  }
+  // hi / lo tiles for BOTH uses of a [ROWS x 32] matrix X: K-major (operand X: MN index = row, K = feature)
+  // and MN-major (operand X^T: MN index = feature, K = row).  One split, four conflict-free 16-byte stores
+  // (the lanes of a warp cover 4 rows x 128 bytes).
+  __device__ __forceinline__ void store_rows_and_mn_as(int tid, float* hi, float* lo, float* hi_mn, float* lo_mn) const {
+    static_assert(D == 32, "the MN-major tile is one 32-element atom wide");
+    constexpr int SBO = CH * 32;
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      int r, c;
+      coord_of(tid, it, r, c);
+      float4 h, l;
+      split_tf32(v[it].x, h.x, l.x); split_tf32(v[it].y, h.y, l.y);
+      split_tf32(v[it].z, h.z, l.z); split_tf32(v[it].w, h.w, l.w);
+      const int off = core_off(r, c, SBO);
+      *reinterpret_cast<float4*>(hi + off) = h;
+      *reinterpret_cast<float4*>(lo + off) = l;
+      const int moff = mn_off(r, c);
+      *reinterpret_cast<float4*>(hi_mn + moff) = h;
+      *reinterpret_cast<float4*>(lo_mn + moff) = l;
+    }
+  }
+  // the MN-major tile alone
+  __device__ __forceinline__ void store_mn(float* hi_mn, float* lo_mn) const { store_mn_as((int)threadIdx.x - TOFF, hi_mn, lo_mn); }
+  __device__ __forceinline__ void store_mn_as(int tid, float* hi_mn, float* lo_mn) const {
+    static_assert(D % 32 == 0, "MN-major tiles are made of 32-column blocks");
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+      int r, c;
+      coord_of(tid, it, r, c);
+      float4 h, l;
+      split_tf32(v[it].x, h.x, l.x); split_tf32(v[it].y, h.y, l.y);
+      split_tf32(v[it].z, h.z, l.z); split_tf32(v[it].w, h.w, l.w);
+      const int moff = mn_off(r, c);
+      *reinterpret_cast<float4*>(hi_mn + moff) = h;
+      *reinterpret_cast<float4*>(lo_mn + moff) = l;
+    }
+  }
   // hi / lo K-major tiles of the TRANSPOSE: MN index = feature (D rows), K index = row (ROWS columns).
   // Lanes l, l^1, l^2, l^3 hold the same 16-byte column of 4 consecutive rows; a 4x4 register
   // transpose (4 shuffles) lets every lane write one 16-byte chunk: feature 4c + (l & 3), 4 rows.
@@ -339,6 +393,12 @@ __device__ __forceinline__ OperandDesc operand_desc(const float* hi, const float
   return {smem_desc(smem_u32(hi), kLbo, sbo), smem_desc(smem_u32(lo), kLbo, sbo)};
 }
 
+// descriptors of an MN-major tile pair (see smem_desc_mn): [ROWS rows (k)] x [32-column blocks (mn)]
+template <int ROWS = 32>
+__device__ __forceinline__ OperandDesc operand_desc_mn(const float* hi, const float* lo) {
+  return {smem_desc_mn(smem_u32(hi), ROWS * 128), smem_desc_mn(smem_u32(lo), ROWS * 128)};
+}
+
 // 3xTF32 product  D (+)= A B^T  with A, B in shared memory ([rows x KD] K-major tiles, hi / lo).
 template <int KD>
 __device__ __forceinline__ void mma3_ss(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
@@ -360,6 +420,46 @@ __device__ __forceinline__ void mma3_ts(uint32_t d_tmem, uint32_t a_hi_tmem, uin
   for (int j = 0; j < KD / 8; ++j) {
     const uint64_t adv = static_cast<uint64_t>(j * 2 * kLbo / 16);
     const uint32_t col = j * 8;                        // 8 k values = 8 TMEM columns per MMA
+    mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.hi + adv, idesc, 1);
+  }
+}
+
+// D (+)= A^T B with A = [KD rows (k) x M] and B = [KD rows (k) x N] row-major MN-major tiles in shared memory
+// (a "TN" product: nothing is transposed on the way in); `idesc` must carry both MN-major bits.
+template <int KD>
+__device__ __forceinline__ void mma3_ss_mn(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                           uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * (8 * 128 / 16));   // 8 rows of 128 bytes per MMA
+    mma_tf32_ss(d_tmem, a.lo + adv, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.lo + adv, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.hi + adv, idesc, 1);
+  }
+}
+// D (+)= A B with A = [M x KD] K-major and B = [KD rows (k) x N] MN-major; `idesc` must carry kIdescBMajorMN.
+template <int KD>
+__device__ __forceinline__ void mma3_ss_bmn(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                            uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv_a = static_cast<uint64_t>(j * 2 * kLbo / 16);
+    const uint64_t adv_b = static_cast<uint64_t>(j * (8 * 128 / 16));
+    mma_tf32_ss(d_tmem, a.lo + adv_a, b.hi + adv_b, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv_a, b.lo + adv_b, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv_a, b.hi + adv_b, idesc, 1);
+  }
+}
+// The same with B = an MN-major tile ([KD rows = k] x [32 = n]); `idesc` must carry kIdescBMajorMN.
+template <int KD>
+__device__ __forceinline__ void mma3_ts_mn(uint32_t d_tmem, uint32_t a_hi_tmem, uint32_t a_lo_tmem,
+                                           const OperandDesc& b, uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * (8 * 128 / 16));   // 8 rows of 128 bytes per MMA
+    const uint32_t col = j * 8;
     mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
     mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);
     mma_tf32_ts(d_tmem, a_hi_tmem + col, b.hi + adv, idesc, 1);

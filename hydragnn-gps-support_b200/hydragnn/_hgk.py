@@ -125,6 +125,12 @@ _SIGNATURES = {
          _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_i64,
          _c_i32, _c_i32, _c_f32, _c_ptr],
     ),
+    "hgk_attn_varlen_bwd_ld": (
+        _c_i32,
+        [_c_ptr, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr,
+         _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_ptr, _c_i64, _c_i64,
+         _c_i32, _c_i32, _c_f32, _c_ptr],
+    ),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
@@ -167,7 +173,7 @@ KERNELS_PER_CALL = {
     "hgk_csr_build": 4, "hgk_csr_build_static": 4, "hgk_contract_node": 1, "hgk_contract_edge_w": 1, "hgk_contract_edge_u": 1,
     "hgk_edge_gather_add": 1, "hgk_schnet_filter_fwd": 1, "hgk_schnet_filter_bwd": 1, "hgk_wgrad_tn": 1, "hgk_wgrad_reduce": 1, "hgk_colsum": 2, "hgk_pna_aggregate_fwd": 1, "hgk_pna_aggregate_bwd": 1,
     "hgk_radius_graph_count": 8, "hgk_radius_graph_fill": 1, "hgk_attn_varlen_fwd": 1,
-    "hgk_attn_varlen_bwd": 3, "hgk_wgrad_rows": 2, "hgk_linear_tc": 1, "hgk_bn_stats": 2, "hgk_bn_apply": 1,
+    "hgk_attn_varlen_bwd": 3, "hgk_attn_varlen_bwd_ld": 3, "hgk_wgrad_rows": 2, "hgk_linear_tc": 1, "hgk_bn_stats": 2, "hgk_bn_apply": 1,
     "hgk_bn_bwd": 3, "hgk_mask_axpy": 1, "hgk_edge_geom_fwd": 1, "hgk_edge_geom_bwd": 1, "hgk_edge_geom_bwd2": 1,
     "hgk_collate_rows": 1, "hgk_collate_edges": 1, "hgk_cfconv_filter_bwd": 1, "hgk_cfconv_wgrad": 1,
 }

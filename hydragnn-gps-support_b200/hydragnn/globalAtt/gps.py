@@ -21,7 +21,7 @@ from torch import Tensor
 from torch.nn import Dropout, Sequential
 
 from ..nn import BatchNorm, Linear, activation_resolver, normalization_resolver
-from ..ops import attn_varlen, linear_rows
+from ..ops import attn_varlen_packed, linear_rows
 from ..ops import node as node_ops
 from . import graphed_tail
 
@@ -157,8 +157,7 @@ class GPSConv(torch.nn.Module):
             h_local, equiv_node_feat = self.conv(inv_node_feat=x, equiv_node_feat=equiv_node_feat, **kwargs)
         cu_seqlens = self._segments(x, graph_batch, cu_seqlens)
         h1, qkv = graphed_tail.run(self, "pre", x, h_local)
-        c = self.channels
-        o = attn_varlen(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu_seqlens, self.heads)  # gps.py:126-133
+        o = attn_varlen_packed(qkv, cu_seqlens, self.heads)  # gps.py:126-133
         out = graphed_tail.run(self, "post", x, h1, o)
         return out, equiv_node_feat
 

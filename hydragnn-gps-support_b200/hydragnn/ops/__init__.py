@@ -10,7 +10,7 @@ from .contract import (
     edge_gather_add,
 )
 from .radius import radius_graph, radius_graph_pbc, MODE_ASE, MODE_CLUSTER
-from .attention import attn_varlen
+from .attention import attn_varlen, attn_varlen_packed
 from .pna import pna_aggregate
 from .linear import linear_rows, colsum
 from .node import linear_fast, linear_tc, wgrad_rows

@@ -40,22 +40,30 @@ def _attn_fwd_raw(q, k, v, cu_seqlens, H, scale):
     return o, lse, q_t, k_t, v_t
 
 
-def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
+def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale, packed=False):
+    """dq, dk, dv [N, H*D]; packed=True: the three column blocks of ONE [N, 3*H*D] tensor, which is returned
+    instead (the gradient of a packed in-projection output: no slice-backward / accumulate pass afterwards)."""
     N, HD = o.shape
     D = HD // H
     do_t, lddo = _hgk.rows(do)
-    dq = torch.empty((N, HD), dtype=torch.float32, device=o.device)
-    dk = torch.empty_like(dq)
-    dv = torch.empty_like(dq)
+    if packed:
+        dqkv = torch.empty((N, 3 * HD), dtype=torch.float32, device=o.device)
+        dq, dk, dv = dqkv[:, :HD], dqkv[:, HD:2 * HD], dqkv[:, 2 * HD:]
+        ldg = 3 * HD
+    else:
+        dq = torch.empty((N, HD), dtype=torch.float32, device=o.device)
+        dk = torch.empty_like(dq)
+        dv = torch.empty_like(dq)
+        ldg = HD
     delta = torch.empty((N, H), dtype=torch.float32, device=o.device)
     q_t, ldq = _hgk.rows(q)
     k_t, ldk = _hgk.rows(k)
     v_t, ldv = _hgk.rows(v)
-    _hgk.call("hgk_attn_varlen_bwd", _hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), _hgk.ptr(delta),
+    _hgk.call("hgk_attn_varlen_bwd_ld", _hgk.ptr(dq), _hgk.ptr(dk), _hgk.ptr(dv), ldg, _hgk.ptr(delta),
               _hgk.ptr(do_t), lddo, _hgk.ptr(o), HD, _hgk.ptr(lse), _hgk.ptr(q_t), ldq, _hgk.ptr(k_t), ldk,
               _hgk.ptr(v_t), ldv, _hgk.ptr(cu), cu.numel() - 1, N, H, D, float(scale),
               cost=(4 * (8 * N * HD + 2 * N * H), 10 * HD * _sum_sq(cu)))
-    return dq, dk, dv
+    return dqkv if packed else (dq, dk, dv)
 
 
 def _segment_bounds(cu):
@@ -139,6 +147,39 @@ class AttnVarlen(torch.autograd.Function):
         else:
             dq, dk, dv = _attn_bwd_raw(do, o, lse, q, k, v, cu, ctx.H, ctx.scale)
         return dq, dk, dv, None, None, None
+
+
+class AttnVarlenPacked(torch.autograd.Function):
+    """The same on the packed in-projection output qkv [N, 3*H*D] (q | k | v column blocks): ONE autograd
+    edge carries the [N, 3*H*D] gradient, written in place by the backward kernels."""
+
+    @staticmethod
+    def forward(ctx, qkv, cu_seqlens, H, scale):
+        c = qkv.size(1) // 3
+        o, lse, *_ = _attn_fwd_raw(qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu_seqlens, H, scale)
+        ctx.save_for_backward(qkv, o, lse, cu_seqlens)
+        ctx.H, ctx.scale = H, scale
+        ctx.bounds = getattr(cu_seqlens, "_hgk_bounds", None)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse, cu = ctx.saved_tensors
+        c = qkv.size(1) // 3
+        q, k, v = qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:]
+        if torch.is_grad_enabled():        # create_graph=True: stay differentiable
+            if ctx.bounds is not None:
+                cu._hgk_bounds = ctx.bounds
+            return torch.cat(_dense_backward(do, q, k, v, cu, ctx.H, ctx.scale), dim=1), None, None, None
+        return _attn_bwd_raw(do, o, lse, q, k, v, cu, ctx.H, ctx.scale, packed=True), None, None, None
+
+
+def attn_varlen_packed(qkv, cu_seqlens, num_heads, scale=None):
+    """attn_varlen(qkv[:, :C], qkv[:, C:2C], qkv[:, 2C:]) for a packed [N, 3C] projection output."""
+    D = qkv.size(1) // (3 * num_heads)
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    return AttnVarlenPacked.apply(qkv, cu_seqlens.to(torch.int32), num_heads, scale)
 
 
 def attn_varlen(q, k, v, cu_seqlens, num_heads, scale=None):

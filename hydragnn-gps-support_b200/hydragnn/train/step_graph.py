@@ -17,8 +17,14 @@ whole step -- forward, loss, backward, optimizer -- is captured once per SIZE BU
   * tensors of one bucket live in static buffers; a step copies the batch in and replays the graph.
     Shapes are static per bucket, batch-dependent values (sizes, offsets, scale) are device tensors.
 
+Data-parallel training: the captured part is forward + loss + backward, which packs the gradients into ONE
+flat buffer shared by all buckets (the parameters' .grad are views of it); the gradient mean over the
+ranks is one eager all-reduce of that buffer between the replay and a second, bucket-independent graph
+that holds the optimizer step.  Warm-up and capture issue no collective, so ranks may capture at
+different steps without falling out of step with each other.
+
 A stream of random mini-batches of a molecular dataset hits a handful of buckets (sum of 64 molecule
-sizes: +-2 %), each captured on first use.  Eligible: single-rank training, mse / mae losses, SchNet /
+sizes: +-2 %), each captured on first use.  Eligible: mse / mae losses, SchNet /
 EGNN / PAINN stacks (their per-node normalisation, if any, is the GPS block's, which honours
 `valid_rows`), with or without the energy + force loss (the double backward is captured like
 everything else; not through a GPS layer); everything else runs the eager `train_step`.
@@ -42,7 +48,7 @@ def _roundup(n, m):
 
 
 class _Entry:
-    __slots__ = ("static", "graph", "loss", "tasks", "uses", "launches", "grads")
+    __slots__ = ("static", "graph", "loss", "tasks", "uses", "launches")
 
 
 class BucketedStepGraph:
@@ -57,6 +63,11 @@ class BucketedStepGraph:
         # it): while capturing, the param groups carry the rate as a device tensor; before a replay the
         # tensor is refreshed from the (host) value the scheduler left in the group.
         self._lr_dev, self._lr_host = None, None
+        self._flat = None              # flat fp32 gradient buffer; p.grad = views of it
+        self._views = None
+        self._opt_graph = None         # the optimizer step, captured once
+        import torch.distributed as dist
+        self._world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
 
     # ----------------------------------------------------------------------------- eligibility ---
     def eligible(self, data, compute_grad_energy=False):
@@ -66,8 +77,6 @@ class BucketedStepGraph:
         if compute_grad_energy and (core.use_global_attn or core.num_heads != 1 or core.head_type[0] != "node"
                                     or getattr(data, "energy", None) is None or getattr(data, "forces", None) is None):
             return False            # the force loss through a GPS layer differentiates attention twice: eager
-        if getattr(self.model, "averager", None) is not None and self.model.averager.enabled:
-            return False                                    # gradient all-reduce: eager path
         if core.loss_function_type not in ("mse", "mae") or core.var_output or core.num_branches > 1:
             return False
         name = str(core)
@@ -204,8 +213,59 @@ class BucketedStepGraph:
         else:
             loss, tasks = self._masked_loss(pred, static)
         loss.backward()
-        self.optimizer.step()
         return loss.detach(), [t.detach() for t in tasks]
+
+    # ------------------------------------------------------------------------- gradients ---
+    def _discover(self, static):
+        """Which parameters this model's backward reaches (an eager optimizer skips the others: no weight
+        decay, no moment update) -- one backward with .grad = None.  The flat buffer covers exactly those."""
+        params = [p for p in self.core.parameters() if p.requires_grad]
+        for p in params:
+            p.grad = None
+        if static["data"].pos.requires_grad:
+            static["data"].pos.grad = None
+        self._clear_caches(static)
+        self._body(static)
+        used = [p for p in params if p.grad is not None]
+        if self._views is None:
+            total = sum(p.numel() for p in used)
+            self._flat = torch.zeros(total, dtype=torch.float32, device=used[0].device)
+            self._views, off = [], 0
+            for p in used:
+                self._views.append((p, self._flat[off:off + p.numel()].view_as(p)))
+                off += p.numel()
+        elif [id(p) for p in used] != [id(p) for p, _ in self._views]:
+            raise RuntimeError("step graph: this bucket's backward reaches a different set of parameters than the "
+                               "first one did; the captured optimizer step cannot serve both")
+
+    def _bind_grads(self):
+        """p.grad = the parameter's view of the flat buffer (parameters backward never reaches: None)."""
+        for p, v in self._views:
+            p.grad = v
+        averager = getattr(self.model, "averager", None)
+        if averager is not None:
+            averager.suspended = True           # its per-chunk hooks stay quiet: the mean is taken here
+
+    def _fwd_bwd(self, static):
+        """Forward, loss, backward; the gradients land in the flat buffer by ONE concatenation (backward is
+        handed .grad = None, so there is no accumulate kernel per parameter), .grad = views of the buffer."""
+        for p, _ in self._views:
+            p.grad = None
+        if static["data"].pos.requires_grad:
+            static["data"].pos.grad = None
+        out = self._body(static)
+        torch.cat([p.grad.reshape(-1) for p, _ in self._views], out=self._flat)
+        self._bind_grads()
+        return out
+
+    def _reduce_and_step(self):
+        if self._world > 1:
+            import torch.distributed as dist
+            op = dist.ReduceOp.AVG if dist.get_backend() == "nccl" else dist.ReduceOp.SUM
+            dist.all_reduce(self._flat, op=op)
+            if op == dist.ReduceOp.SUM:
+                self._flat.mul_(1.0 / self._world)
+        self._opt_graph.replay()
 
     # ----------------------------------------------------------------------------- targets ---
     def _targets(self, data, padded, key):
@@ -318,23 +378,26 @@ class BucketedStepGraph:
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            for _ in range(self.warmup):                 # eager runs: allocator / lazy-init warm-up
+            self._discover(entry.static)
+            self._bind_grads()
+            for _ in range(self.warmup):                 # eager runs: allocator / lazy-init warm-up, no collective
                 self._clear_caches(entry.static)
-                self._zero_grad(entry.static)
-                self._body(entry.static)
+                self._fwd_bwd(entry.static)
+                self.optimizer.step()
         torch.cuda.current_stream().wait_stream(side)
+        if self._opt_graph is None:                      # the optimizer step: one graph for all buckets
+            opt_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(opt_graph):
+                self.optimizer.step()
+            self._opt_graph = opt_graph
         self._restore(snap)
         self._clear_caches(entry.static)
-        self._zero_grad(entry.static)
         graph = torch.cuda.CUDAGraph()
         before = _hgk.stats.launches()
         with torch.cuda.graph(graph):
-            entry.loss, entry.tasks = self._body(entry.static)
+            entry.loss, entry.tasks = self._fwd_bwd(entry.static)
         entry.launches = _hgk.stats.launches() - before      # libhgk kernels inside one replay
         entry.graph = graph
-        # the gradient buffers this graph writes (allocated inside its capture); after a replay the
-        # parameters' .grad are pointed back at them, so that `.grad` is what the step just computed
-        entry.grads = [(p, p.grad) for p in self.core.parameters() if p.grad is not None]
         self.captures += 1
         return entry
 
@@ -353,18 +416,19 @@ class BucketedStepGraph:
                 self._lr_dev[k].fill_(v)
                 self._lr_host[k] = v
 
-    def _zero_grad(self, static=None):
-        for p in self.core.parameters():
-            p.grad = None
-        if static is not None and static["data"].pos.requires_grad:
-            static["data"].pos.grad = None
-
     # ---------------------------------------------------------------------------------- step ---
+    def eager_step(self, data, compute_grad_energy=False):
+        """The plain `train_step` on the same model / optimizer (ineligible batches, instrumented runs)."""
+        self.eager_steps += 1
+        averager = getattr(self.model, "averager", None)
+        if averager is not None:
+            averager.suspended = False
+        return train_step(self.model, self.optimizer, data, compute_grad_energy)
+
     def step(self, data, compute_grad_energy=False):
         """One optimisation step; returns (loss, per-task losses) like `train_step`."""
         if not self.eligible(data, compute_grad_energy):
-            self.eager_steps += 1
-            return train_step(self.model, self.optimizer, data, compute_grad_energy)
+            return self.eager_step(data, compute_grad_energy)
         key = self._key_of(data, compute_grad_energy)
         padded = self._pad(data, key)
         entry = self.entries.get(key)
@@ -372,9 +436,10 @@ class BucketedStepGraph:
             entry = self.entries[key] = self._capture(data, padded, key)
         self._fill(entry.static, data, padded, key)
         self._sync_lr()
+        if self._views[0][0].grad is not self._views[0][1]:
+            self._bind_grads()                   # somebody (an eager step's zero_grad) dropped the views
         entry.graph.replay()
-        for p, g in entry.grads:
-            p.grad = g
+        self._reduce_and_step()
         entry.uses += 1
         self.replays += 1
         _hgk.stats.replayed += entry.launches

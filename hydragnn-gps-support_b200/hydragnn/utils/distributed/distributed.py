@@ -184,7 +184,11 @@ class GradientAverager:
             work = dist.all_reduce(chunk["view"], op=op, group=self.group, async_op=True)
         self._works.append(work)
 
+    suspended = False      # set by train/step_graph.py, which reduces one flat buffer itself
+
     def _on_grad_ready(self, p):
+        if self.suspended:
+            return
         idx = self._chunk_of[p]
         self._pending[idx] -= 1
         # rank-independent order: only the chunk at the cursor may go, then any completed ones behind it

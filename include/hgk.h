@@ -436,6 +436,19 @@ int hgk_attn_varlen_bwd(float* dq, float* dk, float* dv, float* delta,
                         const int32_t* cu_seqlens, int64_t S, int64_t N,
                         int32_t H, int32_t D, float scale, void* stream);
 
+/* The same with a row stride for the gradients: dq, dk, dv are [N, H*D] blocks
+ * of rows `ldg` floats apart (ldg >= H*D, multiple of 4) -- e.g. the three
+ * column blocks of ONE [N, 3*H*D] gradient of the packed in-projection output
+ * (reference hydragnn/globalAtt/gps.py:126-133: nn.MultiheadAttention's packed
+ * in_proj), so that no slice-backward / accumulate pass runs after the kernel. */
+int hgk_attn_varlen_bwd_ld(float* dq, float* dk, float* dv, int64_t ldg, float* delta,
+                           const float* dout, int64_t lddo, const float* o,
+                           int64_t ldo, const float* lse, const float* q,
+                           int64_t ldq, const float* k, int64_t ldk,
+                           const float* v, int64_t ldv,
+                           const int32_t* cu_seqlens, int64_t S, int64_t N,
+                           int32_t H, int32_t D, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,8 +57,9 @@ def _attn_fwd_raw(q, k, v, cu, H, scale):
     return o, lse, q, k, v
 
 
-def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale):
-    return ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
+def _attn_bwd_raw(do, o, lse, q, k, v, cu, H, scale, packed=False):
+    grads = ks.attn_varlen_bwd(do, q, k, v, cu, H, scale)
+    return torch.cat(grads, dim=1) if packed else grads
 
 
 def _build_csr(key, num_rows):

@@ -248,6 +248,29 @@ def test_attn_strided_qkv(ops):
     torch.testing.assert_close(out.cpu(), ref, rtol=1e-5, atol=2e-6)
 
 
+def test_attn_packed_gradient_is_written_in_place(ops):
+    """attn_varlen_packed(qkv): the backward kernels write dq | dk | dv straight into the column blocks of ONE
+    [N, 3C] gradient (hgk_attn_varlen_bwd_ld, row stride 3C).  Output and gradient equal the three-tensor op
+    bit for bit (same kernels), and the oracle within tolerance."""
+    gen = torch.Generator().manual_seed(5)
+    sizes, H, D = [130, 7, 300, 64], 4, 32
+    N, c = sum(sizes), H * D
+    cu = torch.tensor([0] + list(np.cumsum(sizes)), dtype=torch.int32)
+    qkv = torch.randn(N, 3 * c, generator=gen)
+    do = torch.randn(N, c, generator=gen)
+    a = qkv.to(DEV).requires_grad_(True)
+    out_a = ops["ops"].attn_varlen_packed(a, cu.to(DEV), H)
+    out_a.backward(do.to(DEV))
+    b = qkv.to(DEV).requires_grad_(True)
+    out_b = ops["ops"].attn_varlen(b[:, :c], b[:, c:2 * c], b[:, 2 * c:], cu.to(DEV), H)
+    out_b.backward(do.to(DEV))
+    assert torch.equal(out_a, out_b)
+    assert torch.equal(a.grad, b.grad)
+    rq, rk, rv = ks.attn_varlen_bwd(do, qkv[:, :c], qkv[:, c:2 * c], qkv[:, 2 * c:], cu, H, 1.0 / np.sqrt(D))
+    want = torch.cat([rq, rk, rv], dim=1)
+    torch.testing.assert_close(a.grad.cpu(), want, rtol=1e-5, atol=1e-5 * float(want.abs().max()))
+
+
 # --------------------------------------------------------------------- radius graph ---
 def _canon(src, dst, S):
     order = np.lexsort((S[:, 2], S[:, 1], S[:, 0], src, dst))

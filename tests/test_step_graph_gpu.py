@@ -138,3 +138,72 @@ def test_run_training_with_step_graphs(libhgk, tmp_path, monkeypatch):
     hydragnn.run_training(copy.deepcopy(config))
     error, task_errors, true_values, predicted = hydragnn.run_prediction(copy.deepcopy(config))
     assert torch.sqrt(torch.mean((true_values[0] - predicted[0]) ** 2)).item() < 0.20
+
+
+def _rank_worker(rank, world, port, out_dir):
+    """One data-parallel rank (both ranks share cuda:0; gloo carries the CUDA all-reduce)."""
+    import os
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path[:0] = [os.path.join(os.path.dirname(here), "hydragnn-gps-support_b200"), here]
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK="0", HYDRAGNN_BACKEND="gloo")
+    import torch.distributed as dist
+    from hydragnn.train import train_step
+    from hydragnn.utils.distributed import setup_ddp
+
+    setup_ddp()
+    base, batches = _setup("schnet_qm9")
+    mine = batches[rank::world]                                     # each rank its own shard of the stream
+    twin = copy.deepcopy(base)                                      # this rank's own gradients, no exchange
+    opt_twin = torch.optim.AdamW(twin.parameters(), lr=0.0, fused=True)
+    model, sg, step = _runner(base, True, 0.0)
+    assert model.averager.enabled
+    record = []
+    for rep in range(2):
+        for make in mine:
+            train_step(twin, opt_twin, make())
+            loss = step(make())
+            record.append({"loss": float(loss),
+                           "local": {n: p.grad.detach().cpu().clone() for n, p in twin.named_parameters()
+                                     if p.grad is not None},
+                           "avg": {n: p.grad.detach().cpu().clone() for n, p in model.module.named_parameters()
+                                   if p.grad is not None}})
+    assert sg.eager_steps == 0 and sg.replays == len(record)
+    # real steps: the ranks must stay in lockstep
+    for g in sg.optimizer.param_groups:
+        g["lr"] = 1e-3
+    for make in mine:
+        step(make())
+    params = {n: p.detach().cpu().clone() for n, p in model.module.named_parameters()}
+    torch.save({"record": record, "params": params}, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_step_graph_two_ranks_average_gradients(libhgk, tmp_path):
+    """World size 2: every rank replays its own bucket's graph (the ranks' batches differ in size, so do their
+    buckets and capture steps), the flat gradient buffer is averaged between the replay and the captured
+    optimizer step.  Averaged gradient = mean of the two ranks' own eager gradients; parameters after real
+    steps are identical on both ranks."""
+    import socket
+
+    import torch.multiprocessing as mp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (torch.load(tmp_path / f"rank{r}.pt") for r in range(2))
+    assert len(r0["record"]) == len(r1["record"]) == 6
+    for a, b in zip(r0["record"], r1["record"]):
+        assert set(a["avg"]) == set(a["local"]) == set(b["local"])
+        for n in a["avg"]:
+            want = 0.5 * (a["local"][n] + b["local"][n])
+            scale = float(want.abs().max())
+            torch.testing.assert_close(a["avg"][n], b["avg"][n], rtol=0, atol=0, msg=lambda m, n=n: f"{n}: {m}")
+            torch.testing.assert_close(a["avg"][n], want, rtol=1e-4, atol=max(1e-4 * scale, 1e-9),
+                                       msg=lambda m, n=n: f"{n}: {m}")
+    for n in r0["params"]:
+        torch.testing.assert_close(r0["params"][n], r1["params"][n], rtol=0, atol=0)
