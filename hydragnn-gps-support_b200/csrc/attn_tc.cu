@@ -227,7 +227,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   const bool issuer = warp_u == G * kFwdGroup / 32;    // the last warp
 
   constexpr int kTile = BK * D;
-  constexpr int kStage = 4 * kTile;                    // K rows hi/lo (K-major), V rows hi/lo (MN-major: B = V^T)
+  constexpr int kStage = 4 * kTile;                    // K rows hi/lo (B = K of the scores), V rows hi/lo (B = V^T)
   constexpr int oKhi = 0, oKlo = kTile, oVThi = 2 * kTile, oVTlo = 3 * kTile;
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColS = 0, kColPlo = G * BK, kColO = 2 * G * BK, kColQhi = 2 * G * BK + G * D,
@@ -245,15 +245,15 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
   constexpr uint32_t kIdescO = idesc_tf32(BM, D) | kIdescBMajorMN;
 
   if (issuer) {
-    const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo);
+    const OperandDesc dK = operand_desc_k32(smem + oKhi, smem + oKlo);
     const OperandDesc dVt = operand_desc_mn(smem + oVThi, smem + oVTlo);
     auto at_stage = [](const OperandDesc& d, int st) {
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
     };
     auto issue_scores = [&](int s) {
-      mma3_ts<D>(tmem + kColS + (uint32_t)(s % G) * BK, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s % NST),
-                 kIdescS, false);
+      mma3_ts_k32<D>(tmem + kColS + (uint32_t)(s % G) * BK, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s % NST),
+                     kIdescS, false);
     };
     named_bar_sync(1, kFwdThreads);                    // Q rows are in TMEM, the first G stages are written
     fence_after_sync();
@@ -291,7 +291,7 @@ k_attn_fwd_pipe(const AttnTcArgs p, float* __restrict__ o, int64_t ldo, float* _
     };
     auto stage = [&](int st) {
       float* base = smem + st * kStage;
-      tk.store_rows_as(tl, base + oKhi, base + oKlo);
+      tk.store_mn_as(tl, base + oKhi, base + oKlo);
       tv.store_mn_as(tl, base + oVThi, base + oVTlo);
     };
     if (g < nsub) { load(seg_beg + g * BK); stage(g); }
@@ -783,11 +783,10 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   const bool issuer = warp_u == kKvThreads / 32;       // warp 16
 
   constexpr int kTile = BQ * D;                        // floats per operand tile
-  constexpr int kStage = 8 * kTile;                    // floats per stage
-  constexpr int oQhi = 0, oQlo = kTile;                // rows = queries (B of S^T)
-  constexpr int oGhi = 2 * kTile, oGlo = 3 * kTile;    // dO rows        (B of dP^T)
-  constexpr int oQThi = 4 * kTile, oQTlo = 5 * kTile;  // Q rows, MN-major  (B = Q^T of dK)
-  constexpr int oGThi = 6 * kTile, oGTlo = 7 * kTile;  // dO rows, MN-major (B = dO^T of dV)
+  constexpr int kStage = 4 * kTile;                    // floats per stage
+  // one tile pair per matrix: read K-major as B = Q / dO (S^T, dP^T) and MN-major as B = Q^T / dO^T (dK, dV)
+  constexpr int oQhi = 0, oQlo = kTile;                // Q rows
+  constexpr int oGhi = 2 * kTile, oGlo = 3 * kTile;    // dO rows
 
   constexpr uint32_t kCols = 512;
   // one (dV, dK) accumulator pair per compute group: columns kColAcc + g * 2D (dV) and + D (dK); a group's
@@ -805,16 +804,16 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
 
   if (issuer) {
     // ------------------------------------------------------------------ MMA-issuing warp ---
-    const OperandDesc dQ = operand_desc<D>(smem + oQhi, smem + oQlo), dG = operand_desc<D>(smem + oGhi, smem + oGlo);
-    const OperandDesc dQt = operand_desc_mn(smem + oQThi, smem + oQTlo), dGt = operand_desc_mn(smem + oGThi, smem + oGTlo);
+    const OperandDesc dQ = operand_desc_k32(smem + oQhi, smem + oQlo), dG = operand_desc_k32(smem + oGhi, smem + oGlo);
+    const OperandDesc dQt = operand_desc_mn(smem + oQhi, smem + oQlo), dGt = operand_desc_mn(smem + oGhi, smem + oGlo);
     auto at_stage = [](const OperandDesc& d, int st) {   // start-address field is in 16-byte units
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
     };
     auto issue_scores = [&](int s) {                   // S^T, dP^T of step s into column set s & 1
       const uint32_t set = (uint32_t)(s & 1) * BQ;
-      mma3_ts<D>(tmem + kColST + set, tmem + kColKhi, tmem + kColKlo, at_stage(dQ, s & (NST - 1)), kIdescS, false);
-      mma3_ts<D>(tmem + kColDPT + set, tmem + kColVhi, tmem + kColVlo, at_stage(dG, s & (NST - 1)), kIdescS, false);
+      mma3_ts_k32<D>(tmem + kColST + set, tmem + kColKhi, tmem + kColKlo, at_stage(dQ, s & (NST - 1)), kIdescS, false);
+      mma3_ts_k32<D>(tmem + kColDPT + set, tmem + kColVhi, tmem + kColVlo, at_stage(dG, s & (NST - 1)), kIdescS, false);
     };
     auto issue_updates = [&](int s) {                  // dV += P^T dO, dK += dS^T Q of step s
       const uint32_t set = (uint32_t)(s & 1) * BQ;
@@ -878,12 +877,12 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       float* base = smem + st * kStage;
       if (g == 0) {
         tq0.scale(qmul);
-        tq0.store_rows_and_mn_as(tl, base + oQhi, base + oQlo, base + oQThi, base + oQTlo);
-        tg0.store_rows_and_mn_as(tl, base + oGhi, base + oGlo, base + oGThi, base + oGTlo);
+        tq0.store_mn_as(tl, base + oQhi, base + oQlo);
+        tg0.store_mn_as(tl, base + oGhi, base + oGlo);
       } else {
         tq1.scale(qmul);
-        tq1.store_rows_and_mn_as(tl, base + oQhi, base + oQlo, base + oQThi, base + oQTlo);
-        tg1.store_rows_and_mn_as(tl, base + oGhi, base + oGlo, base + oGThi, base + oGTlo);
+        tq1.store_mn_as(tl, base + oQhi, base + oQlo);
+        tg1.store_mn_as(tl, base + oGhi, base + oGlo);
       }
       if (tl < BQ) {
         lse2_s[st][tl] = lse_r * kLog2e;
@@ -1030,10 +1029,9 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   const bool issuer = warp_u == kKvThreads / 32;       // warp 16
 
   constexpr int kTile = BK * D;                        // floats per operand tile
-  constexpr int kStage = 6 * kTile;                    // floats per stage
-  constexpr int oKhi = 0, oKlo = kTile;                // rows = keys    (B of S)
-  constexpr int oVhi = 2 * kTile, oVlo = 3 * kTile;    // V rows         (B of dP)
-  constexpr int oKThi = 4 * kTile, oKTlo = 5 * kTile;  // K rows, MN-major (B = K^T of dQ)
+  constexpr int kStage = 4 * kTile;                    // floats per stage
+  constexpr int oKhi = 0, oKlo = kTile;                // K rows: K-major as B = K (S), MN-major as B = K^T (dQ)
+  constexpr int oVhi = 2 * kTile, oVlo = 3 * kTile;    // V rows: B = V (dP)
 
   constexpr uint32_t kCols = 512;
   // one dQ accumulator per compute group (columns kColDQ + g * D): a group's chain of updates is then
@@ -1049,16 +1047,16 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr uint32_t kIdescQ = idesc_tf32(BM, D) | kIdescBMajorMN;
 
   if (issuer) {
-    const OperandDesc dK = operand_desc<D>(smem + oKhi, smem + oKlo), dV = operand_desc<D>(smem + oVhi, smem + oVlo);
-    const OperandDesc dKt = operand_desc_mn(smem + oKThi, smem + oKTlo);
+    const OperandDesc dK = operand_desc_k32(smem + oKhi, smem + oKlo), dV = operand_desc_k32(smem + oVhi, smem + oVlo);
+    const OperandDesc dKt = operand_desc_mn(smem + oKhi, smem + oKlo);
     auto at_stage = [](const OperandDesc& d, int st) {
       const uint64_t adv = (uint64_t)st * (kStage * sizeof(float) / 16);
       return OperandDesc{d.hi + adv, d.lo + adv};
     };
     auto issue_scores = [&](int s) {                   // S, dP of step s into column set s & 1
       const uint32_t set = (uint32_t)(s & 1) * BK;
-      mma3_ts<D>(tmem + kColS + set, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s & (NST - 1)), kIdescS, false);
-      mma3_ts<D>(tmem + kColDP + set, tmem + kColGhi, tmem + kColGlo, at_stage(dV, s & (NST - 1)), kIdescS, false);
+      mma3_ts_k32<D>(tmem + kColS + set, tmem + kColQhi, tmem + kColQlo, at_stage(dK, s & (NST - 1)), kIdescS, false);
+      mma3_ts_k32<D>(tmem + kColDP + set, tmem + kColGhi, tmem + kColGlo, at_stage(dV, s & (NST - 1)), kIdescS, false);
     };
     named_bar_sync(1, kKvPipeThreads);                 // Q / dO rows are in TMEM, stages 0 and 1 are written
     fence_after_sync();
@@ -1106,11 +1104,11 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     auto stage = [&](int st) {
       float* base = smem + st * kStage;
       if (g == 0) {
-        tk0.store_rows_and_mn_as((int)threadIdx.x, base + oKhi, base + oKlo, base + oKThi, base + oKTlo);
-        tv0.store_rows(base + oVhi, base + oVlo);
+        tk0.store_mn(base + oKhi, base + oKlo);
+        tv0.store_mn(base + oVhi, base + oVlo);
       } else {
-        tk1.store_rows_and_mn_as((int)threadIdx.x - kKvGroup, base + oKhi, base + oKlo, base + oKThi, base + oKTlo);
-        tv1.store_rows(base + oVhi, base + oVlo);
+        tk1.store_mn(base + oKhi, base + oKlo);
+        tv1.store_mn(base + oVhi, base + oVlo);
       }
     };
     if (g < nsub) { load(seg_beg + g * BK); stage(g); }
@@ -1289,10 +1287,12 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
     return check_launch("attn_varlen_bwd(tcgen05)");
   }
-  smem_kv += 1024;                                                     // alignment slack of the pipelined kernels
+  // pipelined kernels: 4 stages of 4 tiles [32 x D] (hi / lo of two matrices) + the groups' fp32 totals + alignment slack
+  smem_kv = sizeof(float) * (4 * 4 * 32 * D + 4 * D * BM) + 1024;
+  if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;                      // one CTA per SM either way (512 TMEM columns)
   rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
   if (rc) return rc;
-  size_t smem_q = sizeof(float) * (4 * 6 * 32 * D + 2 * D * BM);       // 4 stages + the groups' fp32 totals
+  size_t smem_q = sizeof(float) * (4 * 4 * 32 * D + 2 * D * BM);       // 4 stages + the groups' fp32 totals
   if (smem_q < 120 * 1024) smem_q = 120 * 1024;
   smem_q += 1024;
   rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");

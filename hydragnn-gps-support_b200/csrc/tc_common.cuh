@@ -393,6 +393,10 @@ __device__ __forceinline__ OperandDesc operand_desc(const float* hi, const float
   return {smem_desc(smem_u32(hi), kLbo, sbo), smem_desc(smem_u32(lo), kLbo, sbo)};
 }
 
+// K-major descriptors of the same tile pair (operand X itself: MN index = row, K index = column < 32)
+__device__ __forceinline__ OperandDesc operand_desc_k32(const float* hi, const float* lo) {
+  return {smem_desc_mn(smem_u32(hi), 1024), smem_desc_mn(smem_u32(lo), 1024)};
+}
 // descriptors of an MN-major tile pair (see smem_desc_mn): [ROWS rows (k)] x [32-column blocks (mn)]
 template <int ROWS = 32>
 __device__ __forceinline__ OperandDesc operand_desc_mn(const float* hi, const float* lo) {
@@ -459,6 +463,22 @@ __device__ __forceinline__ void mma3_ts_mn(uint32_t d_tmem, uint32_t a_hi_tmem, 
 #pragma unroll
   for (int j = 0; j < KD / 8; ++j) {
     const uint64_t adv = static_cast<uint64_t>(j * (8 * 128 / 16));   // 8 rows of 128 bytes per MMA
+    const uint32_t col = j * 8;
+    mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);
+    mma_tf32_ts(d_tmem, a_hi_tmem + col, b.hi + adv, idesc, 1);
+  }
+}
+
+// D (+)= A B^T with A (hi, lo) in TMEM and B = a [N x KD <= 32] row tile in the SWIZZLE_128B_BASE32B layout used
+// K-major (operand_desc_k32); plain K-major `idesc`.
+template <int KD>
+__device__ __forceinline__ void mma3_ts_k32(uint32_t d_tmem, uint32_t a_hi_tmem, uint32_t a_lo_tmem,
+                                            const OperandDesc& b, uint32_t idesc, bool accumulate) {
+  static_assert(KD <= 32, "one 128-byte row holds 32 k values");
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2);                // 32 bytes of every row per MMA
     const uint32_t col = j * 8;
     mma_tf32_ts(d_tmem, a_lo_tmem + col, b.hi + adv, idesc, accumulate || j > 0);
     mma_tf32_ts(d_tmem, a_hi_tmem + col, b.lo + adv, idesc, 1);

@@ -60,18 +60,12 @@ int main(int argc, char** argv) {
   std::vector<float> h(128 * N);
   struct Cfg { uint32_t lbo, sbo, adv, major, ts, layout, extra; const char* name; };
   const Cfg cfgs[] = {
-      {128, 1024, 256, 0, 0, 0, 0, "K-major INTERLEAVE reference"},
-      {16, 1024, 1024, 1, 0, 2, 0, "MN SW128 lbo=16 sbo=1024 adv=1024"},
-      {1024, 128, 1024, 1, 0, 0, 0, "MN INTERLEAVE lbo=1024 sbo=128"},
-      {128, 1024, 256, 0, 0, 0, 1u << 15, "K-major INTERLEAVE, a_major bit set (A one-hot K-major tile)"},
-      {1024, 512, 1024, 1, 0, 1, 0, "MN BASE32B lbo=1024 sbo=512 adv=1024"},
-      {1024, 1024, 1024, 1, 0, 1, 0, "MN BASE32B lbo=1024 sbo=1024 adv=1024"},
-      {512, 1024, 1024, 1, 0, 1, 0, "MN BASE32B lbo=512 sbo=1024 adv=1024"},
-      {4096, 512, 1024, 1, 0, 1, 0, "MN BASE32B lbo=4096 sbo=512 adv=1024"},
-      {16, 512, 512, 1, 0, 1, 0, "MN BASE32B lbo=16 sbo=512 adv=512"},
-      {2048, 512, 512, 1, 0, 4, 0, "MN SW64 lbo=2048 sbo=512 adv=512"},
-      {2048, 256, 256, 1, 0, 6, 0, "MN SW32 lbo=2048 sbo=256 adv=256"},
-      {1024, 128, 1024, 1, 1, 0, 0, "MN INTERLEAVE lbo=1024 sbo=128 (ts)"},
+      {1024, 1024, 32, 0, 0, 1, 0, "K-major BASE32B lbo=1024 sbo=1024 adv=32"},
+      {4096, 1024, 32, 0, 0, 1, 0, "K-major BASE32B lbo=4096 sbo=1024 adv=32"},
+      {1024, 512, 32, 0, 0, 1, 0, "K-major BASE32B lbo=1024 sbo=512 adv=32"},
+      {128, 1024, 32, 0, 0, 1, 0, "K-major BASE32B lbo=128 sbo=1024 adv=32"},
+      {1024, 1024, 32, 0, 1, 1, 0, "K-major BASE32B lbo=1024 sbo=1024 adv=32 (ts)"},
+      {1024, 1024, 64, 0, 0, 1, 0, "K-major BASE32B lbo=1024 sbo=1024 adv=64"},
   };
   const int which = argc > 1 ? atoi(argv[1]) : 0;
   if (which >= (int)(sizeof(cfgs) / sizeof(cfgs[0]))) return 0;
