@@ -16,6 +16,7 @@
 // pad to 64].  fp32 accuracy through 3xTF32 operand splitting as in attn_tc.cu.
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
+#include "tma_host.cuh"
 
 namespace hgk {
 namespace tc {
@@ -577,6 +578,228 @@ k_wgrad_tn(const WgradArgs p) {
   cta_teardown(tmem, kCols);
 }
 
+// ---- the same with TMA loads ------------------------------------------------------------------------
+// The streamed operands arrive by cp.async.bulk.tensor straight in the MN-major operand layout (tensor-map
+// swizzle 128B_ATOM_32B = the matrix descriptor's SWIZZLE_128B_BASE32B), one iteration ahead, into one of two
+// buffers.  kind::tf32 ignores the 13 low mantissa bits of its operands (profiles/_scratch/tf32_round_probe.cu),
+// so the raw fp32 tile IS the `hi` operand; the threads only read it back to form lo = x - hi (and the
+// bias-gradient sums), half of the staging work of k_wgrad_tn and no global-load latency in the loop.  A row
+// scale (cosine envelope) rewrites hi as well; the gaussian B operand is still built by the threads.
+template <int KB, bool GAUSS, int G, int R>
+__global__ void __launch_bounds__(kThreads, 2)
+k_wgrad_tma(const WgradArgs p, const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b) {
+  constexpr int BE = 32;                               // edges per iteration (the MMA K extent)
+  constexpr int GP = (G + 3) / 4 * 4;
+  extern __shared__ __align__(1024) float smem_raw[];
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
+  __shared__ __align__(8) uint64_t bar;                // the iteration's MMAs are complete
+  __shared__ __align__(8) uint64_t full[2];            // the TMA loads of buffer b have landed
+  __shared__ uint32_t tmem_slot;
+  __shared__ float off_s[64];
+  __shared__ __align__(16) float cs_s[2][kFilt];
+  constexpr int kA = kFilt * BE, kB = KB * BE;         // floats per tile
+  float* const Ahi0 = smem;                            // [2][kA]
+  float* const Bhi0 = smem + 2 * kA;                   // [2][kB]
+  float* const Alo = Bhi0 + 2 * kB;
+  float* const Blo = Alo + kA;
+  constexpr int kWgradPromote = 4;
+  constexpr uint32_t kCols = 2 * KB;
+  constexpr uint32_t kColTot = KB;
+  if (threadIdx.x == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); }
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);
+  const uint32_t tmem = cs.tmem;
+  const int warp_u = warp_id_uniform();
+  auto promote = [&](bool first_time) {
+#pragma unroll
+    for (int c0 = 0; c0 < KB / 2; c0 += 16) {
+      const uint32_t col = cs.lane_base + cs.half * (KB / 2) + c0;
+      uint32_t a16[16], t16[16];
+      tmem_ld16(tmem + col, a16);
+      if (!first_time) tmem_ld16(tmem + kColTot + col, t16);
+      tmem_ld_wait();
+      if (!first_time) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) a16[j] = __float_as_uint(__uint_as_float(a16[j]) + __uint_as_float(t16[j]));
+      }
+      tmem_st16(tmem + kColTot + col, a16);
+    }
+    tmem_st_wait();
+  };
+  if (GAUSS && threadIdx.x < 64) off_s[threadIdx.x] = threadIdx.x < G ? p.offset[threadIdx.x] : 0.f;
+  __syncthreads();
+
+  const OperandDesc dA0 = operand_desc_mn<BE>(Ahi0, Alo), dA1 = operand_desc_mn<BE>(Ahi0 + kA, Alo);
+  const OperandDesc dB0 = operand_desc_mn<BE>(Bhi0, Blo), dB1 = operand_desc_mn<BE>(Bhi0 + kB, Blo);
+  constexpr uint32_t kIdesc = idesc_tf32(kFilt, KB) | kIdescAMajorMN | kIdescBMajorMN;
+  const int a_slice = gridDim.y > 1 ? (int)blockIdx.y % p.num_a_slices : 0;
+  const int b_slice = gridDim.y > 1 ? (int)blockIdx.y / p.num_a_slices : 0;
+  const int64_t part = (int64_t)blockIdx.y * gridDim.x + blockIdx.x;     // this CTA's partial slot
+  using TA = Tile<BE, kFilt>;
+  using TB = Tile<BE, KB>;
+  TB tb;                                               // GAUSS: the next B tile, built in registers
+  float dsc[TA::PER];                                  // the next tile's row-scale arguments (d_e)
+  float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);     // this thread's 4 columns of A, summed over its rows
+  const float c2 = p.coeff * kLog2e;
+
+  const int64_t num_tiles = (p.E + BE - 1) / BE;
+  const int64_t stride = gridDim.x;
+  // one thread: the boxes of [32 rows x 32 columns] of tile `tile` into buffer b
+  auto issue_tma = [&](int64_t tile, int b) {
+    const int32_t row0 = (int32_t)(tile * BE);
+    mbar_expect_tx(&full[b], (uint32_t)sizeof(float) * (kA + (GAUSS ? 0 : kB)));
+#pragma unroll
+    for (int blk = 0; blk < kFilt / 32; ++blk)
+      tma_load_2d(Ahi0 + b * kA + blk * (BE * 32), &tm_a, &full[b], a_slice * kFilt + blk * 32, row0);
+    if (!GAUSS) {
+#pragma unroll
+      for (int blk = 0; blk < KB / 32; ++blk)
+        tma_load_2d(Bhi0 + b * kB + blk * (BE * 32), &tm_b, &full[b], b_slice * KB + blk * 32, row0);
+    }
+  };
+  // what still goes through registers, one tile ahead: the row scale and the gaussian operand
+  auto fetch = [&](int64_t tile) {
+    const int32_t row0 = (int32_t)(tile * BE);
+    const int32_t row_end = (int32_t)p.E;
+    if (p.scale_d != nullptr) {
+#pragma unroll
+      for (int it = 0; it < TA::PER; ++it) {
+        int r, c;
+        TA::coord(it, r, c);
+        dsc[it] = 0.f;
+        if (row0 + r < row_end) asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(dsc[it]) : "l"(p.scale_d + row0 + r));
+      }
+    }
+    if (GAUSS) {
+#pragma unroll
+      for (int it = 0; it < TB::PER; ++it) {
+        int r, c;
+        TB::coord(it, r, c);
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t e = (int64_t)row0 + r;
+        if (e < p.E) {
+          const int k0 = 4 * c;
+          if (k0 < G) {
+            const float dd = __ldg(p.d + e);
+            float g[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float t = dd - off_s[k0 + i];
+              g[i] = (k0 + i < G) ? fast_exp2(c2 * (t * t)) : 0.f;
+            }
+            x = make_float4(g[0], g[1], g[2], g[3]);
+          } else if (R > 0 && k0 >= GP && k0 < GP + R) {
+            x = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + (k0 - GP)));
+          }
+        }
+        tb.v[it] = x;
+      }
+    }
+  };
+  // lo tiles (and hi where the threads own it) of the landed tile in buffer b
+  auto stage = [&](int b) {
+    float* Ahi = Ahi0 + b * kA;
+    const bool scaled = p.scale_d != nullptr;
+#pragma unroll
+    for (int it = 0; it < TA::PER; ++it) {
+      int r, c;
+      TA::coord(it, r, c);
+      const int off = TA::mn_off(r, c);
+      float4 v = *reinterpret_cast<const float4*>(Ahi + off);
+      if (scaled) {
+        const float env = 0.5f * (__cosf(dsc[it] * p.pi_over_cutoff) + 1.0f);
+        v.x *= env; v.y *= env; v.z *= env; v.w *= env;
+      }
+      colsum.x += v.x; colsum.y += v.y; colsum.z += v.z; colsum.w += v.w;
+      float4 h, l;
+      split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
+      split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+      if (scaled) *reinterpret_cast<float4*>(Ahi + off) = h;
+      *reinterpret_cast<float4*>(Alo + off) = l;
+    }
+    if (GAUSS) {
+      tb.store_mn(Bhi0 + b * kB, Blo);
+    } else {
+      const float* Bhi = Bhi0 + b * kB;
+#pragma unroll
+      for (int it = 0; it < TB::PER; ++it) {
+        int r, c;
+        TB::coord(it, r, c);
+        const int off = TB::mn_off(r, c);
+        const float4 v = *reinterpret_cast<const float4*>(Bhi + off);
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
+        split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        *reinterpret_cast<float4*>(Blo + off) = l;
+      }
+    }
+  };
+
+  uint32_t parity = 0;
+  int in_chain = 0;            // iterations accumulated since the accumulator was last restarted
+  int promotions = 0;
+  if ((int64_t)blockIdx.x < num_tiles) {
+    if (threadIdx.x == 0) issue_tma(blockIdx.x, 0);
+    fetch(blockIdx.x);
+  }
+  int it = 0;
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += stride, ++it) {
+    const int b = it & 1;
+    // the other buffer was last read by the MMAs of the previous iteration, which have completed
+    if (threadIdx.x == 0 && tile + stride < num_tiles) issue_tma(tile + stride, b ^ 1);
+    mbar_wait(&full[b], (uint32_t)(it >> 1) & 1u);
+    stage(b);
+    publish_operands();        // also orders the promotion's TMEM reads before the restarting MMA
+    if (warp_u == 0 && elect_one_sync()) {
+      fence_after_sync();
+      mma3_ss_mn<BE>(tmem, b ? dA1 : dA0, b ? dB1 : dB0, kIdesc, in_chain > 0);
+      mma_commit(&bar);
+    }
+    if (tile + stride < num_tiles) fetch(tile + stride);
+    mbar_wait(&bar, parity);
+    parity ^= 1;
+    fence_after_sync();
+    if (++in_chain == kWgradPromote) {
+      promote(promotions == 0);
+      ++promotions;
+      in_chain = 0;
+    }
+  }
+  if (in_chain > 0) {          // the unfinished chain
+    promote(promotions == 0);
+    ++promotions;
+  }
+
+  // ---- partial dW: lane n, this thread's KB/2 columns ----
+  float* out = p.dw_partial + (part * kFilt + cs.row_local) * KB + cs.half * (KB / 2);
+  const bool any = (int64_t)blockIdx.x < num_tiles;
+#pragma unroll
+  for (int c0 = 0; c0 < KB / 2; c0 += 32) {
+    uint32_t t[32];
+    tmem_ld32(tmem + kColTot + cs.lane_base + cs.half * (KB / 2) + c0, t);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+      *reinterpret_cast<float4*>(out + c0 + j) =
+          any ? make_float4(__uint_as_float(t[j]), __uint_as_float(t[j + 1]), __uint_as_float(t[j + 2]), __uint_as_float(t[j + 3]))
+              : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  // ---- partial db: as in k_wgrad_tn ----
+#pragma unroll
+  for (int off = 1; off < 4; off <<= 1) {
+    colsum.x += __shfl_xor_sync(0xffffffffu, colsum.x, off);
+    colsum.y += __shfl_xor_sync(0xffffffffu, colsum.y, off);
+    colsum.z += __shfl_xor_sync(0xffffffffu, colsum.z, off);
+    colsum.w += __shfl_xor_sync(0xffffffffu, colsum.w, off);
+  }
+  if ((threadIdx.x & 3) == 0) {
+    const int c = (threadIdx.x >> 2) % (kFilt / 4);
+    *reinterpret_cast<float4*>(&cs_s[threadIdx.x >> 7][4 * c]) = colsum;
+  }
+  __syncthreads();
+  if (threadIdx.x < kFilt) p.db_partial[part * kFilt + threadIdx.x] = cs_s[0][threadIdx.x] + cs_s[1][threadIdx.x];
+  cta_teardown(tmem, kCols);
+}
+
 // Sum of the per-CTA partials of k_wgrad_tn in CTA order (fixed, so the result is reproducible):
 // element i of [dw | db] = sum_p partial[p][i].  Consecutive threads read consecutive addresses.
 __global__ void __launch_bounds__(256)
@@ -737,6 +960,11 @@ extern "C" int hgk_cfconv_wgrad(float* dw_partial, float* db_partial, const floa
                        0, nullptr, 0, 0.f, E, F, stream);
 }
 
+static bool wgrad_use_tma() {
+  static const bool v = [] { const char* e = getenv("HGK_WGRAD_TMA"); return !(e && e[0] == '0'); }();
+  return v;
+}
+
 static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, int64_t lda, const int32_t* a_idx,
                          const float* a2, int64_t lda2, const int32_t* a2_idx,
                          const float* scale_d, float cutoff, const float* b, int64_t ldb, int32_t KB, const float* d,
@@ -772,6 +1000,29 @@ static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, i
     kernel<<<grid, tc::kThreads, smem, st>>>(args);
     return check_launch("wgrad_tn");
   };
+  // plain streamed rows: the TMA kernel (HGK_WGRAD_TMA=0: the register-staged one, for A/B runs); a gathered A
+  // operand, or a driver that will not encode the tensor maps, takes the register-staged kernel
+  if (a_idx == nullptr && wgrad_use_tma()) {
+    CUtensorMap tm_a, tm_b;
+    if (tma::rows_map_32(&tm_a, a, E, F, lda, 32) && (gauss ? true : tma::rows_map_32(&tm_b, b, E, KB, ldb, 32))) {
+      if (gauss) tm_b = tm_a;
+      static bool configured_tma[3] = {false, false, false};
+      auto launch_tma = [&](auto kernel, int kb, int slot) -> int {
+        size_t smem = sizeof(float) * 3 * 32 * (tc::kFilt + kb) + 1024;   // two hi buffers + lo, + alignment slack
+        if (smem < 80 * 1024) smem = 80 * 1024;
+        if (!configured_tma[slot]) {
+          cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+          if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_tn: smem opt-in: %s", cudaGetErrorString(err));
+          configured_tma[slot] = true;
+        }
+        kernel<<<grid, tc::kThreads, smem, st>>>(args, tm_a, tm_b);
+        return check_launch("wgrad_tn(tma)");
+      };
+      if (!gauss) return launch_tma(tc::k_wgrad_tma<128, false, 50, 0>, 128, 0);
+      if (R == 8) return launch_tma(tc::k_wgrad_tma<64, true, 50, 8>, 64, 1);
+      return launch_tma(tc::k_wgrad_tma<64, true, 50, 0>, 64, 2);
+    }
+  }
   if (!gauss) return launch(tc::k_wgrad_tn<128, false, 50, 0>, 128, 0);
   if (R == 8) return launch(tc::k_wgrad_tn<64, true, 50, 8>, 64, 1);
   return launch(tc::k_wgrad_tn<64, true, 50, 0>, 64, 2);
@@ -818,7 +1069,19 @@ extern "C" int hgk_wgrad_rows(float* dw, int64_t lddw, float* db, float* workspa
   }
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((unsigned)P, (unsigned)(nA * nB));
-  tc::k_wgrad_tn<128, false, 50, 0><<<grid, tc::kThreads, smem, st>>>(args);
+  CUtensorMap tm_a, tm_b;
+  if (wgrad_use_tma() && tma::rows_map_32(&tm_a, a, M, NA, lda, 32) && tma::rows_map_32(&tm_b, b, M, NB, ldb, 32)) {
+    size_t smem_tma = sizeof(float) * 3 * 32 * (tc::kFilt + 128) + 1024;
+    static bool configured_tma = false;
+    if (!configured_tma) {
+      cudaError_t err = cudaFuncSetAttribute(tc::k_wgrad_tma<128, false, 50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
+      if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "wgrad_rows: smem opt-in: %s", cudaGetErrorString(err));
+      configured_tma = true;
+    }
+    tc::k_wgrad_tma<128, false, 50, 0><<<grid, tc::kThreads, smem_tma, st>>>(args, tm_a, tm_b);
+  } else {
+    tc::k_wgrad_tn<128, false, 50, 0><<<grid, tc::kThreads, smem, st>>>(args);
+  }
   const int64_t total = (int64_t)nA * nB * tc::kFilt * tc::kFilt + (db ? nA * tc::kFilt : 0);
   tc::k_wgrad_rows_reduce<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(dw, lddw, db, dw_partial, db_partial, (int)P, nA, nB);
   return check_launch("wgrad_rows");

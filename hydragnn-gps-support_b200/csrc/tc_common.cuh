@@ -108,6 +108,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ---- TMA: bulk tensor load global -> shared memory, completion counted in bytes on an mbarrier ----------
+// (tensor maps: tma_host.cuh; they cover this GPU's memory only, and no load here is multicast)
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(float* dst_smem, const void* tensor_map, uint64_t* bar, int32_t col, int32_t row) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(smem_u32(dst_smem)), "l"(reinterpret_cast<uint64_t>(tensor_map)), "r"(smem_u32(bar)), "r"(col), "r"(row)
+      : "memory");
+}
+
 // ---- named barriers: producers arrive and move on, the consumer warp waits ------------------------
 __device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
   asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(count) : "memory");
