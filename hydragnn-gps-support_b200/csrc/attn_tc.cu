@@ -16,10 +16,12 @@
 //     dQ kernel  : lanes = queries;  S, dP (SS)  ->  dS (hi, lo) to TMEM  ->  dQ += dS K     (TS)
 //     dK/dV kern.: lanes = keys;   S^T, dP^T (SS) -> P^T, dS^T to TMEM -> dV += P^T dO, dK += dS^T Q (TS)
 //   Deterministic: every output element is produced by exactly one CTA, no float atomics.
+#include <cstring>
 #include <mutex>
 
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
+#include "tma_host.cuh"
 
 namespace hgk {
 
@@ -764,16 +766,23 @@ __device__ __forceinline__ unsigned long long prof_clock() {
 constexpr int kKvPipeThreads = kKvThreads + 32;
 constexpr int kKvGroup = 256;                          // threads per compute group
 
-template <int D>
+// TMA = true: the Q / dO tiles are not loaded by the compute threads but land by cp.async.bulk.tensor straight in
+// the operand layout, three of the group's steps ahead (8 stages instead of 4); the raw fp32 tile is the hi
+// operand (kind::tf32 ignores the 13 low mantissa bits), the threads read it back only to form lo = x - hi.
+// Q is then used unscaled: the resident K rows carry scale * log2(e) instead, and dK is scaled on the way out.
+// Rows past the end of the segment are whatever follows in memory (finite); their columns are masked below.
+template <int D, bool TMA>
 __global__ void __launch_bounds__(kKvPipeThreads, 1)
-k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv) {
+k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dk, float* __restrict__ dv,
+                   const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_g) {
   constexpr int BQ = 32;                               // queries per pipeline step
   constexpr int QC = BQ / 2;                           // query columns per thread
-  constexpr int NST = 4;                               // shared-memory stages
+  constexpr int NST = TMA ? 8 : 4;                     // shared-memory stages
   extern __shared__ __align__(1024) float smem_raw[];
   // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
   float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
+  __shared__ __align__(8) uint64_t full[NST];          // TMA: the tiles of stage st have landed
   __shared__ uint32_t tmem_slot;
   __shared__ __align__(16) float lse2_s[NST][BQ], delta_s[NST][BQ];
   int32_t seg_beg, seg_end, key0;
@@ -795,7 +804,13 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
   constexpr uint32_t kColST = 0, kColDPT = 64, kColPlo = 128, kColDSlo = 192, kColAcc = 256;
   constexpr uint32_t kColKhi = 256 + 4 * D, kColKlo = 256 + 5 * D, kColVhi = 256 + 6 * D, kColVlo = 256 + 7 * D;
   static_assert(256 + 8 * D <= 512, "TMEM budget");
-  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }   // bar[0]: cta_setup, which also publishes all three
+  if (threadIdx.x == 0) {                              // bar[0]: cta_setup, which also publishes the others
+    mbar_init(&bar[1], 1); mbar_init(&bar[2], 1);
+    if (TMA) {
+#pragma unroll
+      for (int i = 0; i < NST; ++i) mbar_init(&full[i], 1);
+    }
+  }
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BQ - 1) / BQ;
@@ -851,7 +866,8 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       const int64_t krow_ld = key0 + cs.row_local;
       const bool kok = krow_ld < seg_end;
       if (part < 2)
-        row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, part, 1.f);
+        row_to_tmem<D>(tmem + cs.lane_base + kColKhi, tmem + cs.lane_base + kColKlo, p.k + h * D, p.ldk, krow_ld, kok, part,
+                       TMA ? p.scale * kLog2e : 1.f);
       else
         row_to_tmem<D>(tmem + cs.lane_base + kColVhi, tmem + cs.lane_base + kColVlo, p.v + h * D, p.ldv, krow_ld, kok, part - 2, 1.f);
     }
@@ -861,9 +877,19 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     float lse_r = 0.f, delta_r = 0.f;                  // next step's row statistics (first warp of the group)
     const int tl = (int)threadIdx.x - g * kKvGroup;    // thread index inside the group
     const float qmul = p.scale * kLog2e;
+    // TMA: one thread of the group requests the two tiles of step s (stage s % NST)
+    auto request = [&](int s) {
+      const int st = s & (NST - 1);
+      float* base = smem + st * kStage;
+      mbar_expect_tx(&full[st], 2u * kTile * (uint32_t)sizeof(float));
+      tma_load_2d(base + oQhi, &tm_q, &full[st], h * D, seg_beg + s * BQ);
+      tma_load_2d(base + oGhi, &tm_g, &full[st], h * D, seg_beg + s * BQ);
+    };
     auto load = [&](int32_t q_at) {
-      if (g == 0) { tq0.load(p.q + h * D, p.ldq, q_at, seg_end); tg0.load(b.dout + h * D, b.lddo, q_at, seg_end); }
-      else        { tq1.load(p.q + h * D, p.ldq, q_at, seg_end); tg1.load(b.dout + h * D, b.lddo, q_at, seg_end); }
+      if (!TMA) {
+        if (g == 0) { tq0.load(p.q + h * D, p.ldq, q_at, seg_end); tg0.load(b.dout + h * D, b.lddo, q_at, seg_end); }
+        else        { tq1.load(p.q + h * D, p.ldq, q_at, seg_end); tg1.load(b.dout + h * D, b.lddo, q_at, seg_end); }
+      }
       if (tl < BQ) {
         const int32_t qrow = q_at + tl;
         lse_r = 0.f; delta_r = 0.f;
@@ -873,9 +899,23 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
         }
       }
     };
-    auto stage = [&](int st) {
+    auto stage = [&](int s) {
+      const int st = s & (NST - 1);
       float* base = smem + st * kStage;
-      if (g == 0) {
+      if (TMA) {
+        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested three of my steps ago
+        int r, c;
+        Tile<BQ, D, kKvGroup, 0>::coord_of(tl, 0, r, c);    // one 16-byte chunk of each tile per thread
+        static_assert(Tile<BQ, D, kKvGroup, 0>::PER == 1, "one chunk per thread");
+        const int off = Tile<BQ, D, kKvGroup, 0>::mn_off(r, c);
+        const float4 q4 = *reinterpret_cast<const float4*>(base + oQhi + off);
+        const float4 g4 = *reinterpret_cast<const float4*>(base + oGhi + off);
+        float4 hq, lq, hg, lg;
+        split_tf32(q4.x, hq.x, lq.x); split_tf32(q4.y, hq.y, lq.y); split_tf32(q4.z, hq.z, lq.z); split_tf32(q4.w, hq.w, lq.w);
+        split_tf32(g4.x, hg.x, lg.x); split_tf32(g4.y, hg.y, lg.y); split_tf32(g4.z, hg.z, lg.z); split_tf32(g4.w, hg.w, lg.w);
+        *reinterpret_cast<float4*>(base + oQlo + off) = lq;
+        *reinterpret_cast<float4*>(base + oGlo + off) = lg;
+      } else if (g == 0) {
         tq0.scale(qmul);
         tq0.store_mn_as(tl, base + oQhi, base + oQlo);
         tg0.store_mn_as(tl, base + oGhi, base + oGlo);
@@ -890,6 +930,11 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       }
     };
 
+    if (TMA && tl == 0) {                              // my first three steps' tiles are on their way
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        if (g + 2 * j < nsub) request(g + 2 * j);
+    }
     if (g < nsub) { load(seg_beg + g * BQ); stage(g); }
     fence_smem_to_async();
     fence_before_sync();
@@ -907,6 +952,8 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       par ^= 1;
       fence_after_sync();
       KV_PROF(0)
+      // the MMAs of my previous step are complete: its stage, (s - 2) % NST == (s + 6) % NST, is free again
+      if (TMA && tl == 0 && s + 6 < nsub) request(s + 6);
       const int ls = s >> 1;                           // index of this step among the group's steps
       if (ls > 0 && ls % kPromote == 0) {              // the issuer restarts the group's dV / dK with this step
 #pragma unroll
@@ -962,7 +1009,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       tmem_st_wait();
       KV_PROF(3)
 
-      if (s + 2 < nsub) stage((s + 2) & (NST - 1));    // registers -> stage of my next step
+      if (s + 2 < nsub) stage(s + 2);                  // lo tiles (registers -> stage) of my next step
       KV_PROF(4)
       fence_smem_to_async();
       fence_before_sync();
@@ -998,7 +1045,8 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       for (int j = 0; j < EC; ++j) accv[j] += __uint_as_float(t[j]) + (steps > kPromote ? tg[j * BM] : 0.f);
     }
     if (ok) {
-      const float mul = is_k ? kLn2 : 1.f;             // Q was staged as q * scale * log2(e)
+      // Q was staged as q * scale * log2(e) (TMA: unscaled, the scores' scale sits on the K rows)
+      const float mul = is_k ? (TMA ? p.scale : kLn2) : 1.f;
       float* orow = (is_k ? dk : dv) + (int64_t)krow * b.ldg + h * D + chalf * EC;
 #pragma unroll
       for (int j = 0; j < EC; j += 4)
@@ -1011,16 +1059,19 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
 // ---- dQ: the same pipeline, CTA = 128 queries (TMEM lane = query), 32-key steps ----------------
 // Q and dO rows (hi, lo) are resident in TMEM as the A operands of S = Q K^T and dP = dO V^T;
 // dS (hi, lo) overwrites the step's S / dP columns and is the A operand of dQ += dS K.
-template <int D>
+// TMA = true: K / V tiles by cp.async.bulk.tensor, as in k_attn_bwd_kv_pipe.
+template <int D, bool TMA>
 __global__ void __launch_bounds__(kKvPipeThreads, 1)
-k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dq) {
+k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__ dq,
+                  const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v) {
   constexpr int BK = 32;                               // keys per pipeline step
   constexpr int KC = BK / 2;                           // key columns per thread
-  constexpr int NST = 4;                               // shared-memory stages
+  constexpr int NST = TMA ? 8 : 4;                     // shared-memory stages
   extern __shared__ __align__(1024) float smem_raw[];
   // the MN-major operand tiles need 1024-byte alignment; the launchers request 1024 bytes more than the layout
   float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar[3];             // [g]: column set g is ready; [2]: everything done
+  __shared__ __align__(8) uint64_t full[NST];          // TMA: the tiles of stage st have landed
   __shared__ uint32_t tmem_slot;
   int32_t seg_beg, seg_end, row0;
   if (!locate_tile128(p.cu, p.S, blockIdx.x, &seg_beg, &seg_end, &row0)) return;
@@ -1039,7 +1090,13 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
   constexpr uint32_t kColS = 0, kColDP = 64, kColDQ = 128;
   constexpr uint32_t kColQhi = 128 + 2 * D, kColQlo = 128 + 3 * D, kColGhi = 128 + 4 * D, kColGlo = 128 + 5 * D;
   static_assert(128 + 6 * D <= 512, "TMEM budget");
-  if (threadIdx.x == 0) { mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); }
+  if (threadIdx.x == 0) {
+    mbar_init(&bar[1], 1); mbar_init(&bar[2], 1);
+    if (TMA) {
+#pragma unroll
+      for (int k = 0; k < NST; ++k) mbar_init(&full[k], 1);
+    }
+  }
   const CtaSetup cs = cta_setup(&bar[0], &tmem_slot, kCols);  // cs.half = warp / 4
   const uint32_t tmem = cs.tmem;
   const int nsub = (seg_end - seg_beg + BK - 1) / BK;
@@ -1097,13 +1154,37 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
 
     Tile<BK, D, kKvGroup, 0> tk0, tv0;                 // the group's next K and V tiles, in registers
     Tile<BK, D, kKvGroup, kKvGroup> tk1, tv1;
+    const int tl = (int)threadIdx.x - g * kKvGroup;    // thread index inside the group
+    // TMA: one thread of the group requests the two tiles of step s (stage s % NST)
+    auto request = [&](int s) {
+      const int st = s & (NST - 1);
+      float* base = smem + st * kStage;
+      mbar_expect_tx(&full[st], 2u * kTile * (uint32_t)sizeof(float));
+      tma_load_2d(base + oKhi, &tm_k, &full[st], h * D, seg_beg + s * BK);
+      tma_load_2d(base + oVhi, &tm_v, &full[st], h * D, seg_beg + s * BK);
+    };
     auto load = [&](int32_t k_at) {
+      if (TMA) return;
       if (g == 0) { tk0.load(p.k + h * D, p.ldk, k_at, seg_end); tv0.load(p.v + h * D, p.ldv, k_at, seg_end); }
       else        { tk1.load(p.k + h * D, p.ldk, k_at, seg_end); tv1.load(p.v + h * D, p.ldv, k_at, seg_end); }
     };
-    auto stage = [&](int st) {
+    auto stage = [&](int s) {
+      const int st = s & (NST - 1);
       float* base = smem + st * kStage;
-      if (g == 0) {
+      if (TMA) {
+        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested three of my steps ago
+        int r, c;
+        Tile<BK, D, kKvGroup, 0>::coord_of(tl, 0, r, c);    // one 16-byte chunk of each tile per thread
+        static_assert(Tile<BK, D, kKvGroup, 0>::PER == 1, "one chunk per thread");
+        const int off = Tile<BK, D, kKvGroup, 0>::mn_off(r, c);
+        const float4 k4 = *reinterpret_cast<const float4*>(base + oKhi + off);
+        const float4 v4 = *reinterpret_cast<const float4*>(base + oVhi + off);
+        float4 hk, lk, hv, lv;
+        split_tf32(k4.x, hk.x, lk.x); split_tf32(k4.y, hk.y, lk.y); split_tf32(k4.z, hk.z, lk.z); split_tf32(k4.w, hk.w, lk.w);
+        split_tf32(v4.x, hv.x, lv.x); split_tf32(v4.y, hv.y, lv.y); split_tf32(v4.z, hv.z, lv.z); split_tf32(v4.w, hv.w, lv.w);
+        *reinterpret_cast<float4*>(base + oKlo + off) = lk;
+        *reinterpret_cast<float4*>(base + oVlo + off) = lv;
+      } else if (g == 0) {
         tk0.store_mn(base + oKhi, base + oKlo);
         tv0.store_mn(base + oVhi, base + oVlo);
       } else {
@@ -1111,6 +1192,11 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
         tv1.store_mn(base + oVhi, base + oVlo);
       }
     };
+    if (TMA && tl == 0) {                              // my first three steps' tiles are on their way
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        if (g + 2 * j < nsub) request(g + 2 * j);
+    }
     if (g < nsub) { load(seg_beg + g * BK); stage(g); }
     fence_smem_to_async();
     fence_before_sync();
@@ -1125,6 +1211,8 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       mbar_wait(&bar[g], par);
       par ^= 1;
       fence_after_sync();
+      // the MMAs of my previous step are complete: its stage, (s - 2) % NST == (s + 6) % NST, is free again
+      if (TMA && tl == 0 && s + 6 < nsub) request(s + 6);
       const int ls = s >> 1;                           // index of this step among the group's steps
       if (ls > 0 && ls % kPromote == 0) {              // the issuer restarts dQ_g with this step's update
         uint32_t qa[KC];
@@ -1160,7 +1248,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       tmem_st16(tmem + cs.lane_base + kColDP + set + col0, dv);
       tmem_st_wait();
 
-      if (s + 2 < nsub) stage((s + 2) & (NST - 1));
+      if (s + 2 < nsub) stage(s + 2);
       fence_smem_to_async();
       fence_before_sync();
       named_bar_arrive(2 + g, kKvGroup + 32);
@@ -1287,15 +1375,27 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
     k_attn_bwd_q_tc<D><<<grid, kThreads, smem_q, st>>>(a, b, dq);
     return check_launch("attn_varlen_bwd(tcgen05)");
   }
-  // pipelined kernels: 4 stages of 4 tiles [32 x D] (hi / lo of two matrices) + the groups' fp32 totals + alignment slack
-  smem_kv = sizeof(float) * (4 * 4 * 32 * D + 4 * D * BM) + 1024;
+  // pipelined kernels: stages of 4 tiles [32 x D] (hi / lo of two matrices) + the groups' fp32 totals + alignment
+  // slack; 4 stages filled from registers, or 8 filled by TMA (HGK_ATTN_BWD_TMA=0: the register path, A/B runs)
+  static const bool want_tma = [] { const char* e = getenv("HGK_ATTN_BWD_TMA"); return !(e && e[0] == '0'); }();
+  CUtensorMap tm_q, tm_k, tm_v, tm_g;
+  const int64_t cols = (int64_t)a.H * D;
+  const bool use_tma = want_tma && tma::rows_map_32(&tm_q, a.q, N, cols, a.ldq, 32) && tma::rows_map_32(&tm_k, a.k, N, cols, a.ldk, 32) &&
+                       tma::rows_map_32(&tm_v, a.v, N, cols, a.ldv, 32) && tma::rows_map_32(&tm_g, b.dout, N, cols, b.lddo, 32);
+  const int nst = use_tma ? 8 : 4;
+  smem_kv = sizeof(float) * (nst * 4 * 32 * D + 4 * D * BM) + 1024;
   if (smem_kv < 120 * 1024) smem_kv = 120 * 1024;                      // one CTA per SM either way (512 TMEM columns)
-  rc = opt_in_smem(k_attn_bwd_kv_pipe<D>, smem_kv, "attn_bwd_kv_pipe");
-  if (rc) return rc;
-  size_t smem_q = sizeof(float) * (4 * 4 * 32 * D + 2 * D * BM);       // 4 stages + the groups' fp32 totals
+  size_t smem_q = sizeof(float) * (nst * 4 * 32 * D + 2 * D * BM) + 1024;
   if (smem_q < 120 * 1024) smem_q = 120 * 1024;
-  smem_q += 1024;
-  rc = opt_in_smem(k_attn_bwd_q_pipe<D>, smem_q, "attn_bwd_q_pipe");
+  if (use_tma) {
+    rc = opt_in_smem(k_attn_bwd_kv_pipe<D, true>, smem_kv, "attn_bwd_kv_pipe(tma)");
+    if (rc) return rc;
+    rc = opt_in_smem(k_attn_bwd_q_pipe<D, true>, smem_q, "attn_bwd_q_pipe(tma)");
+  } else {
+    rc = opt_in_smem(k_attn_bwd_kv_pipe<D, false>, smem_kv, "attn_bwd_kv_pipe");
+    if (rc) return rc;
+    rc = opt_in_smem(k_attn_bwd_q_pipe<D, false>, smem_q, "attn_bwd_q_pipe");
+  }
   if (rc) return rc;
   // The dK/dV and dQ kernels are independent and each runs one CTA per SM: 256 + 256 CTAs on 148 SMs are
   // two partly empty second waves when the kernels run back to back.  With the dQ kernel on a second
@@ -1306,8 +1406,14 @@ int launch_bwd(const AttnTcArgs& a, const AttnTcBwdArgs& b, float* dq, float* dk
   SideStream* ss = overlap ? side_stream() : nullptr;
   const bool forked = ss != nullptr && cudaEventRecord(ss->fork, st) == cudaSuccess &&
                       cudaStreamWaitEvent(ss->stream, ss->fork, 0) == cudaSuccess;
-  k_attn_bwd_kv_pipe<D><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv);
-  k_attn_bwd_q_pipe<D><<<grid, kKvPipeThreads, smem_q, forked ? ss->stream : st>>>(a, b, dq);
+  if (use_tma) {
+    k_attn_bwd_kv_pipe<D, true><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv, tm_q, tm_g);
+    k_attn_bwd_q_pipe<D, true><<<grid, kKvPipeThreads, smem_q, forked ? ss->stream : st>>>(a, b, dq, tm_k, tm_v);
+  } else {
+    memset(&tm_q, 0, sizeof(tm_q));                    // unused by the register-staged kernels
+    k_attn_bwd_kv_pipe<D, false><<<grid, kKvPipeThreads, smem_kv, st>>>(a, b, dk, dv, tm_q, tm_q);
+    k_attn_bwd_q_pipe<D, false><<<grid, kKvPipeThreads, smem_q, forked ? ss->stream : st>>>(a, b, dq, tm_q, tm_q);
+  }
   if (forked) {
     if (cudaEventRecord(ss->join, ss->stream) != cudaSuccess || cudaStreamWaitEvent(st, ss->join, 0) != cudaSuccess)
       return fail(HGK_ERR_CUDA, "attn_varlen_bwd: joining the side stream failed: %s", cudaGetErrorString(cudaGetLastError()));
