@@ -14,6 +14,7 @@
 // `raw` is the un-embedded edge attribute of nn.FactoredEdgeAttr (e.g. rel_pe, r = 8 columns) whose
 // embedding matrix is folded into W0' on the host; W0' columns are [G gaussians | pad to 4 | r raw |
 // pad to 64].  fp32 accuracy through 3xTF32 operand splitting as in attn_tc.cu.
+#include <cstring>
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
 #include "tma_host.cuh"
@@ -37,6 +38,7 @@ struct FilterArgs {
   float* h;                       // [E, 128] out: ssp(Z0 + b0)   (kept for the backward)
   float* w;                       // [E, 128] out: filter
   int64_t E;
+  int tma_out;                    // TMA variant: bit 0: h through the bulk store, bit 1: w (else row-per-thread stores)
 };
 
 __device__ __forceinline__ float fast_log2(float x) {
@@ -70,17 +72,24 @@ __device__ __forceinline__ unsigned long long fprof_clock() {
 #define F_PROF_FLUSH
 #endif
 
-template <int G, int R>
+// TMA = true: h and w leave through shared memory and cp.async.bulk.tensor stores.  A thread owns 32 columns of one
+// row; written straight to global memory that is one LSU wavefront per 32 bytes (the two epilogues' stores cost
+// ~8k of the 17k cycles of a tile, profiles/filter_phase_profile.py).  Instead each column quarter (4 warps) has an
+// 8 KB buffer [128 rows x 16 columns] (64-byte swizzle: row-per-thread 16-byte stores without bank conflicts),
+// filled and handed to one bulk store twice per epilogue; the global writes drain while the next MMAs run.
+template <int G, int R, bool TMA>
 __global__ void __launch_bounds__(kFiltThreads, 1)
-k_schnet_filter_fwd(const FilterArgs p) {
+k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_w) {
   constexpr int GP = (G + 3) / 4 * 4;
   static_assert(GP + R <= kK0 && R % 4 == 0 && G > 48 && GP <= 52, "input layout: gaussians end in the last quarter");
-  extern __shared__ __align__(128) float smem[];
+  extern __shared__ __align__(512) float smem_raw[];
+  float* const smem = smem_raw + (((512u - (smem_u32(smem_raw) & 511u)) & 511u) >> 2);
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   __shared__ float off_s[kK0], b0_s[kFilt], b1_s[kFilt];
 
-  float* W0hi = smem;                 float* W0lo = W0hi + kFilt * kK0;
+  float* sbuf = smem;                 // TMA: [4 quarters][128 rows][16 floats] staging of the outputs
+  float* W0hi = smem + (TMA ? 4 * kFilt * 16 : 0);   float* W0lo = W0hi + kFilt * kK0;
   float* W1hi = W0lo + kFilt * kK0;   float* W1lo = W1hi + kFilt * kFilt;
 
   constexpr uint32_t kCols = 512;
@@ -109,6 +118,27 @@ k_schnet_filter_fwd(const FilterArgs p) {
   uint32_t parity = 0;
   const float c2 = p.coeff * kLog2e;
   const int64_t num_tiles = (p.E + kFilt - 1) / kFilt;
+  // TMA: this thread's 32 columns v[0..31] of row (tile, row_local) -> two bulk stores of the quarter's buffer
+  float* const qbuf = sbuf + quarter * (kFilt * 16);
+  const bool q_issuer = cs.row_local == 0;             // first thread of the quarter's four warps
+  auto store_quarter = [&](const CUtensorMap* map, const uint32_t (&v)[32], int64_t tile) {
+#pragma unroll
+    for (int ph = 0; ph < 2; ++ph) {
+      if (q_issuer) tma_store_wait_read();             // the previous store has read the buffer
+      named_bar_sync(4 + quarter, 128);
+      float* rowp = qbuf + cs.row_local * 16;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<uint4*>(rowp + ((j ^ ((cs.row_local >> 1) & 3)) << 2)) =
+            make_uint4(v[ph * 16 + 4 * j], v[ph * 16 + 4 * j + 1], v[ph * 16 + 4 * j + 2], v[ph * 16 + 4 * j + 3]);
+      fence_smem_to_async();
+      named_bar_sync(4 + quarter, 128);
+      if (q_issuer) {
+        tma_store_2d(map, qbuf, quarter * 32 + ph * 16, (int32_t)(tile * kFilt));
+        tma_store_commit();
+      }
+    }
+  };
   F_PROF_DECL
   for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     F_PROF(7)
@@ -181,7 +211,9 @@ k_schnet_filter_fwd(const FilterArgs p) {
         z[j] = __float_as_uint(hv);
         lo[j] = __float_as_uint(lo_);
       }
-      if (ok) {
+      if (TMA && (p.tma_out & 1)) {
+        store_quarter(&tm_h, z, tile);
+      } else if (ok) {
         float* hrow = p.h + e * kFilt + c0;
 #pragma unroll
         for (int j = 0; j < 32; j += 8)
@@ -215,7 +247,11 @@ k_schnet_filter_fwd(const FilterArgs p) {
       uint32_t z[32];
       tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
       tmem_ld_wait();
-      if (ok) {
+      if (TMA && (p.tma_out & 2)) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) z[j] = __float_as_uint((__uint_as_float(z[j]) + b1_s[c0 + j]) * env);
+        store_quarter(&tm_w, z, tile);
+      } else if (ok) {
         float* wrow = p.w + e * kFilt + c0;
 #pragma unroll
         for (int j = 0; j < 32; j += 8) {
@@ -230,6 +266,7 @@ k_schnet_filter_fwd(const FilterArgs p) {
   }
   F_PROF(7)
   F_PROF_FLUSH
+  if (TMA && q_issuer) tma_store_wait();               // my bulk stores are complete before the CTA retires
   cta_teardown(tmem, kCols);
 }
 
@@ -254,13 +291,24 @@ struct FilterBwdArgs {
   int64_t E;
 };
 
+// TMA = true (a materialised gw): the [128 x 128] gradient tile of the NEXT tile is requested with four
+// cp.async.bulk.tensor boxes as soon as every thread has consumed the current one, and lands (128-byte swizzle:
+// a thread reads its own row without bank conflicts) while the MMAs and the epilogue run.  Before, each tile began
+// with a full DRAM round trip, fetched as row-per-lane 32-byte pieces (one LSU wavefront per 32 bytes).
+// (dz0 through shared memory and bulk stores, as in the forward kernel, was tried: 0.155 -> 0.174 ms, the two
+// store phases per tile wait for each other; its row-per-thread stores already overlap the next tile's start.)
+template <bool TMA>
 __global__ void __launch_bounds__(kFiltThreads, 1)
-k_schnet_filter_bwd(const FilterBwdArgs p) {
-  extern __shared__ __align__(128) float smem[];
+k_schnet_filter_bwd(const FilterBwdArgs p, const __grid_constant__ CUtensorMap tm_gw) {
+  extern __shared__ __align__(1024) float smem_raw[];
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
   __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t full;               // TMA: the gw tile has landed
   __shared__ uint32_t tmem_slot;
   float* Whi = smem;
   float* Wlo = Whi + kFilt * kFilt;
+  float* gbuf = Wlo + kFilt * kFilt;                   // TMA: [4 column blocks][128 rows][32 floats], swizzled
+  if (TMA && threadIdx.x == 0) mbar_init(&full, 1);
   constexpr uint32_t kCols = 512;
   constexpr uint32_t kColAhi = 0, kColAlo = 128, kColDH = 256;
   const CtaSetup cs = cta_setup(&bar, &tmem_slot, kCols);     // cs.half = column quarter 0..3
@@ -278,12 +326,40 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
 
   uint32_t parity = 0;
   const int64_t num_tiles = (p.E + kFilt - 1) / kFilt;
+  auto request = [&](int64_t tile) {                   // one thread
+    mbar_expect_tx(&full, (uint32_t)sizeof(float) * kFilt * kFilt);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) tma_load_2d(gbuf + q * (kFilt * 32), &tm_gw, &full, q * 32, (int32_t)(tile * kFilt));
+  };
+  if (TMA && threadIdx.x == 0 && (int64_t)blockIdx.x < num_tiles) request(blockIdx.x);
+  uint32_t full_parity = 0;
   for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const int64_t e = tile * kFilt + cs.row_local;
     const bool ok = e < p.E;
     const float dist = ok ? __ldg(p.d + e) : 0.f;
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);
-    {
+    if (TMA) {
+      mbar_wait(&full, full_parity);
+      full_parity ^= 1;
+      // my row's 32 columns: block cs.half, 16-byte chunk j stored at chunk j ^ (row & 7)
+      const float* rowp = gbuf + cs.half * (kFilt * 32) + cs.row_local * 32;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 g4 = *reinterpret_cast<const float4*>(rowp + ((j ^ (cs.row_local & 7)) << 2));
+        const float x[4] = {g4.x * env, g4.y * env, g4.z * env, g4.w * env};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float h_, l_;
+          split_tf32(ok ? x[i] : 0.f, h_, l_);
+          hi[4 * j + i] = __float_as_uint(h_);
+          lo[4 * j + i] = __float_as_uint(l_);
+        }
+      }
+      tmem_st32(tmem + cs.lane_base + kColAhi + c0, hi);
+      tmem_st32(tmem + cs.lane_base + kColAlo + c0, lo);
+      tmem_st_wait();
+    } else {
       const bool gathered = p.gw == nullptr;
       const float* grow = nullptr;
       const float* xrow = nullptr;
@@ -327,6 +403,8 @@ k_schnet_filter_bwd(const FilterBwdArgs p) {
       fence_after_sync();
       mma3_ts<kFilt>(tmem + kColDH, tmem + kColAhi, tmem + kColAlo, dW, kIdesc, false);   // dH = dZ1 W1
       mma_commit(&bar);
+      // every thread has read its row of the gw tile (the barrier above): the buffer takes the next tile's
+      if (TMA && tile + gridDim.x < num_tiles) request(tile + gridDim.x);
     }
     // the saved activations of this thread's columns arrive while the MMAs run
     float4 hv[8];
@@ -873,36 +951,56 @@ extern "C" int hgk_schnet_filter_fwd(float* w, float* h, const float* d, const f
   if (F != tc::kFilt || G != 50 || !(R == 0 || R == 8))
     return fail(HGK_ERR_UNSUPPORTED, "schnet_filter_fwd: built for F=128, G=50, R in {0, 8} (got F=%d G=%d R=%d)", F, G, R);
   HGK_REQUIRE(R == 0 || (ldr % 4 == 0 && (reinterpret_cast<uintptr_t>(raw) & 15) == 0), "schnet_filter_fwd: raw must be 16-byte aligned rows");
-  tc::FilterArgs a{d, raw, ldr, offset, coeff, 3.14159265358979323846f / cutoff, w0p, b0, w1, b1, h, w, E};
+  tc::FilterArgs a{d, raw, ldr, offset, coeff, 3.14159265358979323846f / cutoff, w0p, b0, w1, b1, h, w, E, 3};
   // torch evaluates d * pi / cutoff; keep that operation order exactly in the kernel argument
   a.pi_over_cutoff = 3.14159265358979323846f / cutoff;
-  const size_t smem = sizeof(float) * (2 * tc::kFilt * tc::kK0 + 2 * tc::kFilt * tc::kFilt);
+  // resident weights (hi, lo) + alignment slack; the TMA variant adds the 32 KB output staging
+  // HGK_FILTER_FWD_TMA = 0 (row-per-thread stores) | 1 (h by bulk store) | 2 (w) | 3 (both, default)
+  static const int tma_out = [] { const char* e = getenv("HGK_FILTER_FWD_TMA"); return e && e[0] >= '0' && e[0] <= '3' ? e[0] - '0' : 3; }();
+  a.tma_out = tma_out;
+  CUtensorMap tm_h, tm_w;
+  const bool use_tma = tma_out != 0 && tma::rows_map_store16(&tm_h, h, E, tc::kFilt, tc::kFilt, 128) &&
+                       tma::rows_map_store16(&tm_w, w, E, tc::kFilt, tc::kFilt, 128);
+  if (!use_tma) memset(&tm_h, 0, sizeof(tm_h)), memset(&tm_w, 0, sizeof(tm_w));
+  const size_t smem = sizeof(float) * (2 * tc::kFilt * tc::kK0 + 2 * tc::kFilt * tc::kFilt + (use_tma ? 4 * tc::kFilt * 16 : 0)) + 512;
   const int64_t tiles = ceil_div(E, tc::kFilt);
   const unsigned grid = (unsigned)imin64(tiles, kNumSM);
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t err;
-  static bool configured[2] = {false, false};
-  if (!configured[R == 8 ? 1 : 0]) {
-    err = R == 8 ? cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                 : cudaFuncSetAttribute(tc::k_schnet_filter_fwd<50, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in: %s", cudaGetErrorString(err));
-    configured[R == 8 ? 1 : 0] = true;
-  }
-  if (R == 8) tc::k_schnet_filter_fwd<50, 8><<<grid, tc::kFiltThreads, smem, st>>>(a);
-  else tc::k_schnet_filter_fwd<50, 0><<<grid, tc::kFiltThreads, smem, st>>>(a);
-  return check_launch("schnet_filter_fwd");
+  static bool configured[4] = {false, false, false, false};
+  auto launch = [&](auto kernel, int slot) -> int {
+    if (!configured[slot]) {
+      cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_fwd: smem opt-in (%zu B): %s", smem, cudaGetErrorString(err));
+      configured[slot] = true;
+    }
+    kernel<<<grid, tc::kFiltThreads, smem, st>>>(a, tm_h, tm_w);
+    return check_launch("schnet_filter_fwd");
+  };
+  if (use_tma) return R == 8 ? launch(tc::k_schnet_filter_fwd<50, 8, true>, 0) : launch(tc::k_schnet_filter_fwd<50, 0, true>, 1);
+  return R == 8 ? launch(tc::k_schnet_filter_fwd<50, 8, false>, 2) : launch(tc::k_schnet_filter_fwd<50, 0, false>, 3);
 }
 
 static int filter_bwd_launch(const tc::FilterBwdArgs& a, void* stream) {
-  const size_t smem = sizeof(float) * 2 * tc::kFilt * tc::kFilt;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t err = cudaFuncSetAttribute(tc::k_schnet_filter_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // resident W1^T (hi, lo) + alignment slack; the TMA variant adds the [128 x 128] gradient tile buffer
+  static const bool want_tma = [] { const char* e = getenv("HGK_FILTER_BWD_TMA"); return !(e && e[0] == '0'); }();
+  CUtensorMap tm_gw;
+  const bool use_tma = want_tma && a.gw != nullptr && tma::rows_map_128b(&tm_gw, a.gw, a.E, tc::kFilt, tc::kFilt, 128);
+  const size_t smem = sizeof(float) * (2 + (use_tma ? 1 : 0)) * tc::kFilt * tc::kFilt + 1024;
+  static bool configured[2] = {false, false};
+  if (!configured[use_tma]) {
+    cudaError_t err = use_tma
+        ? cudaFuncSetAttribute(tc::k_schnet_filter_bwd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+        : cudaFuncSetAttribute(tc::k_schnet_filter_bwd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "schnet_filter_bwd: smem opt-in: %s", cudaGetErrorString(err));
-    configured = true;
+    configured[use_tma] = true;
   }
   const unsigned grid = (unsigned)imin64(ceil_div(a.E, tc::kFilt), kNumSM);
-  tc::k_schnet_filter_bwd<<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a);
+  if (use_tma) {
+    tc::k_schnet_filter_bwd<true><<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a, tm_gw);
+  } else {
+    memset(&tm_gw, 0, sizeof(tm_gw));
+    tc::k_schnet_filter_bwd<false><<<grid, tc::kFiltThreads, smem, (cudaStream_t)stream>>>(a, tm_gw);
+  }
   return check_launch("schnet_filter_bwd");
 }
 

@@ -120,6 +120,17 @@ __device__ __forceinline__ void tma_load_2d(float* dst_smem, const void* tensor_
       : "memory");
 }
 
+// bulk tensor store shared memory -> global (rows past the tensor's end are clipped), tracked in bulk groups
+__device__ __forceinline__ void tma_store_2d(const void* tensor_map, const float* src_smem, int32_t col, int32_t row) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               :: "l"(reinterpret_cast<uint64_t>(tensor_map)), "r"(smem_u32(src_smem)), "r"(col), "r"(row) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// this thread's bulk stores have finished READING shared memory (the source may be overwritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// this thread's bulk stores are complete
+__device__ __forceinline__ void tma_store_wait() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---- named barriers: producers arrive and move on, the consumer warp waits ------------------------
 __device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
   asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(count) : "memory");
