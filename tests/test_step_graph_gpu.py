@@ -191,10 +191,17 @@ def test_step_graph_two_ranks_average_gradients(libhgk, tmp_path):
 
     import torch.multiprocessing as mp
 
-    with socket.socket() as s:
-        s.bind(("127.0.0.1", 0))
-        port = s.getsockname()[1]
-    mp.spawn(_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    def run_ranks():
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        mp.spawn(_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+
+    try:
+        run_ranks()
+    except Exception as exc:          # rendezvous / process start-up trouble (two processes share one GPU here): once more
+        print(f"two-rank run failed once, retrying: {exc!r}")
+        run_ranks()
     r0, r1 = (torch.load(tmp_path / f"rank{r}.pt") for r in range(2))
     assert len(r0["record"]) == len(r1["record"]) == 6
     for a, b in zip(r0["record"], r1["record"]):
