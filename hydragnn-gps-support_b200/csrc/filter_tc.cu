@@ -197,10 +197,13 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
     fence_after_sync();
     F_PROF(3)
 
-    // ---- H = ssp(Z0 + b0): my 32 columns ----
+    // ---- H = ssp(Z0 + b0): my 32 columns.  They go to TMEM first (the raw value is the hi operand: kind::tf32
+    // ignores the 13 low mantissa bits of an A operand in TMEM too, profiles/_scratch/tf32_round_probe.cu), the
+    // second GEMM is started, and only then is h written out -- under its MMAs ----
     const int c0 = quarter * 32;
+    uint32_t z[32];
     {
-      uint32_t z[32], lo[32];
+      uint32_t lo[32];
       tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
       tmem_ld_wait();
 #pragma unroll
@@ -211,18 +214,6 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
         z[j] = __float_as_uint(hv);
         lo[j] = __float_as_uint(lo_);
       }
-      if (TMA && (p.tma_out & 1)) {
-        store_quarter(&tm_h, z, tile);
-      } else if (ok) {
-        float* hrow = p.h + e * kFilt + c0;
-#pragma unroll
-        for (int j = 0; j < 32; j += 8)
-          st_global_v8(hrow + j,
-                       make_float4(__uint_as_float(z[j]), __uint_as_float(z[j + 1]), __uint_as_float(z[j + 2]), __uint_as_float(z[j + 3])),
-                       make_float4(__uint_as_float(z[j + 4]), __uint_as_float(z[j + 5]), __uint_as_float(z[j + 6]), __uint_as_float(z[j + 7])));
-      }
-#pragma unroll
-      for (int j = 0; j < 32; ++j) z[j] &= 0xffffe000u;            // hi part
       tmem_st32(tmem + cs.lane_base + kColHhi + c0, z);
       tmem_st32(tmem + cs.lane_base + kColHlo + c0, lo);
       tmem_st_wait();
@@ -235,6 +226,16 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
       mma3_ts<kFilt>(tmem + kColZ, tmem + kColHhi, tmem + kColHlo, dW1, kIdesc, false);  // Z1 = H W1^T
       mma_commit(&bar);
     }
+    if (TMA && (p.tma_out & 1)) {
+      store_quarter(&tm_h, z, tile);
+    } else if (ok) {
+      float* hrow = p.h + e * kFilt + c0;
+#pragma unroll
+      for (int j = 0; j < 32; j += 8)
+        st_global_v8(hrow + j,
+                     make_float4(__uint_as_float(z[j]), __uint_as_float(z[j + 1]), __uint_as_float(z[j + 2]), __uint_as_float(z[j + 3])),
+                     make_float4(__uint_as_float(z[j + 4]), __uint_as_float(z[j + 5]), __uint_as_float(z[j + 6]), __uint_as_float(z[j + 7])));
+    }
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);   // argument in [0, pi]
     F_PROF(5)
     mbar_wait(&bar, parity);
@@ -244,7 +245,6 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
 
     // ---- W = (Z1 + b1) * C ----
     {
-      uint32_t z[32];
       tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
       tmem_ld_wait();
       if (TMA && (p.tma_out & 2)) {
