@@ -140,59 +140,65 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
     }
   };
   F_PROF_DECL
-  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    F_PROF(7)
-    const int64_t e = tile * kFilt + cs.row_local;
-    const bool ok = e < p.E;
-    const float dist = ok ? __ldg(p.d + e) : 0.f;
-
-    // ---- X = [gauss | raw]: this thread's 16 of the 64 columns -> TMEM (hi, lo) ----
-    {
-      uint32_t xh[16], xl[16];
-      float val[16];
-      if (quarter < 3) {                                // columns 0..47: gaussians only
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float t = dist - off_s[quarter * 16 + j];
-          val[j] = fast_exp2(c2 * (t * t));
-        }
-      } else {                                          // columns 48..63: last gaussians | pad | raw | pad
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int k = 48 + j;                         // compile-time after unrolling
-          if (k < G) { const float t = dist - off_s[k]; val[j] = fast_exp2(c2 * (t * t)); }
-          else val[j] = 0.f;
-        }
-        if (R > 0 && ok) {
-#pragma unroll
-          for (int c = 0; c < R; c += 4) {
-            const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + c));
-            val[GP - 48 + c] = r4.x; val[GP - 48 + c + 1] = r4.y; val[GP - 48 + c + 2] = r4.z; val[GP - 48 + c + 3] = r4.w;
-          }
-        }
-      }
+  // X = [gauss | raw] of one edge row: this thread's 16 of the 64 columns -> TMEM (hi, lo)
+  auto build_x = [&](int64_t e, bool ok, float dist) {
+    uint32_t xh[16], xl[16];
+    float val[16];
+    if (quarter < 3) {                                  // columns 0..47: gaussians only
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
-        float hi_, lo_;
-        split_tf32(ok ? val[j] : 0.f, hi_, lo_);
-        xh[j] = __float_as_uint(hi_);
-        xl[j] = __float_as_uint(lo_);
+        const float t = dist - off_s[quarter * 16 + j];
+        val[j] = fast_exp2(c2 * (t * t));
       }
-      tmem_st16(tmem + cs.lane_base + kColXhi + quarter * 16, xh);
-      tmem_st16(tmem + cs.lane_base + kColXlo + quarter * 16, xl);
-      tmem_st_wait();
+    } else {                                            // columns 48..63: last gaussians | pad | raw | pad
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int k = 48 + j;                           // compile-time after unrolling
+        if (k < G) { const float t = dist - off_s[k]; val[j] = fast_exp2(c2 * (t * t)); }
+        else val[j] = 0.f;
+      }
+      if (R > 0 && ok) {
+#pragma unroll
+        for (int c = 0; c < R; c += 4) {
+          const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.raw + e * p.ldr + c));
+          val[GP - 48 + c] = r4.x; val[GP - 48 + c + 1] = r4.y; val[GP - 48 + c + 2] = r4.z; val[GP - 48 + c + 3] = r4.w;
+        }
+      }
     }
-    F_PROF(0)
-    fence_before_sync();
-    __syncthreads();
-    F_PROF(1)
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float hi_, lo_;
+      split_tf32(ok ? val[j] : 0.f, hi_, lo_);
+      xh[j] = __float_as_uint(hi_);
+      xl[j] = __float_as_uint(lo_);
+    }
+    tmem_st16(tmem + cs.lane_base + kColXhi + quarter * 16, xh);
+    tmem_st16(tmem + cs.lane_base + kColXlo + quarter * 16, xl);
+    tmem_st_wait();
+  };
+  auto issue_mma0 = [&]() {                             // Z0 = X W0'^T (all threads call; one issues)
     if (warp_u == 0 && elect_one_sync()) {
       fence_after_sync();
-      mma3_ts<kK0>(tmem + kColZ, tmem + kColXhi, tmem + kColXlo, dW0, kIdesc, false);   // Z0 = X W0'^T
+      mma3_ts<kK0>(tmem + kColZ, tmem + kColXhi, tmem + kColXlo, dW0, kIdesc, false);
       mma_commit(&bar);
     }
-    F_PROF(2)
-    mbar_wait(&bar, parity);
+  };
+  // Software pipeline over the CTA's tiles: X of the next tile is built while the second GEMM of the current one
+  // runs (the X columns are free once Z0 is complete), and the next tile's first GEMM is issued as soon as every
+  // thread has taken its Z1 columns out of TMEM, so the w epilogue runs under it.
+  int64_t e = (int64_t)blockIdx.x * kFilt + cs.row_local;
+  bool ok = e < p.E;
+  float dist = ok ? __ldg(p.d + e) : 0.f;
+  if ((int64_t)blockIdx.x < num_tiles) {
+    build_x(e, ok, dist);
+    fence_before_sync();
+    __syncthreads();
+    issue_mma0();
+  }
+  const int c0 = quarter * 32;
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    F_PROF(7)
+    mbar_wait(&bar, parity);                            // Z0 of this tile
     parity ^= 1;
     fence_after_sync();
     F_PROF(3)
@@ -200,7 +206,6 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
     // ---- H = ssp(Z0 + b0): my 32 columns.  They go to TMEM first (the raw value is the hi operand: kind::tf32
     // ignores the 13 low mantissa bits of an A operand in TMEM too, profiles/_scratch/tf32_round_probe.cu), the
     // second GEMM is started, and only then is h written out -- under its MMAs ----
-    const int c0 = quarter * 32;
     uint32_t z[32];
     {
       uint32_t lo[32];
@@ -237,32 +242,42 @@ k_schnet_filter_fwd(const FilterArgs p, const __grid_constant__ CUtensorMap tm_h
                      make_float4(__uint_as_float(z[j + 4]), __uint_as_float(z[j + 5]), __uint_as_float(z[j + 6]), __uint_as_float(z[j + 7])));
     }
     const float env = 0.5f * (__cosf(dist * p.pi_over_cutoff) + 1.0f);   // argument in [0, pi]
+    const bool ok_w = ok;
+    const int64_t e_w = e;
+    // the next tile's X, under the second GEMM
+    const int64_t next = tile + gridDim.x;
+    if (next < num_tiles) {
+      e = next * kFilt + cs.row_local;
+      ok = e < p.E;
+      dist = ok ? __ldg(p.d + e) : 0.f;
+      build_x(e, ok, dist);
+    }
     F_PROF(5)
-    mbar_wait(&bar, parity);
+    mbar_wait(&bar, parity);                            // Z1 of this tile
     parity ^= 1;
     fence_after_sync();
     F_PROF(6)
 
     // ---- W = (Z1 + b1) * C ----
-    {
-      tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
-      tmem_ld_wait();
-      if (TMA && (p.tma_out & 2)) {
+    tmem_ld32(tmem + cs.lane_base + kColZ + c0, z);
+    tmem_ld_wait();
+    fence_before_sync();
+    __syncthreads();                                    // everybody holds its Z1 columns, the next X is in TMEM
+    if (next < num_tiles) issue_mma0();                 // overwrites the Z columns: runs under the w epilogue
+    if (TMA && (p.tma_out & 2)) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) z[j] = __float_as_uint((__uint_as_float(z[j]) + b1_s[c0 + j]) * env);
-        store_quarter(&tm_w, z, tile);
-      } else if (ok) {
-        float* wrow = p.w + e * kFilt + c0;
+      for (int j = 0; j < 32; ++j) z[j] = __float_as_uint((__uint_as_float(z[j]) + b1_s[c0 + j]) * env);
+      store_quarter(&tm_w, z, tile);
+    } else if (ok_w) {
+      float* wrow = p.w + e_w * kFilt + c0;
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-          float o[8];
+      for (int j = 0; j < 32; j += 8) {
+        float o[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) o[i] = (__uint_as_float(z[j + i]) + b1_s[c0 + j + i]) * env;
-          st_global_v8(wrow + j, make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]));
-        }
+        for (int i = 0; i < 8; ++i) o[i] = (__uint_as_float(z[j + i]) + b1_s[c0 + j + i]) * env;
+        st_global_v8(wrow + j, make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]));
       }
     }
-    // the next tile's first barrier (after its X store) orders these Z reads before the next MMA
   }
   F_PROF(7)
   F_PROF_FLUSH
