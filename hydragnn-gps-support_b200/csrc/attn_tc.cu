@@ -890,7 +890,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
         if (g == 0) { tq0.load(p.q + h * D, p.ldq, q_at, seg_end); tg0.load(b.dout + h * D, b.lddo, q_at, seg_end); }
         else        { tq1.load(p.q + h * D, p.ldq, q_at, seg_end); tg1.load(b.dout + h * D, b.lddo, q_at, seg_end); }
       }
-      if (tl < BQ) {
+      if (!TMA && tl < BQ) {
         const int32_t qrow = q_at + tl;
         lse_r = 0.f; delta_r = 0.f;
         if (qrow < seg_end) {
@@ -903,7 +903,7 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       const int st = s & (NST - 1);
       float* base = smem + st * kStage;
       if (TMA) {
-        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested three of my steps ago
+        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested one of my steps ago (prologue: just now)
         int r, c;
         Tile<BQ, D, kKvGroup, 0>::coord_of(tl, 0, r, c);    // one 16-byte chunk of each tile per thread
         static_assert(Tile<BQ, D, kKvGroup, 0>::PER == 1, "one chunk per thread");
@@ -925,6 +925,14 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
         tg1.store_mn_as(tl, base + oGhi, base + oGlo);
       }
       if (tl < BQ) {
+        if (TMA) {                                     // staged in the group's idle time: loaded here, no prefetch
+          const int32_t qrow = seg_beg + s * BQ + tl;
+          lse_r = 0.f; delta_r = 0.f;
+          if (qrow < seg_end) {
+            lse_r = __ldg(b.lse + (int64_t)qrow * p.H + h);
+            delta_r = __ldg(b.delta + (int64_t)qrow * p.H + h);
+          }
+        }
         lse2_s[st][tl] = lse_r * kLog2e;
         delta_s[st][tl] = delta_r;
       }
@@ -939,7 +947,13 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
     fence_smem_to_async();
     fence_before_sync();
     named_bar_arrive(1, kKvPipeThreads);
-    if (g + 2 < nsub) load(seg_beg + (g + 2) * BQ);    // after the fence: it would wait for these loads
+    if (TMA) {
+      // TMA: the lo tiles are formed TWO of my steps ahead, after the hand-off to the issuer -- in the time the
+      // group would otherwise spend waiting for its MMAs -- so staging is off the step's critical path
+      if (g + 2 < nsub) stage(g + 2);
+    } else if (g + 2 < nsub) {
+      load(seg_beg + (g + 2) * BQ);                    // after the fence: it would wait for these loads
+    }
 
     // fp32 totals of the group's finished accumulator chains: [2 groups][dV | dK][D][BM] floats behind the
     // stages; this thread takes dV (ch == 0) or dK (ch == 1) of its group, all D columns of its row
@@ -1009,13 +1023,17 @@ k_attn_bwd_kv_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict_
       tmem_st_wait();
       KV_PROF(3)
 
-      if (s + 2 < nsub) stage(s + 2);                  // lo tiles (registers -> stage) of my next step
+      if (!TMA && s + 2 < nsub) stage(s + 2);          // registers -> stage of my next step
       KV_PROF(4)
-      fence_smem_to_async();
+      fence_smem_to_async();                           // (TMA: also publishes the lo tiles written after the last arrive)
       fence_before_sync();
       named_bar_arrive(2 + g, kKvGroup + 32);
       KV_PROF(5)
-      if (s + 4 < nsub) load(seg_beg + (s + 4) * BQ);  // global -> registers for the step after next
+      if (TMA) {
+        if (s + 4 < nsub) stage(s + 4);                // lo tiles of the step after next, while my MMAs run
+      } else if (s + 4 < nsub) {
+        load(seg_beg + (s + 4) * BQ);                  // global -> registers for the step after next
+      }
       KV_PROF(6)
     }
     mbar_wait(&bar[2], 0);                             // committed after the last step's MMAs
@@ -1172,7 +1190,7 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       const int st = s & (NST - 1);
       float* base = smem + st * kStage;
       if (TMA) {
-        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested three of my steps ago
+        mbar_wait(&full[st], (uint32_t)(s / NST) & 1u);     // requested one of my steps ago (prologue: just now)
         int r, c;
         Tile<BK, D, kKvGroup, 0>::coord_of(tl, 0, r, c);    // one 16-byte chunk of each tile per thread
         static_assert(Tile<BK, D, kKvGroup, 0>::PER == 1, "one chunk per thread");
@@ -1201,7 +1219,11 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
     fence_smem_to_async();
     fence_before_sync();
     named_bar_arrive(1, kKvPipeThreads);
-    if (g + 2 < nsub) load(seg_beg + (g + 2) * BK);
+    if (TMA) {                                         // lo tiles two of my steps ahead, in the idle time after a hand-off
+      if (g + 2 < nsub) stage(g + 2);
+    } else if (g + 2 < nsub) {
+      load(seg_beg + (g + 2) * BK);
+    }
 
     // fp32 totals of the group's finished accumulator chains: [2][D][BM] floats behind the stages;
     // this thread's 16 of the group's 32 columns
@@ -1248,11 +1270,15 @@ k_attn_bwd_q_pipe(const AttnTcArgs p, const AttnTcBwdArgs b, float* __restrict__
       tmem_st16(tmem + cs.lane_base + kColDP + set + col0, dv);
       tmem_st_wait();
 
-      if (s + 2 < nsub) stage(s + 2);
+      if (!TMA && s + 2 < nsub) stage(s + 2);
       fence_smem_to_async();
       fence_before_sync();
       named_bar_arrive(2 + g, kKvGroup + 32);
-      if (s + 4 < nsub) load(seg_beg + (s + 4) * BK);
+      if (TMA) {
+        if (s + 4 < nsub) stage(s + 4);                // lo tiles of the step after next, while my MMAs run
+      } else if (s + 4 < nsub) {
+        load(seg_beg + (s + 4) * BK);
+      }
     }
     mbar_wait(&bar[2], 0);
     fence_after_sync();
