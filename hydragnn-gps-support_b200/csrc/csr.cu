@@ -106,6 +106,10 @@ k_csr_scatter(const int32_t* __restrict__ key, int64_t E, int32_t N,
   }
 }
 
+// Segments up to this length are rank-sorted by one warp (O(len^2 / 32): 58 edges per row at config 5);
+// longer ones (a hub row, a per-graph key) go to k_csr_segsort_long.
+constexpr int32_t kSegsortWarpMax = 128;
+
 // One warp per segment: rank-by-counting sort of distinct int32 values.
 __global__ void __launch_bounds__(256)
 k_csr_segsort(const int32_t* __restrict__ rowptr, int64_t N,
@@ -116,12 +120,73 @@ k_csr_segsort(const int32_t* __restrict__ rowptr, int64_t N,
   for (int64_t n = warp; n < N; n += nwarps) {
     const int32_t beg = rowptr[n], end = rowptr[n + 1];
     const int32_t len = end - beg;
+    if (len > kSegsortWarpMax) continue;               // k_csr_segsort_long
     for (int32_t t = lane; t < len; t += 32) {
       const int32_t v = tmp[beg + t];
       int32_t rank = 0;
       for (int32_t s = 0; s < len; ++s) rank += (tmp[beg + s] < v) ? 1 : 0;
       perm[beg + rank] = v;
     }
+  }
+}
+
+// Long segments, one CTA each: the segment is cut into chunks of kSegChunk values, every chunk is sorted in shared
+// memory (bitonic network, padded with INT32_MAX) and written back in place; the rank of a value is then the sum over
+// the chunks of the number of smaller values (binary search: the values are distinct), and the value goes to its
+// place.  O(len log^2 chunk + len (len / chunk) log chunk) instead of O(len^2).
+constexpr int kSegChunk = 4096;
+
+__global__ void __launch_bounds__(256)
+k_csr_segsort_long(const int32_t* __restrict__ rowptr, int64_t N, int32_t* __restrict__ tmp, int32_t* __restrict__ perm) {
+  __shared__ int32_t buf[kSegChunk];
+  for (int64_t n = blockIdx.x; n < N; n += gridDim.x) {
+    const int32_t beg = rowptr[n], len = rowptr[n + 1] - beg;
+    if (len <= kSegsortWarpMax) continue;              // CTA-uniform
+    int32_t* seg = tmp + beg;
+    const int32_t nchunks = (len + kSegChunk - 1) / kSegChunk;
+    for (int32_t c = 0; c < nchunks; ++c) {
+      const int32_t c0 = c * kSegChunk;
+      const int32_t clen = min(kSegChunk, len - c0);
+      int32_t pot = 1;                                 // power of two >= clen
+      while (pot < clen) pot <<= 1;
+      for (int32_t i = threadIdx.x; i < pot; i += blockDim.x) buf[i] = i < clen ? seg[c0 + i] : INT32_MAX;
+      __syncthreads();
+      for (int32_t k = 2; k <= pot; k <<= 1) {
+        for (int32_t j = k >> 1; j > 0; j >>= 1) {
+          for (int32_t i = threadIdx.x; i < pot; i += blockDim.x) {
+            const int32_t partner = i ^ j;
+            if (partner > i) {
+              const int32_t a = buf[i], b2 = buf[partner];
+              const bool up = (i & k) == 0;
+              if ((a > b2) == up) { buf[i] = b2; buf[partner] = a; }
+            }
+          }
+          __syncthreads();
+        }
+      }
+      for (int32_t i = threadIdx.x; i < clen; i += blockDim.x) seg[c0 + i] = buf[i];
+      __syncthreads();
+    }
+    if (nchunks == 1) {
+      for (int32_t i = threadIdx.x; i < len; i += blockDim.x) perm[beg + i] = seg[i];
+    } else {
+      __threadfence_block();
+      for (int32_t i = threadIdx.x; i < len; i += blockDim.x) {
+        const int32_t v = seg[i];
+        int32_t rank = 0;
+        for (int32_t c = 0; c < nchunks; ++c) {
+          const int32_t* ch = seg + c * kSegChunk;
+          int32_t lo = 0, hi = min(kSegChunk, len - c * kSegChunk);
+          while (lo < hi) {                            // first position whose value is >= v
+            const int32_t mid = (lo + hi) >> 1;
+            if (ch[mid] < v) lo = mid + 1; else hi = mid;
+          }
+          rank += lo;
+        }
+        perm[beg + rank] = v;
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -159,6 +224,11 @@ int csr_build_impl(const int32_t* key, int64_t E, int64_t N, int32_t* rowptr,
     k_csr_scatter<<<blocks, 256, 0, st>>>(key, E, (int32_t)N, rowptr, slot, tmp);
     const int sblocks = (int)imin64(ceil_div(N, 8), (int64_t)kNumSM * 32);
     k_csr_segsort<<<sblocks, 256, 0, st>>>(rowptr, N, tmp, perm);
+    // rows longer than kSegsortWarpMax exist only if E / N allows one: skip the launch for the common case
+    if (E > kSegsortWarpMax) {
+      const int lblocks = (int)imin64(N, (int64_t)kNumSM * 4);
+      k_csr_segsort_long<<<lblocks, 256, 0, st>>>(rowptr, N, tmp, perm);
+    }
   }
   return check_launch("csr_build");
 }

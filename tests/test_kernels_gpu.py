@@ -36,7 +36,9 @@ def make_topo(ops, ei, N, sorted_side=None):
 
 
 # ----------------------------------------------------------------------------- CSR ---
-@pytest.mark.parametrize("N,E", [(1, 1), (7, 0), (50, 400), (1000, 20000), (8192, 475000), (3, 5000)])
+@pytest.mark.parametrize("N,E", [(1, 1), (7, 0), (50, 400), (1000, 20000), (8192, 475000), (3, 5000),
+                                 # long rows: one sorted chunk (<= 4096) and several chunks merged by rank
+                                 (2, 300), (3, 20000), (1, 9000)])
 def test_csr_build_bit_exact(ops, N, E):
     gen = torch.Generator().manual_seed(N + E)
     key = torch.randint(0, N, (E,), generator=gen, dtype=torch.int32)
