@@ -12,6 +12,7 @@
 // see the same mask.  All reductions over the N rows use a fixed slab / order: bit-reproducible.
 #include "hgk_common.cuh"
 #include "tc_common.cuh"
+#include "tma_host.cuh"
 
 namespace hgk {
 namespace tc {
@@ -48,6 +49,97 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, b
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+// ---- epilogue shared by the two kernels: lane = row, this thread's 64 of the 128 columns ----
+// `stage` / `tm_y` (TMA kernel): the tile leaves through shared memory ([4 column blocks][128 rows][32 floats],
+// 128-byte swizzle: row-per-thread 16-byte stores without bank conflicts) and four bulk tensor stores, which clip
+// at the matrix edge; NULL: row-per-thread global stores (one LSU wavefront per 16 bytes).
+__device__ __forceinline__ void linear_epilogue(const LinearArgs& p, const CtaSetup& cs, uint32_t tmem, int32_t row0, int32_t col0,
+                                                float* stage = nullptr, const CUtensorMap* tm_y = nullptr) {
+  const int64_t row = (int64_t)row0 + cs.row_local;
+  const bool row_ok = row < p.M;
+#pragma unroll
+  for (int cc = 0; cc < 64; cc += 32) {
+    const int c_tile = cs.half * 64 + cc;               // column inside the tile
+    float v[32];
+    for (int chunk = 0; chunk < p.chunks; ++chunk) {    // CTA uniform: tcgen05.ld is warp collective
+      uint32_t t[32];
+      tmem_ld32(tmem + cs.lane_base + (uint32_t)chunk * 128 + c_tile, t);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = chunk == 0 ? __uint_as_float(t[j]) : v[j] + __uint_as_float(t[j]);
+    }
+    const int col = col0 + c_tile;
+    if (row_ok && col < p.N) {                          // N is a multiple of 32: whole chunk in or out
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+          v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+        }
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (p.mask != nullptr) {
+        const uint4* mp = reinterpret_cast<const uint4*>(p.mask + row * p.N + col);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          const uint4 m = __ldg(mp + q);
+          const uint32_t w4[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const uint32_t byte = (w4[j >> 2] >> (8 * (j & 3))) & 0xffu;
+            v[16 * q + j] = byte ? v[16 * q + j] * p.scale : 0.f;
+          }
+        }
+      }
+      if (p.nz != nullptr) {
+        const float* np_ = p.nz + row * p.ldnz + col;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 z = __ldg(reinterpret_cast<const float4*>(np_ + j));
+          v[j] = z.x != 0.f ? v[j] * p.scale : 0.f;
+          v[j + 1] = z.y != 0.f ? v[j + 1] * p.scale : 0.f;
+          v[j + 2] = z.z != 0.f ? v[j + 2] * p.scale : 0.f;
+          v[j + 3] = z.w != 0.f ? v[j + 3] * p.scale : 0.f;
+        }
+      }
+      if (p.residual != nullptr) {
+        const float* rp = p.residual + row * p.ldr + col;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 r = __ldg(reinterpret_cast<const float4*>(rp + j));
+          v[j] += r.x; v[j + 1] += r.y; v[j + 2] += r.z; v[j + 3] += r.w;
+        }
+      }
+      if (stage == nullptr) {
+        float* yp = p.y + row * p.ldy + col;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(yp + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+    if (stage != nullptr) {                             // rows / columns outside the matrix are clipped by the store
+      float* rowp = stage + (c_tile >> 5) * (128 * 32) + cs.row_local * 32;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(rowp + ((j ^ (cs.row_local & 7)) << 2)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  }
+  if (stage != nullptr) {
+    fence_smem_to_async();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int blk = 0; blk < 4; ++blk)
+        if (col0 + blk * 32 < p.N) tma_store_2d(tm_y, stage + blk * (128 * 32), col0 + blk * 32, row0);
+      tma_store_commit();
+      tma_store_wait();
+    }
+  }
+}
 
 constexpr int kLinDepth = 4;                             // K chunks in flight (raw copies in shared memory)
 
@@ -172,72 +264,117 @@ k_linear_tc(const LinearArgs p) {
   mbar_wait(&bar, parity);                               // the last chunk's MMAs (K >= 32: at least one chunk)
   fence_after_sync();
 
-  // ---- epilogue: lane = row, this thread's 64 of the 128 columns ----
-  const int64_t row = (int64_t)row0 + cs.row_local;
-  const bool row_ok = row < p.M;
+  linear_epilogue(p, cs, tmem, row0, col0);
+  cta_teardown(tmem, kCols);
+}
+
+// ---- the same with TMA loads -----------------------------------------------------------------------------
+// x and w chunks ([128 x 32] boxes, or [32 x 128] of a transposed weight) land by cp.async.bulk.tensor in a ring of
+// four hi slots, all requested up front; the raw tile is the hi operand (kind::tf32 truncates), the threads form the
+// lo tiles in one of two buffers, so lo(c + 1) is computed while the MMAs of chunk c run.  Before, every chunk went
+// cp.async -> registers -> split -> hi and lo stores -> MMA -> wait, one after the other.
+template <bool TRANS_B>
+__global__ void __launch_bounds__(kThreads, 1)
+k_linear_tma(const LinearArgs p, const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+             const __grid_constant__ CUtensorMap tm_y) {
+  extern __shared__ __align__(1024) float smem_raw[];
+  float* const smem = smem_raw + (((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 2);
+  __shared__ __align__(8) uint64_t bar;                 // cta_setup
+  __shared__ __align__(8) uint64_t full[4];             // hi slot s has landed
+  __shared__ __align__(8) uint64_t done[2];             // the MMAs that read lo buffer b are complete
+  __shared__ uint32_t tmem_slot;
+  constexpr int kT = 128 * kBK;                         // floats per tile
+  float* const Ahi = smem;                              // [4][kT]
+  float* const Bhi = smem + 4 * kT;                     // [4][kT]
+  float* const Alo = smem + 8 * kT;                     // [2][kT]
+  float* const Blo = smem + 10 * kT;                    // [2][kT]
+  if (threadIdx.x == 0) {
 #pragma unroll
-  for (int cc = 0; cc < 64; cc += 32) {
-    const int c_tile = cs.half * 64 + cc;               // column inside the tile
-    float v[32];
-    for (int chunk = 0; chunk < p.chunks; ++chunk) {    // CTA uniform: tcgen05.ld is warp collective
-      uint32_t t[32];
-      tmem_ld32(tmem + cs.lane_base + (uint32_t)chunk * 128 + c_tile, t);
-      tmem_ld_wait();
+    for (int i = 0; i < 4; ++i) mbar_init(&full[i], 1);
+    mbar_init(&done[0], 1); mbar_init(&done[1], 1);
+  }
+  const CtaSetup cs = cta_setup(&bar, &tmem_slot, p.tmem_cols);
+  const uint32_t tmem = cs.tmem;
+  const int warp_u = warp_id_uniform();
+  const int32_t row0 = (int32_t)blockIdx.x * 128;
+  const int32_t col0 = (int32_t)blockIdx.y * 128;
+  const int nchunks = p.K / kBK;
+  constexpr uint32_t kIdesc = idesc_tf32(128, 128) | (TRANS_B ? kIdescBMajorMN : 0u);
+
+  auto request = [&](int c) {                           // one thread: chunk c into slot c % 4
+    const int sl = c & 3;
+    mbar_expect_tx(&full[sl], 2u * kT * (uint32_t)sizeof(float));
+    tma_load_2d(Ahi + sl * kT, &tm_x, &full[sl], c * kBK, row0);
+    if (!TRANS_B) {
+      tma_load_2d(Bhi + sl * kT, &tm_w, &full[sl], c * kBK, col0);
+    } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = chunk == 0 ? __uint_as_float(t[j]) : v[j] + __uint_as_float(t[j]);
+      for (int blk = 0; blk < 4; ++blk) tma_load_2d(Bhi + sl * kT + blk * (kBK * 32), &tm_w, &full[sl], col0 + blk * 32, c * kBK);
     }
-    const int col = col0 + c_tile;
-    if (row_ok && col < p.N) {                          // N is a multiple of 32: whole chunk in or out
-      if (p.bias != nullptr) {
+  };
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < 4 && c < nchunks; ++c) request(c);
+  }
+  using TA = Tile<128, kBK>;                            // rows = output rows (or features), 32 k per chunk
+  using TBT = Tile<kBK, 128>;                           // TRANS_B: rows = k
+  uint32_t done_phase[2] = {0, 0};
+  for (int c = 0; c < nchunks; ++c) {
+    const int sl = c & 3, lb = c & 1;
+    if (c >= 2) {                                       // lo buffer lb was read by the MMAs of chunk c - 2
+      mbar_wait(&done[lb], done_phase[lb]);
+      done_phase[lb] ^= 1;
+      // ... and so was hi slot (c - 2) % 4: it takes chunk c + 2
+      if (threadIdx.x == 0 && c + 2 >= 4 && c + 2 < nchunks) request(c + 2);
+    }
+    mbar_wait(&full[sl], (uint32_t)(c >> 2) & 1u);
+    const float* ah = Ahi + sl * kT;
+    const float* bh = Bhi + sl * kT;
+    float* al = Alo + lb * kT;
+    float* bl = Blo + lb * kT;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
-          v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-        }
+    for (int it = 0; it < TA::PER; ++it) {
+      int r, cc;
+      TA::coord(it, r, cc);
+      const int off = TA::mn_off(r, cc);
+      const float4 v = *reinterpret_cast<const float4*>(ah + off);
+      float4 h, l;
+      split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+      *reinterpret_cast<float4*>(al + off) = l;
+    }
+    constexpr int kPerB = TRANS_B ? TBT::PER : TA::PER;
+#pragma unroll
+    for (int it = 0; it < kPerB; ++it) {
+      int r, cc;
+      if (TRANS_B) TBT::coord(it, r, cc); else TA::coord(it, r, cc);
+      const int off = TRANS_B ? TBT::mn_off(r, cc) : TA::mn_off(r, cc);
+      const float4 v = *reinterpret_cast<const float4*>(bh + off);
+      float4 h, l;
+      split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+      *reinterpret_cast<float4*>(bl + off) = l;
+    }
+    publish_operands();
+    if (warp_u == 0 && elect_one_sync()) {
+      fence_after_sync();
+      const int k0 = c * kBK;
+      const int acc = k0 / p.chunk_k;
+      const OperandDesc dA = operand_desc_k32(ah, al);
+      const bool accumulate = k0 > acc * p.chunk_k;
+      if (TRANS_B) {
+        const OperandDesc dB = operand_desc_mn<kBK>(bh, bl);
+        mma3_ss_k32_mn<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, accumulate);
+      } else {
+        const OperandDesc dB = operand_desc_k32(bh, bl);
+        mma3_ss_k32<kBK>(tmem + (uint32_t)acc * 128, dA, dB, kIdesc, accumulate);
       }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-      }
-      if (p.mask != nullptr) {
-        const uint4* mp = reinterpret_cast<const uint4*>(p.mask + row * p.N + col);
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const uint4 m = __ldg(mp + q);
-          const uint32_t w4[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const uint32_t byte = (w4[j >> 2] >> (8 * (j & 3))) & 0xffu;
-            v[16 * q + j] = byte ? v[16 * q + j] * p.scale : 0.f;
-          }
-        }
-      }
-      if (p.nz != nullptr) {
-        const float* np_ = p.nz + row * p.ldnz + col;
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 z = __ldg(reinterpret_cast<const float4*>(np_ + j));
-          v[j] = z.x != 0.f ? v[j] * p.scale : 0.f;
-          v[j + 1] = z.y != 0.f ? v[j + 1] * p.scale : 0.f;
-          v[j + 2] = z.z != 0.f ? v[j + 2] * p.scale : 0.f;
-          v[j + 3] = z.w != 0.f ? v[j + 3] * p.scale : 0.f;
-        }
-      }
-      if (p.residual != nullptr) {
-        const float* rp = p.residual + row * p.ldr + col;
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 r = __ldg(reinterpret_cast<const float4*>(rp + j));
-          v[j] += r.x; v[j + 1] += r.y; v[j + 2] += r.z; v[j + 3] += r.w;
-        }
-      }
-      float* yp = p.y + row * p.ldy + col;
-#pragma unroll
-      for (int j = 0; j < 32; j += 4)
-        *reinterpret_cast<float4*>(yp + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      mma_commit(&done[lb]);
     }
   }
-  cta_teardown(tmem, kCols);
+  // the last (up to two) chunks' MMAs
+  if (nchunks >= 2) { const int lb = (nchunks - 2) & 1; mbar_wait(&done[lb], done_phase[lb]); done_phase[lb] ^= 1; }
+  { const int lb = (nchunks - 1) & 1; mbar_wait(&done[lb], done_phase[lb]); }
+  fence_after_sync();
+  linear_epilogue(p, cs, tmem, row0, col0, Ahi, &tm_y);   // every MMA is complete: the hi slots are free
+  cta_teardown(tmem, p.tmem_cols);
 }
 
 }  // namespace tc
@@ -549,6 +686,24 @@ extern "C" int hgk_linear_tc(float* y, int64_t ldy, const float* x, int64_t ldx,
     configured[trans_w ? 1 : 0] = true;
   }
   dim3 grid((unsigned)ceil_div(M, 128), (unsigned)ceil_div(N, 128));
+  // TMA-fed kernel (HGK_LINEAR_TMA=0: the cp.async one, for A/B runs; also when the driver will not encode the maps)
+  static const bool want_tma = [] { const char* e = getenv("HGK_LINEAR_TMA"); return !(e && e[0] == '0'); }();
+  CUtensorMap tm_x, tm_w, tm_y;
+  if (want_tma && tma::rows_map_32(&tm_x, x, M, K, ldx, 128) &&
+      (trans_w ? tma::rows_map_32(&tm_w, w, K, N, ldw, 32) : tma::rows_map_32(&tm_w, w, N, K, ldw, 128)) &&
+      tma::rows_map_128b(&tm_y, y, M, N, ldy, 128)) {
+    const size_t smem_tma = sizeof(float) * 12 * 128 * tc::kBK + 1024;   // 4 + 4 hi slots, 2 + 2 lo buffers, alignment slack
+    static bool configured_tma[2] = {false, false};
+    if (!configured_tma[trans_w ? 1 : 0]) {
+      err = trans_w ? cudaFuncSetAttribute(tc::k_linear_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma)
+                    : cudaFuncSetAttribute(tc::k_linear_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tma);
+      if (err != cudaSuccess) return fail(HGK_ERR_CUDA, "linear_tc: smem opt-in: %s", cudaGetErrorString(err));
+      configured_tma[trans_w ? 1 : 0] = true;
+    }
+    if (trans_w) tc::k_linear_tma<true><<<grid, tc::kThreads, smem_tma, (cudaStream_t)stream>>>(a, tm_x, tm_w, tm_y);
+    else tc::k_linear_tma<false><<<grid, tc::kThreads, smem_tma, (cudaStream_t)stream>>>(a, tm_x, tm_w, tm_y);
+    return check_launch("linear_tc(tma)");
+  }
   if (trans_w) tc::k_linear_tc<true><<<grid, tc::kThreads, smem, (cudaStream_t)stream>>>(a);
   else tc::k_linear_tc<false><<<grid, tc::kThreads, smem, (cudaStream_t)stream>>>(a);
   return check_launch("linear_tc");

@@ -466,6 +466,35 @@ __device__ __forceinline__ void mma3_ss_mn(uint32_t d_tmem, const OperandDesc& a
     mma_tf32_ss(d_tmem, a.hi + adv, b.hi + adv, idesc, 1);
   }
 }
+// D (+)= A B^T with A = [M x KD] and B = [N x KD] row tiles in the SWIZZLE_128B_BASE32B layout, both read K-major
+// (operand_desc_k32): 32 bytes of every row per MMA.
+template <int KD>
+__device__ __forceinline__ void mma3_ss_k32(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                            uint32_t idesc, bool accumulate) {
+  static_assert(KD <= 32, "one 128-byte row holds 32 k values");
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv = static_cast<uint64_t>(j * 2);
+    mma_tf32_ss(d_tmem, a.lo + adv, b.hi + adv, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.lo + adv, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv, b.hi + adv, idesc, 1);
+  }
+}
+// D (+)= A B with A = [M x KD] row tile read K-major and B = [KD rows (k) x N] MN-major blocks; `idesc` must carry
+// kIdescBMajorMN.
+template <int KD>
+__device__ __forceinline__ void mma3_ss_k32_mn(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
+                                               uint32_t idesc, bool accumulate) {
+  static_assert(KD <= 32, "one 128-byte row holds 32 k values");
+#pragma unroll
+  for (int j = 0; j < KD / 8; ++j) {
+    const uint64_t adv_a = static_cast<uint64_t>(j * 2);
+    const uint64_t adv_b = static_cast<uint64_t>(j * (8 * 128 / 16));
+    mma_tf32_ss(d_tmem, a.lo + adv_a, b.hi + adv_b, idesc, accumulate || j > 0);
+    mma_tf32_ss(d_tmem, a.hi + adv_a, b.lo + adv_b, idesc, 1);
+    mma_tf32_ss(d_tmem, a.hi + adv_a, b.hi + adv_b, idesc, 1);
+  }
+}
 // D (+)= A B with A = [M x KD] K-major and B = [KD rows (k) x N] MN-major; `idesc` must carry kIdescBMajorMN.
 template <int KD>
 __device__ __forceinline__ void mma3_ss_bmn(uint32_t d_tmem, const OperandDesc& a, const OperandDesc& b,
