@@ -22,6 +22,7 @@ from ..globalAtt.gps import GPSConv
 from ..graph import pool_topo
 from ..nn import BatchNorm, FactoredEdgeAttr
 from ..ops import segment_sum
+from ..ops.node import linear_fast
 from ..utils.model import activation_function_selection, loss_function_selection
 
 
@@ -158,7 +159,8 @@ class Base(Module):
         """Node / edge input embeddings when global attention is on (Base.py:229-243)."""
         x = self.pos_emb(data.pe)
         if self.input_dim:
-            x = self.node_lin(torch.cat((self.node_emb(data.x.float()), x), 1))
+            # [N, 2 hidden] -> hidden on the tensor cores when the widths allow it (ops/node.py: linear_fast)
+            x = linear_fast(torch.cat((self.node_emb(data.x.float()), x), 1), self.node_lin.weight, self.node_lin.bias)
         if self.is_edge_model:
             # e = rel_pos_emb(rel_pe)  [or edge_lin(cat(edge_emb(edge_attr), rel_pos_emb(rel_pe)))],
             # all bias-free Linears: handed to the convs in factored form (see nn.FactoredEdgeAttr)

@@ -1,0 +1,29 @@
+import os, sys, torch
+ROOT="/root/repo"; sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "hydragnn-gps-support_b200"))
+import bench
+from hydragnn.graph import Data
+from hydragnn.models import create_model
+from hydragnn.train import train_step
+from hydragnn.utils import synthetic as syn
+from hydragnn.utils.distributed import get_distributed_model
+name="schnet_gps_fesi1024"; dev=torch.device("cuda:0")
+torch.backends.cuda.matmul.allow_tf32=False
+spec=syn.WORKLOADS[name]
+host=bench.build_batch_gpu(name, syn.sample_graphs(name, spec["graphs_per_gpu"]), dev)
+model=get_distributed_model(create_model(**spec["arch"]))
+opt=torch.optim.AdamW(model.module.parameters(), lr=1e-3)
+res=bench.to_data(host, dev, Data)
+def step():
+    d=Data(**{k:(v.detach().clone() if k in ("edge_index","pos") else v) for k,v in res.__dict__.items()})
+    train_step(model, opt, d, compute_grad_energy=spec["forces"])
+for _ in range(4): step()
+torch.cuda.synchronize()
+with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA, torch.profiler.ProfilerActivity.CPU], record_shapes=True) as prof:
+    step(); torch.cuda.synchronize()
+rows=[]
+for e in prof.key_averages(group_by_input_shape=True):
+    if e.key in ("aten::mm","aten::addmm","aten::bmm","aten::mv","aten::matmul","aten::linear"):
+        t=getattr(e,"device_time_total",0) or getattr(e,"cuda_time_total",0)
+        rows.append((t, e.count, e.key, str(e.input_shapes)))
+rows.sort(reverse=True)
+for r in rows[:25]: print(f"{r[0]:8.1f} us {r[1]:3d}x {r[2]:12s} {r[3]}")
