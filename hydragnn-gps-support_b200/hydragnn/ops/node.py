@@ -15,6 +15,8 @@ dropout mask / residual applied in the accumulator read-out, `hgk_bn_stats` + `h
 and bias gradients.  Dropout masks are torch's own Bernoulli draws (uint8), so the random stream is
 torch's; forward and backward read the same mask.
 """
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -176,6 +178,48 @@ def dropout_mask(shape, p, device):
 
 
 # ------------------------------------------------------------------ autograd: Linear ---
+# Weight gradients on a side stream.  In the backward pass of a Linear the weight / bias gradient (hgk_wgrad_rows)
+# and the input gradient (hgk_linear_tc) are independent and both are small grids (64-192 CTAs on 148 SMs): run side
+# by side they fill the GPU.  Done only while a CUDA graph is being captured (train/step_graph.py, graphed_tail.py),
+# where the fork and the join are graph edges and cost nothing at replay; eagerly the event calls would cost more
+# host time than the overlap saves.  HYDRAGNN_SIDE_WGRAD=0 switches it off.
+_SIDE_WGRAD = os.environ.get("HYDRAGNN_SIDE_WGRAD", "1") != "0"
+_side_streams = {}
+
+
+class _SideWgrad:
+    """`with side: ...` runs the enclosed launches on the side stream (which first waits for the work already on
+    the current stream); `side.join()` makes the current stream wait for them.  Inactive outside a capture."""
+
+    def __init__(self, tensor):
+        self.active = bool(_SIDE_WGRAD and tensor.is_cuda and torch.cuda.is_current_stream_capturing())
+        self.used = False
+        if self.active:
+            dev = tensor.device
+            self.cur = torch.cuda.current_stream(dev)
+            if dev not in _side_streams:
+                _side_streams[dev] = torch.cuda.Stream(dev)
+            self.side = _side_streams[dev]
+            self.ctx = None
+
+    def __enter__(self):
+        if self.active:
+            self.side.wait_stream(self.cur)
+            self.ctx = torch.cuda.stream(self.side)
+            self.ctx.__enter__()
+            self.used = True
+        return self
+
+    def __exit__(self, *exc):
+        if self.active:
+            self.ctx.__exit__(*exc)
+        return False
+
+    def join(self):
+        if self.active and self.used:
+            self.cur.wait_stream(self.side)
+
+
 class LinearTC(torch.autograd.Function):
     """y = x W^T + b on the tensor cores.  Backward: input gradient by the same kernel on the
     transposed weight, weight / bias gradients by hgk_wgrad_rows; when the backward pass is itself
@@ -195,10 +239,13 @@ class LinearTC(torch.autograd.Function):
             gw = g.t() @ x if ctx.needs_input_grad[1] else None
             gb = g.sum(0) if ctx.has_bias and ctx.needs_input_grad[2] else None
             return gx, gw, gb
-        gx = linear_tc(g, weight, trans_w=True) if ctx.needs_input_grad[0] else None
+        side = _SideWgrad(g)
         gw = gb = None
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            gw, gb = wgrad_rows(g, x, want_bias=ctx.has_bias)
+            with side:
+                gw, gb = wgrad_rows(g, x, want_bias=ctx.has_bias)
+        gx = linear_tc(g, weight, trans_w=True) if ctx.needs_input_grad[0] else None
+        side.join()
         return gx, gw, gb
 
 
@@ -239,11 +286,14 @@ class GpsTailPre(torch.autograd.Function):
     def backward(ctx, *grads):
         x, in_w, mask = ctx.saved_tensors
         dt1, dqkv = grads if ctx.has_local else (None, grads[0])
+        side = _SideWgrad(dqkv)
+        with side:
+            dw, db = wgrad_rows(dqkv, x)
         dx = linear_tc(dqkv, in_w, trans_w=True, residual=dt1)
-        dw, db = wgrad_rows(dqkv, x)
         dh = None
         if ctx.has_local:
             dh = mask_axpy(dt1, mask, ctx.scale) if mask is not None else dt1
+        side.join()
         return dx, dh, dw, db, None
 
 
@@ -283,9 +333,12 @@ class GpsTailPost(torch.autograd.Function):
         scale, nv = ctx.scale, ctx.nv
         r3 = bn_bwd(gy, t3, BnParams(mean3, rstd3, g3, None), mask_a=m4, scale_a=scale, n_valid=nv)
         dt3, dz4 = r3["dta"], r3["dza"]                       # dz4: gradient at W2's output (behind its dropout)
-        dw2, db2 = wgrad_rows(dz4, u)
+        side = _SideWgrad(gy)                                 # the three weight gradients run beside the main chain
+        with side:
+            dw2, db2 = wgrad_rows(dz4, u)
         dzu = linear_tc(dz4, w2, trans_w=True, nz=u, scale=scale)      # through dropout and ReLU: where u != 0
-        dw1, db1 = wgrad_rows(dzu, s)
+        with side:
+            dw1, db1 = wgrad_rows(dzu, s)
         ds = linear_tc(dzu, w1, trans_w=True, residual=dt3)
         p2 = BnParams(mean2, rstd2, g2, None)
         if t1 is not None:
@@ -297,7 +350,9 @@ class GpsTailPost(torch.autograd.Function):
             dt1, dt2, dz2 = None, r["dta"], r["dza"]
             dg1 = dbe1 = None
             dg2, dbe2 = r["dgamma_a"], r["dbeta_a"]
-        dwo, dbo = wgrad_rows(dz2, o)
+        with side:
+            dwo, dbo = wgrad_rows(dz2, o)
         do = linear_tc(dz2, out_w, trans_w=True)
+        side.join()
         return (dt2, dt1, do, dwo, dbo, dw1, db1, dw2, db2, dg1, dbe1, dg2, dbe2, r3["dgamma_a"], r3["dbeta_a"],
                 None, None)
