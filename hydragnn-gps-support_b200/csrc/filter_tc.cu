@@ -1044,9 +1044,9 @@ extern "C" int hgk_cfconv_filter_bwd(float* dz0, const float* g, int64_t ldg, co
 
 extern "C" int64_t hgk_wgrad_tn_partials(int64_t E) {
   if (E <= 0) return 0;
-  // two CTAs per SM; at least two 32-row tiles per CTA so that small inputs do not write more
+  // two CTAs per SM; at least four 32-row tiles per CTA so that small inputs (node rows: 8192) do not write more
   // partial sums than they read operands
-  return imin64(ceil_div(E, 64), 2 * (int64_t)kNumSM);
+  return imin64(ceil_div(E, 128), 2 * (int64_t)kNumSM);
 }
 
 static int wgrad_tn_impl(float* dw_partial, float* db_partial, const float* a, int64_t lda, const int32_t* a_idx,
