@@ -177,6 +177,20 @@ def dropout_mask(shape, p, device):
     return keep, 1.0 / (1.0 - p)
 
 
+def dropout_masks(shapes, p, device):
+    """Several keep masks from ONE Bernoulli launch (each a contiguous chunk of one buffer) + the common scale."""
+    if p <= 0.0:
+        return [None] * len(shapes), 1.0
+    sizes = [int(a) * int(b) for a, b in shapes]
+    # chunk starts kept 16-byte aligned (the kernels read the masks with 16-byte loads)
+    starts, total = [], 0
+    for n in sizes:
+        starts.append(total)
+        total += (n + 15) // 16 * 16
+    buf = torch.empty(total, dtype=torch.uint8, device=device).bernoulli_(1.0 - p)
+    return [buf[st:st + n].view(shape) for st, n, shape in zip(starts, sizes, shapes)], 1.0 / (1.0 - p)
+
+
 # ------------------------------------------------------------------ autograd: Linear ---
 # Weight gradients on a side stream.  In the backward pass of a Linear the weight / bias gradient (hgk_wgrad_rows)
 # and the input gradient (hgk_linear_tc) are independent and both are small grids (64-192 CTAs on 148 SMs): run side
@@ -306,7 +320,7 @@ class GpsTailPost(torch.autograd.Function):
         dev = x.device
         N, C = x.shape
         nv = valid_rows                     # device scalar for a padded batch (train/step_graph.py), else None
-        m2, scale = dropout_mask((N, C), p, dev)
+        (m2, m3, m4), scale = dropout_masks([(N, C), (N, w1.size(0)), (N, C)], p, dev)   # one launch for the three
         t2 = linear_tc(o, out_w, out_b, mask=m2, scale=scale, residual=x)
         p2 = BnParams(*bn_stats(t2, *bufs[1], n_valid=nv), g2, be2)
         if t1 is not None:
@@ -315,9 +329,7 @@ class GpsTailPost(torch.autograd.Function):
         else:
             p1 = None
             s = bn_apply(t2, p2)
-        m3, _ = dropout_mask((N, w1.size(0)), p, dev)
         u = linear_tc(s, w1, b1, relu=True, mask=m3, scale=scale)
-        m4, _ = dropout_mask((N, C), p, dev)
         t3 = linear_tc(u, w2, b2, mask=m4, scale=scale, residual=s)
         p3 = BnParams(*bn_stats(t3, *bufs[2], n_valid=nv), g3, be3)
         y = bn_apply(t3, p3)

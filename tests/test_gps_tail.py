@@ -63,7 +63,15 @@ def _run_case(device, with_local, p, N=200, C=128, heads=4, seed=0):
         drawn.append(m)
         return m, s
 
+    real_many = node.dropout_masks
+
+    def recording_many(shapes, prob, dev):
+        ms, s = real_many(shapes, prob, dev)
+        drawn.extend(ms)
+        return ms, s
+
     node.dropout_mask = recording
+    node.dropout_masks = recording_many
     try:
         xa = leaves[0]
         ha = leaves[1] if with_local else None
@@ -75,6 +83,7 @@ def _run_case(device, with_local, p, N=200, C=128, heads=4, seed=0):
         y.backward(gy)
     finally:
         node.dropout_mask = real
+        node.dropout_masks = real_many
     # order drawn: [h_local (pre)], out_proj, mlp hidden, mlp out
     scale = 1.0 / (1.0 - p) if p > 0 else 1.0
     xb = x.clone().requires_grad_(True)
