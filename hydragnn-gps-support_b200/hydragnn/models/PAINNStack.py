@@ -20,6 +20,7 @@ from torch import nn
 from ..graph import topo_of
 from ..nn import Sequential, edge_linear
 from ..ops import contract_node
+from ..ops.node import linear_fast
 from ..utils.model import get_edge_vectors_and_lengths
 from .Base import Base
 
@@ -41,6 +42,14 @@ def cosine_cutoff(edge_dist: torch.Tensor, cutoff: float):
     """0.5 (cos(pi d / cutoff) + 1) inside the cutoff, 0 outside."""
     inside = 0.5 * (torch.cos(torch.pi * edge_dist / cutoff) + 1)
     return torch.where(edge_dist < cutoff, inside, torch.zeros_like(inside))
+
+
+def _mlp_fast(seq, x):
+    """nn.Sequential of Linears and activations with the Linears on the tensor-core node-row kernel when the
+    widths allow it (ops/node.py: linear_fast; torch otherwise)."""
+    for layer in seq:
+        x = linear_fast(x, layer.weight, layer.bias) if isinstance(layer, nn.Linear) else layer(x)
+    return x
 
 
 class PainnMessage(nn.Module):
@@ -72,7 +81,7 @@ class PainnMessage(nn.Module):
             for layer in list(self.edge_filter)[1:]:
                 gate = layer(gate)
             fw = fw * gate
-        phi = self.scalar_message_mlp(node_scalar)                       # [N, 3F]
+        phi = _mlp_fast(self.scalar_message_mlp, node_scalar)            # [N, 3F]
         fw_sv, fw_ev, fw_s = fw[:, :Fs], fw[:, Fs:2 * Fs], fw[:, 2 * Fs:]
         phi_sv, phi_ev, phi_s = phi[:, :Fs], phi[:, Fs:2 * Fs], phi[:, 2 * Fs:]
         u = edge_diff / edge_dist                                        # [E,3]
@@ -97,9 +106,10 @@ class PainnUpdate(nn.Module):
             nn.Linear(node_size * 2, node_size), nn.SiLU(), nn.Linear(node_size, width_out))
 
     def forward(self, node_scalar, node_vector):
-        Uv = self.update_U(node_vector)
-        Vv = self.update_V(node_vector)
-        gates = self.update_mlp(torch.cat((torch.linalg.norm(Vv, dim=1), node_scalar), dim=1))
+        flat = node_vector.reshape(-1, node_vector.shape[-1])            # [3N, F] rows for the tensor-core Linear
+        Uv = linear_fast(flat, self.update_U.weight, self.update_U.bias).view_as(node_vector)
+        Vv = linear_fast(flat, self.update_V.weight, self.update_V.bias).view_as(node_vector)
+        gates = _mlp_fast(self.update_mlp, torch.cat((torch.linalg.norm(Vv, dim=1), node_scalar), dim=1))
         inner = torch.sum(Uv * Vv, dim=1)
         width = node_vector.shape[-1]
         if self.last_layer:
