@@ -141,7 +141,9 @@ def test_native_tail_matches_torch_ops(libhgk, with_local, p, N, C):
     (1, 128, 128, False, ()), (127, 128, 32, False, ("bias",)), (300, 384, 128, False, ("bias",)),
     (1000, 256, 128, False, ("bias", "relu", "mask")), (513, 128, 256, False, ("bias", "mask", "residual")),
     (700, 256, 128, True, ("nz",)), (8192, 128, 384, True, ("residual",)), (129, 128, 128, True, ()),
-    (260, 96, 64, False, ("bias", "residual")), (8192, 384, 128, False, ("bias",))])
+    (260, 96, 64, False, ("bias", "residual")), (8192, 384, 128, False, ("bias",)),
+    # long K: many wraps of the four-slot TMA ring, accumulation chains of 256 k
+    (200, 128, 1024, False, ("bias",)), (333, 256, 1024, True, ())])
 def test_linear_tc(libhgk, M, N, K, trans, opts):
     """hgk_linear_tc vs the torch ops (fp32 and, as the truth, fp64)."""
     from hydragnn.ops import node
